@@ -1,0 +1,259 @@
+// k_attn.cu — paged-KV decode attention (one query row per entry), sm_100a.
+//
+// Replaces vLLM's flash_attn_varlen_func call over the paged cache
+// (vllm v1/attention/backends/flash_attn.py:796-800) for the decode shape: nkv = nh = 16,
+// d = 64, so there is no GQA reuse and the op is a pure HBM stream (0.5 FMA per byte) —
+// tensor cores would not help; the design goal is to keep the TMA engine saturated.
+//
+// Persistent kernel, one CTA per SM, 17 warps:
+//   warp 16   producer: walks this CTA's work items (row, split) and issues ONE 64 KB
+//             cp.async.bulk (UBLKCP) per KV page into a 3-stage shared-memory ring,
+//             running ahead across item boundaries so the HBM stream never drains;
+//   warps 0-15 consumers, warp = head: QK (lane = token x half-of-d, 128-bit swizzled
+//             LDS), warp-shuffle online softmax in the log2 domain, PV (lane = token-group
+//             x 16-byte chunk), mbarrier hand-back of the stage.
+// Partial (o, m, l) per (row, split) go to scratch; attn_merge_kernel combines them.
+#include "common.cuh"
+
+using namespace cbx;
+namespace cbx { int init_attn(); }
+
+namespace {
+constexpr int kStages = 3;
+constexpr int kConsumerWarps = 16;
+constexpr int kThreads = (kConsumerWarps + 1) * 32;
+constexpr int kSmemBytes = kStages * CBX_PAGE_BYTES + 64;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct AttnPlan { int pps; int nsplit; };
+inline AttnPlan make_plan(int T, int max_kv_len) {
+  int max_pages = (max_kv_len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+  if (max_pages < 1) max_pages = 1;
+  int want = (148 * 6 + T - 1) / T;                 // splits per row to get ~6 items per SM
+  if (want < 1) want = 1;
+  if (want > 32) want = 32;
+  if (want > max_pages) want = max_pages;
+  AttnPlan p;
+  p.pps = (max_pages + want - 1) / want;
+  p.nsplit = (max_pages + p.pps - 1) / p.pps;
+  return p;
+}
+
+__global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
+    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt,
+    int bt_stride, const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len,
+    bf16* __restrict__ out, float* __restrict__ o_part, float2* __restrict__ ml_part, int T, int pps,
+    int nsplit) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
+  uint64_t* empty = full + kStages;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  const int n_items = T * nsplit;
+  uint32_t it = 0;                                    // pages streamed so far by this CTA
+
+  if (warp == kConsumerWarps) {
+    // ------------------------------------------------------------ producer warp
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      const int row = w / nsplit, split = w - row * nsplit;
+      const int len = kv_len[row];
+      const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+      const int p0 = split * pps, p1 = min(p0 + pps, n_pages);
+      const int32_t* btr = bt + (int64_t)row_seq[row] * bt_stride;
+      for (int pb = p0; pb < p1; pb += 32) {
+        const int nb = min(32, p1 - pb);
+        const int my_blk = lane < nb ? btr[pb + lane] : 0;
+        for (int j = 0; j < nb; ++j) {
+          const int blk = __shfl_sync(0xffffffffu, my_blk, j);
+          if (lane == 0) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            mbar_wait(&empty[s], ph ^ 1);
+            mbar_arrive_expect_tx(&full[s], CBX_PAGE_BYTES);
+            bulk_g2s(smem + s * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, CBX_PAGE_BYTES, &full[s]);
+          }
+          ++it;
+        }
+      }
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------- consumer warps
+  const int h = warp;
+  const int t16 = lane & 15, half = lane >> 4;        // QK mapping
+  const int tg = lane >> 3, c = lane & 7;             // PV mapping
+  const float qscale = 0.125f * kLog2e;               // 1/sqrt(64), scores kept in log2 domain
+
+  for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+    const int row = w / nsplit, split = w - row * nsplit;
+    const int len = kv_len[row];
+    const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+    const int p0 = split * pps, p1 = min(p0 + pps, n_pages);
+    if (p0 >= p1) {
+      if (nsplit == 1 && lane < 8)                    // row with no KV (finished pair): zeros
+        reinterpret_cast<uint4*>(out + (size_t)row * CBX_HIDDEN + h * 64)[lane] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    // q for (row, head): this lane's half (32 elements), pre-scaled
+    float q[32];
+    {
+      const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint4 v = qp[i];
+        q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
+        q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
+        q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
+        q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
+      }
+    }
+    float m = -INFINITY, l = 0.f, acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+
+    for (int pg = p0; pg < p1; ++pg, ++it) {
+      const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+      mbar_wait(&full[s], ph);
+      const uint8_t* kt = smem + s * CBX_PAGE_BYTES + h * 2048;
+      const uint8_t* vt = kt + 32768;
+      // ---- scores: lane = (token t16, half)
+      float sc = 0.f;
+      {
+        const uint4* kr = reinterpret_cast<const uint4*>(kt + t16 * 128);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 v = kr[(half * 4 + i) ^ (t16 & 7)];
+          sc = fmaf(q[i * 8 + 0], bf_lo(v.x), sc); sc = fmaf(q[i * 8 + 1], bf_hi(v.x), sc);
+          sc = fmaf(q[i * 8 + 2], bf_lo(v.y), sc); sc = fmaf(q[i * 8 + 3], bf_hi(v.y), sc);
+          sc = fmaf(q[i * 8 + 4], bf_lo(v.z), sc); sc = fmaf(q[i * 8 + 5], bf_hi(v.z), sc);
+          sc = fmaf(q[i * 8 + 6], bf_lo(v.w), sc); sc = fmaf(q[i * 8 + 7], bf_hi(v.w), sc);
+        }
+      }
+      sc += __shfl_xor_sync(0xffffffffu, sc, 16);
+      const int n_valid = len - pg * CBX_BLOCK_SIZE;   // tokens of this page inside the sequence
+      sc = (t16 < n_valid) ? sc : -INFINITY;
+      float mt = sc;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, o));
+      const float m_new = fmaxf(m, mt);
+      const float p = exp2f(sc - m_new);
+      const float corr = exp2f(m - m_new);
+      m = m_new;
+      l = fmaf(l, corr, p);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] *= corr;
+      // ---- PV: lane = (token group tg, chunk c)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int tok = tg * 4 + i;
+        const float pt = __shfl_sync(0xffffffffu, p, tok);
+        if (tok < n_valid) {
+          const uint4 v = reinterpret_cast<const uint4*>(vt + tok * 128)[c];
+          acc[0] = fmaf(pt, bf_lo(v.x), acc[0]); acc[1] = fmaf(pt, bf_hi(v.x), acc[1]);
+          acc[2] = fmaf(pt, bf_lo(v.y), acc[2]); acc[3] = fmaf(pt, bf_hi(v.y), acc[3]);
+          acc[4] = fmaf(pt, bf_lo(v.z), acc[4]); acc[5] = fmaf(pt, bf_hi(v.z), acc[5]);
+          acc[6] = fmaf(pt, bf_lo(v.w), acc[6]); acc[7] = fmaf(pt, bf_hi(v.w), acc[7]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+    }
+    // ---- item epilogue: reduce over token groups, publish
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+      acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+    }
+    const float lsum = warp_sum(l) * 0.5f;             // both halves hold identical p
+    if (nsplit == 1) {
+      if (lane < 8) {
+        const float inv = 1.f / lsum;
+        reinterpret_cast<uint4*>(out + (size_t)row * CBX_HIDDEN + h * 64)[lane] =
+            make_uint4(pack_bf16(acc[0] * inv, acc[1] * inv), pack_bf16(acc[2] * inv, acc[3] * inv),
+                       pack_bf16(acc[4] * inv, acc[5] * inv), pack_bf16(acc[6] * inv, acc[7] * inv));
+      }
+    } else {
+      const size_t pi = (size_t)row * nsplit + split;
+      if (lane < 8) {
+        float4* dst = reinterpret_cast<float4*>(o_part + pi * CBX_HIDDEN + h * 64 + lane * 8);
+        dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+      }
+      if (lane == 0) ml_part[pi * CBX_HEADS + h] = make_float2(m, lsum);
+    }
+  }
+}
+
+// Combine split partials: 256 threads per row, thread = 4 consecutive d of one head.
+__global__ void __launch_bounds__(256) attn_merge_kernel(const float* __restrict__ o_part,
+                                                         const float2* __restrict__ ml_part,
+                                                         const int32_t* __restrict__ kv_len,
+                                                         bf16* __restrict__ out, int pps, int nsplit) {
+  const int row = blockIdx.x, t = threadIdx.x, h = t >> 4;
+  const int n_pages = (kv_len[row] + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+  const int ns = min(nsplit, (n_pages + pps - 1) / pps);
+  float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (ns > 0) {
+    float mx = -INFINITY;
+    for (int s = 0; s < ns; ++s) mx = fmaxf(mx, ml_part[((size_t)row * nsplit + s) * CBX_HEADS + h].x);
+    float lt = 0.f;
+    for (int s = 0; s < ns; ++s) {
+      const size_t pi = (size_t)row * nsplit + s;
+      const float2 ml = ml_part[pi * CBX_HEADS + h];
+      const float wgt = exp2f(ml.x - mx);
+      const float4 a = reinterpret_cast<const float4*>(o_part + pi * CBX_HIDDEN)[t];
+      o.x = fmaf(wgt, a.x, o.x); o.y = fmaf(wgt, a.y, o.y); o.z = fmaf(wgt, a.z, o.z); o.w = fmaf(wgt, a.w, o.w);
+      lt = fmaf(wgt, ml.y, lt);
+    }
+    const float inv = 1.f / lt;
+    o.x *= inv; o.y *= inv; o.z *= inv; o.w *= inv;
+  }
+  reinterpret_cast<uint2*>(out + (size_t)row * CBX_HIDDEN)[t] = make_uint2(pack_bf16(o.x, o.y), pack_bf16(o.z, o.w));
+}
+}  // namespace
+
+namespace cbx {
+int init_attn() {
+  static bool done = false;
+  if (done) return 0;
+  cudaError_t e = cudaFuncSetAttribute(paged_attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kSmemBytes);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  done = true;
+  return 0;
+}
+}  // namespace cbx
+
+extern "C" int64_t cbx_attn_scratch_bytes(int T, int max_kv_len) {
+  if (T <= 0) return 0;
+  const AttnPlan p = make_plan(T, max_kv_len);
+  return (int64_t)T * p.nsplit * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256;
+}
+
+extern "C" int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* block_table,
+                                     int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
+                                     void* scratch, int T, int max_kv_len, void* stream) {
+  if (T <= 0) return 0;
+  if (cbx::init_attn()) return -1;
+  const AttnPlan p = make_plan(T, max_kv_len);
+  float* o_part = reinterpret_cast<float*>(scratch);
+  float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)T * p.nsplit * CBX_HIDDEN);
+  CBX_REQUIRE(p.nsplit == 1 || scratch != nullptr, "cbx_paged_attn_decode: scratch is NULL");
+  const int n_items = T * p.nsplit;
+  const int grid = n_items < 148 ? n_items : 148;
+  paged_attn_decode_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
+      (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out, o_part,
+      ml_part, T, p.pps, p.nsplit);
+  CBX_CHECK_LAUNCH("paged_attn_decode");
+  if (p.nsplit > 1) {
+    attn_merge_kernel<<<T, 256, 0, (cudaStream_t)stream>>>(o_part, ml_part, kv_len, (bf16*)out, p.pps, p.nsplit);
+    CBX_CHECK_LAUNCH("attn_merge");
+  }
+  return 0;
+}

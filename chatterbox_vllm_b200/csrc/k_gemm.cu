@@ -1,0 +1,244 @@
+// k_gemm.cu — bf16 GEMM on the 5th-gen tensor cores: y[M,N] = x[M,K] · W[N,K]^T.
+//
+// Replaces the cuBLASLt GEMMs behind vllm llama.py:117-120,221,225 and the two head GEMMs of
+// t3.py:729-730 once the cond+uncond batch makes them a dense contraction (M > 4 rows).
+//
+// One 128 x BN output tile per CTA, BK = 64 (one 128-byte swizzle atom per row):
+//   warp 0  TMA producer  : cp.async.bulk.tensor 2-D tiles of x and W (SWIZZLE_128B) into a
+//                           kStages-deep shared-memory ring, mbarrier complete_tx;
+//   warp 1  MMA issuer    : one elected thread issues tcgen05.mma.cta_group::1.kind::f16
+//                           (M=128, N=BN, K=16) x4 per stage, accumulator in TMEM;
+//                           tcgen05.commit frees the stage / signals the epilogue;
+//   warp 2  TMEM allocator;
+//   warps 4-7 epilogue    : tcgen05.ld 32x32b -> registers -> (SiLU·mul) -> bf16 -> global.
+#include <cuda.h>
+
+#include <map>
+#include <tuple>
+
+#include "common.cuh"
+
+using namespace cbx;
+namespace cbx { int init_gemm(); }
+
+namespace {
+constexpr int BM = 128, BK = 64;
+constexpr int kThreads = 256;
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = BN == 128 ? 6 : 8;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
+                                                              const __grid_constant__ CUtensorMap tma_b,
+                                                              bf16* __restrict__ y, int M, int N, int K, int ldy) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty = full + C::kStages;
+  uint64_t* tmem_full = empty + C::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+  const int n_kb = K / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < n_kb; ++kb) {
+        const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full[s], C::kStageBytes);
+        uint8_t* sa = smem + s * C::kStageBytes;
+        tma_load_2d(sa, &tma_a, kb * BK, m0, &full[s]);
+        tma_load_2d(sa + C::kABytes, &tma_b, kb * BK, n0, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      for (int kb = 0; kb < n_kb; ++kb) {
+        const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + s * C::kStageBytes);
+        const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + C::kABytes);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)           // +32 bytes per K=16 step inside the swizzle atom
+          umma_bf16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+  } else if (warp >= 4) {
+    const int ew = warp - 4;                           // == warp % 4: TMEM lane quarter
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int row = m0 + ew * 32 + lane;
+#pragma unroll 1
+    for (int cb = 0; cb < BN / 32; ++cb) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + cb * 32, r);
+      tmem_ld_wait();
+      const int col = n0 + cb * 32;
+      if (row < M) {
+        if (EPI == 1) {
+          // packed gate/up: columns [0,16) gate, [16,32) up of the same 16 features
+          uint32_t o[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float g0 = round_bf16(__uint_as_float(r[2 * i])), g1 = round_bf16(__uint_as_float(r[2 * i + 1]));
+            const float u0 = round_bf16(__uint_as_float(r[16 + 2 * i])), u1 = round_bf16(__uint_as_float(r[17 + 2 * i]));
+            o[i] = pack_bf16(g0 / (1.f + __expf(-g0)) * u0, g1 / (1.f + __expf(-g1)) * u1);
+          }
+          if (col + 32 <= N) {
+            uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + col / 2);
+            dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+            dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+          }
+        } else {
+          if (col + 32 <= N) {
+            uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              dst[i] = make_uint4(pack_bf16(__uint_as_float(r[8 * i]), __uint_as_float(r[8 * i + 1])),
+                                  pack_bf16(__uint_as_float(r[8 * i + 2]), __uint_as_float(r[8 * i + 3])),
+                                  pack_bf16(__uint_as_float(r[8 * i + 4]), __uint_as_float(r[8 * i + 5])),
+                                  pack_bf16(__uint_as_float(r[8 * i + 6]), __uint_as_float(r[8 * i + 7])));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (col + i < N) y[(size_t)row * ldy + col + i] = __float2bfloat16_rn(__uint_as_float(r[i]));
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN);
+  }
+}
+
+// ---- host side: tensor maps through the driver entry point (no -lcuda link) -------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D row-major bf16 [rows, cols] tensor, box = {64 cols, box_rows}, 128-byte swizzle.
+int make_map(CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) {
+  typedef std::tuple<const void*, int, int, int> Key;
+  static std::map<Key, CUtensorMap> cache;
+  Key key(ptr, rows, cols, box_rows);
+  auto itr = cache.find(key);
+  if (itr != cache.end()) { *m = itr->second; return 0; }
+  EncodeTiledFn enc = get_encode();
+  CBX_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CBX_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%d cols=%d", (int)r, rows, cols);
+  if (cache.size() > 4096) cache.clear();
+  cache[key] = *m;
+  return 0;
+}
+
+template <int BN, int EPI>
+int set_attr() {
+  cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
+  CBX_REQUIRE(e == cudaSuccess, "gemm smem attribute: %s", cudaGetErrorString(e));
+  return 0;
+}
+}  // namespace
+namespace cbx {
+int init_gemm() {
+  static bool done = false;
+  if (done) return 0;
+  if (set_attr<64, 0>() || set_attr<64, 1>() || set_attr<128, 0>() || set_attr<128, 1>()) return -1;
+  CBX_REQUIRE(get_encode() != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  done = true;
+  return 0;
+}
+}  // namespace cbx
+namespace {
+template <int BN, int EPI>
+int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s) {
+  using C = Cfg<BN>;
+  if (cbx::init_gemm()) return -1;
+  CUtensorMap ma, mb;
+  if (make_map(&ma, x, M, K, BM)) return -1;
+  if (make_map(&mb, W, N, K, BN)) return -1;
+  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
+  gemm_tc_kernel<BN, EPI><<<grid, kThreads, C::kSmem, s>>>(ma, mb, (bf16*)y, M, N, K, ldy);
+  CBX_CHECK_LAUNCH("gemm_tc");
+  return 0;
+}
+}  // namespace
+
+namespace cbx {
+int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int ldy, int epilogue,
+                 cudaStream_t s) {
+  CBX_REQUIRE(M >= 1 && K % BK == 0 && K >= BK, "gemm_tc: bad shape M=%d K=%d", M, K);
+  CBX_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0,
+              "gemm_tc: operands must be 16-byte aligned");
+  CBX_REQUIRE(epilogue == 0 || N % 32 == 0, "gemm_tc: SiLU epilogue needs N %% 32 == 0");
+  // Narrow tiles when the grid would leave most of the 148 SMs idle.
+  const int m_tiles = (M + BM - 1) / BM;
+  const bool narrow = (int64_t)m_tiles * ((N + 127) / 128) < 148;
+  if (epilogue == 1) return narrow ? launch<64, 1>(x, W, y, M, N, K, ldy, s) : launch<128, 1>(x, W, y, M, N, K, ldy, s);
+  return narrow ? launch<64, 0>(x, W, y, M, N, K, ldy, s) : launch<128, 0>(x, W, y, M, N, K, ldy, s);
+}
+int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
+}  // namespace cbx
+
+extern "C" int cbx_linear(const void* x, const void* W, void* y, int T, int N, int K, int ldy, int epilogue,
+                          int path, void* stream) {
+  CBX_REQUIRE(T >= 1, "cbx_linear: T < 1");
+  CBX_REQUIRE(path >= 0 && path <= 2, "cbx_linear: bad path %d", path);
+  const bool gemv_ok = T <= 4 && (K == 1024 || (K == 4096 && epilogue == 0));
+  if (path == 1) CBX_REQUIRE(gemv_ok, "cbx_linear: GEMV path needs T <= 4 and K in {1024,4096}");
+  if (path == 1 || (path == 0 && gemv_ok)) return cbx::gemv_bf16(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream);
+  return cbx::gemm_bf16_tc(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream);
+}

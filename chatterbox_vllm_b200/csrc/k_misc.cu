@@ -1,0 +1,273 @@
+// k_misc.cu — small HBM-bound kernels of the T3 step + host-side block pool.
+//   slot mapping, decode_prepare, prefill_embed, (add+)RMSNorm, RoPE + KV append,
+//   gate/up weight packing.
+#include <stdarg.h>
+
+#include <deque>
+
+#include "common.cuh"
+
+namespace cbx {
+static thread_local char g_err[512] = "";
+static int64_t g_launches = 0;
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int count_launch() { ++g_launches; return 0; }
+int64_t launches() { return g_launches; }
+}  // namespace cbx
+using namespace cbx;
+
+extern "C" const char* cbx_last_error(void) { return cbx::g_err; }
+extern "C" int cbx_abi_version(void) { return 1; }
+
+// ---------------------------------------------------------------- block pool (host) ---
+struct cbx_pool {
+  std::deque<int32_t> free_q;
+  int num_blocks;
+};
+extern "C" cbx_pool* cbx_pool_create(int num_blocks) {
+  if (num_blocks < 1) { set_error("cbx_pool_create: num_blocks < 1"); return nullptr; }
+  cbx_pool* p = new cbx_pool();
+  p->num_blocks = num_blocks;
+  for (int i = 1; i < num_blocks; ++i) p->free_q.push_back(i);   // block 0 popped: null block
+  return p;
+}
+extern "C" void cbx_pool_destroy(cbx_pool* p) { delete p; }
+extern "C" int cbx_pool_num_free(const cbx_pool* p) { return (int)p->free_q.size(); }
+extern "C" int cbx_pool_alloc(cbx_pool* p, int n, int32_t* out) {
+  CBX_REQUIRE(n >= 0 && n <= (int)p->free_q.size(), "Cannot get %d free blocks from the pool", n);
+  for (int i = 0; i < n; ++i) { out[i] = p->free_q.front(); p->free_q.pop_front(); }
+  return 0;
+}
+extern "C" int cbx_pool_free(cbx_pool* p, const int32_t* ids, int n) {
+  for (int i = 0; i < n; ++i) {
+    CBX_REQUIRE(ids[i] >= 0 && ids[i] < p->num_blocks, "cbx_pool_free: bad block id %d", ids[i]);
+    if (ids[i] != 0) p->free_q.push_back(ids[i]);
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------- slot mapping --------
+__global__ void slot_mapping_kernel(const int32_t* __restrict__ bt, int bt_stride,
+                                    const int32_t* __restrict__ req, const int32_t* __restrict__ pos,
+                                    int64_t* __restrict__ slot, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int p = pos[i];
+  int64_t s = -1;
+  if (p >= 0) {
+    int64_t blk = bt[(int64_t)req[i] * bt_stride + p / CBX_BLOCK_SIZE];
+    s = blk * CBX_BLOCK_SIZE + p % CBX_BLOCK_SIZE;
+  }
+  slot[i] = s;
+}
+extern "C" int cbx_slot_mapping(const int32_t* bt, int bt_stride, const int32_t* req, const int32_t* pos,
+                                int64_t* slot, int n, void* stream) {
+  if (n <= 0) return 0;
+  slot_mapping_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(bt, bt_stride, req, pos, slot, n);
+  CBX_CHECK_LAUNCH("slot_mapping");
+  return 0;
+}
+
+// ---------------------------------------------------------------- decode prepare ------
+// One CTA (128 threads) per row r in [0,2B): copies the 2 KB embedding row and thread 0
+// does the row's index arithmetic.
+__global__ void __launch_bounds__(128) decode_prepare_kernel(
+    const uint4* __restrict__ speech_emb, const int32_t* __restrict__ last_tok,
+    const int32_t* __restrict__ finished, const int32_t* __restrict__ seq_len,
+    const int32_t* __restrict__ bt, int bt_stride, uint4* __restrict__ x, int32_t* __restrict__ pos,
+    int64_t* __restrict__ slot, int32_t* __restrict__ kv_len, int32_t* __restrict__ row_seq,
+    int32_t* __restrict__ head_rows, int B) {
+  const int r = blockIdx.x, b = r % B;
+  const int tok = last_tok[b];
+  x[(size_t)r * 128 + threadIdx.x] = speech_emb[(size_t)tok * 128 + threadIdx.x];
+  if (threadIdx.x == 0) {
+    const int p = seq_len[r];
+    const bool live = finished[b] == 0;
+    pos[r] = p;
+    if (row_seq) row_seq[r] = r;
+    if (head_rows) head_rows[r] = r;
+    kv_len[r] = live ? p + 1 : 0;
+    slot[r] = live ? (int64_t)bt[(int64_t)r * bt_stride + p / CBX_BLOCK_SIZE] * CBX_BLOCK_SIZE + p % CBX_BLOCK_SIZE
+                   : (int64_t)-1;
+  }
+}
+
+namespace cbx {
+int launch_decode_prepare(const void* speech_emb, const int32_t* last_tok, const int32_t* finished,
+                          const int32_t* seq_len, const int32_t* bt, int bt_stride, void* x, int32_t* pos,
+                          int64_t* slot, int32_t* kv_len, int32_t* row_seq, int32_t* head_rows, int B,
+                          cudaStream_t s) {
+  decode_prepare_kernel<<<2 * B, 128, 0, s>>>((const uint4*)speech_emb, last_tok, finished, seq_len, bt,
+                                               bt_stride, (uint4*)x, pos, slot, kv_len, row_seq, head_rows, B);
+  CBX_CHECK_LAUNCH("decode_prepare");
+  return 0;
+}
+}  // namespace cbx
+
+extern "C" int cbx_decode_prepare(const void* speech_emb, const int32_t* last_tok, const int32_t* finished,
+                                  const int32_t* seq_len, const int32_t* bt, int bt_stride, void* x,
+                                  int32_t* pos, int64_t* slot, int32_t* kv_len, int B, void* stream) {
+  CBX_REQUIRE(B > 0, "cbx_decode_prepare: B <= 0");
+  // row_seq / head_rows are engine-internal identity maps; the standalone op skips them.
+  return launch_decode_prepare(speech_emb, last_tok, finished, seq_len, bt, bt_stride, x, pos, slot, kv_len,
+                               nullptr, nullptr, B, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------- prefill embed -------
+__global__ void __launch_bounds__(128) prefill_embed_kernel(
+    const int4* __restrict__ desc, const float* __restrict__ cond_emb, const uint4* __restrict__ text_emb,
+    const uint4* __restrict__ text_pos, const uint4* __restrict__ speech_emb,
+    const uint4* __restrict__ speech_pos, uint4* __restrict__ x) {
+  const int r = blockIdx.x, t = threadIdx.x;
+  const int4 d = desc[r];
+  uint4 o = make_uint4(0, 0, 0, 0);
+  if (d.x == 0) {
+    const float4* src = reinterpret_cast<const float4*>(cond_emb + ((size_t)d.y * 34 + d.z) * CBX_HIDDEN) + t * 2;
+    float4 a = src[0], b = src[1];
+    o = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
+  } else if (d.x == 1 || d.x == 3) {
+    uint4 a = (d.x == 1 ? text_emb : speech_emb)[(size_t)d.y * 128 + t];
+    uint4 b = (d.x == 1 ? text_pos : speech_pos)[(size_t)d.z * 128 + t];
+    o.x = pack_bf16(bf_lo(a.x) + bf_lo(b.x), bf_hi(a.x) + bf_hi(b.x));
+    o.y = pack_bf16(bf_lo(a.y) + bf_lo(b.y), bf_hi(a.y) + bf_hi(b.y));
+    o.z = pack_bf16(bf_lo(a.z) + bf_lo(b.z), bf_hi(a.z) + bf_hi(b.z));
+    o.w = pack_bf16(bf_lo(a.w) + bf_lo(b.w), bf_hi(a.w) + bf_hi(b.w));
+  }
+  x[(size_t)r * 128 + t] = o;
+}
+extern "C" int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, const void* text_emb,
+                                 const void* text_pos, const void* speech_emb, const void* speech_pos,
+                                 void* x, int T, void* stream) {
+  if (T <= 0) return 0;
+  prefill_embed_kernel<<<T, 128, 0, (cudaStream_t)stream>>>(
+      (const int4*)desc, cond_emb, (const uint4*)text_emb, (const uint4*)text_pos, (const uint4*)speech_emb,
+      (const uint4*)speech_pos, (uint4*)x);
+  CBX_CHECK_LAUNCH("prefill_embed");
+  return 0;
+}
+
+// ---------------------------------------------------------------- (add +) RMSNorm -----
+// One CTA of 128 threads per row; each thread owns 8 contiguous elements (one 16-byte
+// load).  Rounding points follow vLLM: z = bf16(x + res); out = bf16(bf16(z·rstd)·w).
+template <bool kAdd>
+__global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* __restrict__ x, uint4* __restrict__ res,
+                                                      const uint4* __restrict__ w, uint4* __restrict__ out,
+                                                      float eps) {
+  const int r = blockIdx.x, t = threadIdx.x;
+  uint4 v = x[(size_t)r * 128 + t];
+  float f[8] = {bf_lo(v.x), bf_hi(v.x), bf_lo(v.y), bf_hi(v.y), bf_lo(v.z), bf_hi(v.z), bf_lo(v.w), bf_hi(v.w)};
+  if (kAdd) {
+    uint4 q = res[(size_t)r * 128 + t];
+    float g[8] = {bf_lo(q.x), bf_hi(q.x), bf_lo(q.y), bf_hi(q.y), bf_lo(q.z), bf_hi(q.z), bf_lo(q.w), bf_hi(q.w)};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = round_bf16(f[i] + g[i]);
+    res[(size_t)r * 128 + t] =
+        make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
+  ss = warp_sum(ss);
+  __shared__ float part[4];
+  if ((t & 31) == 0) part[t >> 5] = ss;
+  __syncthreads();
+  const float rstd = rsqrtf((part[0] + part[1] + part[2] + part[3]) * (1.0f / CBX_HIDDEN) + eps);
+  uint4 wv = w[t];
+  float wf[8] = {bf_lo(wv.x), bf_hi(wv.x), bf_lo(wv.y), bf_hi(wv.y), bf_lo(wv.z), bf_hi(wv.z), bf_lo(wv.w), bf_hi(wv.w)};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) f[i] = round_bf16(f[i] * rstd) * wf[i];
+  out[(size_t)r * 128 + t] =
+      make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+extern "C" int cbx_rmsnorm(const void* x, void* residual, const void* w, void* out, int T, float eps,
+                           void* stream) {
+  if (T <= 0) return 0;
+  if (residual)
+    rmsnorm_kernel<true><<<T, 128, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)residual,
+                                                               (const uint4*)w, (uint4*)out, eps);
+  else
+    rmsnorm_kernel<false><<<T, 128, 0, (cudaStream_t)stream>>>((const uint4*)x, nullptr, (const uint4*)w,
+                                                                (uint4*)out, eps);
+  CBX_CHECK_LAUNCH("rmsnorm");
+  return 0;
+}
+
+// ---------------------------------------------------------------- RoPE + KV append ----
+// One CTA of 128 threads per token row.  Threads 0..63 rotate q, 64..127 rotate k: each
+// owns the 8-element chunk c (0..3) of a head's first half and its partner chunk c+4.
+// Then every thread moves one 16-byte chunk of v.  K chunks land XOR-swizzled (chunk ^
+// (tok & 7)) so the attention kernel's per-token 128-bit reads are bank-conflict-free.
+__global__ void __launch_bounds__(128) rope_kv_append_kernel(uint4* __restrict__ qkv,
+                                                             const int32_t* __restrict__ pos,
+                                                             const int64_t* __restrict__ slot,
+                                                             const uint4* __restrict__ cos_sin,
+                                                             uint8_t* __restrict__ kv_layer) {
+  const int r = blockIdx.x, t = threadIdx.x;
+  uint4* row = qkv + (size_t)r * 384;                 // 3072 bf16 = 384 x 16 B
+  const int which = t >> 6, item = t & 63, h = item >> 2, c = item & 3;
+  const int p = pos[r];
+  const int64_t s = slot[r];
+  const uint4 cv = cos_sin[(size_t)p * 8 + c], sv = cos_sin[(size_t)p * 8 + 4 + c];
+  uint4* src = row + which * 128 + h * 8;
+  const uint4 a = src[c], b = src[c + 4];
+  const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+  const uint32_t cw[4] = {cv.x, cv.y, cv.z, cv.w}, sw[4] = {sv.x, sv.y, sv.z, sv.w};
+  uint32_t o1[4], o2[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float x1l = bf_lo(aw[i]), x1h = bf_hi(aw[i]), x2l = bf_lo(bw[i]), x2h = bf_hi(bw[i]);
+    float cl = bf_lo(cw[i]), ch = bf_hi(cw[i]), sl = bf_lo(sw[i]), sh = bf_hi(sw[i]);
+    o1[i] = pack_bf16(x1l * cl - x2l * sl, x1h * ch - x2h * sh);
+    o2[i] = pack_bf16(x2l * cl + x1l * sl, x2h * ch + x1h * sh);
+  }
+  const uint4 r1 = make_uint4(o1[0], o1[1], o1[2], o1[3]), r2 = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+  uint8_t* page = nullptr;
+  int tok = 0;
+  if (s >= 0) {
+    page = kv_layer + (size_t)(s / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
+    tok = (int)(s % CBX_BLOCK_SIZE);
+  }
+  if (which == 0) {
+    src[c] = r1;
+    src[c + 4] = r2;
+  } else if (page) {
+    uint4* kt = reinterpret_cast<uint4*>(page + h * 2048 + tok * 128);
+    kt[c ^ (tok & 7)] = r1;
+    kt[(c + 4) ^ (tok & 7)] = r2;
+  }
+  if (page) {
+    const int vh = t >> 3, vc = t & 7;
+    reinterpret_cast<uint4*>(page + 32768 + vh * 2048 + tok * 128)[vc] = row[256 + t];
+  }
+}
+extern "C" int cbx_rope_kv_append(void* qkv, const int32_t* pos, const int64_t* slot, const void* cos_sin,
+                                  void* kv_layer, int T, void* stream) {
+  if (T <= 0) return 0;
+  rope_kv_append_kernel<<<T, 128, 0, (cudaStream_t)stream>>>((uint4*)qkv, pos, slot, (const uint4*)cos_sin,
+                                                              (uint8_t*)kv_layer);
+  CBX_CHECK_LAUNCH("rope_kv_append");
+  return 0;
+}
+
+// ---------------------------------------------------------------- gate/up packing -----
+__global__ void pack_gate_up_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, int I, int K8) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)2 * I * K8) return;
+  const int row = (int)(i / K8), col = (int)(i % K8);
+  const int which = row / I, j = row % I;               // which: 0 gate, 1 up
+  const int drow = (j / 16) * 32 + which * 16 + (j % 16);
+  dst[(int64_t)drow * K8 + col] = src[i];
+}
+extern "C" int cbx_pack_gate_up(const void* src, void* dst, int I, int K, void* stream) {
+  CBX_REQUIRE(I % 16 == 0 && K % 8 == 0, "cbx_pack_gate_up: I %% 16 or K %% 8 != 0");
+  const int64_t n = (int64_t)2 * I * (K / 8);
+  pack_gate_up_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const uint4*)src,
+                                                                                       (uint4*)dst, I, K / 8);
+  CBX_CHECK_LAUNCH("pack_gate_up");
+  return 0;
+}

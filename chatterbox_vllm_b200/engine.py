@@ -1,0 +1,297 @@
+"""T3Engine — host side of the B200 T3 speech-token path.
+
+Replaces, for this path only, what the reference obtains from ``vllm.LLM(...)`` +
+``T3VllmModel`` (tts.py:130-140,408-418; models/t3/t3.py:302-781): weight loading with q/k/v
+and gate/up stacking (t3.py:347-379), prompt layout (t3.py:229-262,548-569), paged-KV
+bookkeeping (vLLM block pool / block table), the paired cond/uncond forward and the sampler.
+All arithmetic runs in libcbx_t3.so; this file only moves pointers and small index arrays."""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import ops
+from ._lib import (BLOCK_SIZE, EngineCfg, HIDDEN, PAGE_BYTES, SPEECH_VOCAB, Weights, check, load)
+
+BF16 = torch.bfloat16
+COND_LEN = 34                 # CONDITIONING_SIZE, t3.py:42
+START_SPEECH, STOP_SPEECH = 6561, 6562
+SPEECH_TOKEN_OFFSET = 1000    # t3.py:49
+
+
+def llama3_cos_sin(max_pos: int, head_dim: int = 64, theta: float = 500000.0, factor: float = 8.0,
+                   low: float = 1.0, high: float = 4.0, orig_max: int = 8192) -> torch.Tensor:
+    """bf16 [max_pos, 64] = cos(32) ‖ sin(32); llama3 rescale as t3-model/config.json:19-26
+    (vllm rotary_embedding/llama3_rope.py:33-54, base.py:90-100)."""
+    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float) / head_dim))
+    wl = 2 * math.pi / inv
+    smooth = (orig_max / wl - low) / (high - low)
+    inv = torch.where(wl < orig_max / high, inv,
+                      torch.where(wl > orig_max / low, inv / factor, (1 - smooth) * inv / factor + smooth * inv))
+    fr = torch.einsum("i,j->ij", torch.arange(max_pos, dtype=torch.float), inv)
+    return torch.cat((fr.cos(), fr.sin()), dim=-1).to(BF16)
+
+
+@dataclass
+class SamplingParams:
+    """The vLLM SamplingParams fields the reference actually uses (tts.py:408-418)."""
+    temperature: float = 0.8
+    top_p: float = 1.0
+    min_p: float = 0.0
+    top_k: int = 0
+    repetition_penalty: float = 1.0
+    max_tokens: int = 1000
+    seed: int | None = None
+    ignore_eos: bool = False
+    stop_token_ids: list = field(default_factory=lambda: [STOP_SPEECH + SPEECH_TOKEN_OFFSET])
+
+
+@dataclass
+class Request:
+    text_ids: list            # tokenizer output for "[START]…[STOP]" (n_text ids)
+    cond_emb: torch.Tensor    # [34, 1024] fp32 (CPU or CUDA)
+    params: SamplingParams
+    uid: int = 0
+    penalize_prompt_ids: bool = False   # MTL quirk: prompt ids ≥1000 hit speech id−1000
+
+
+class T3Engine:
+    def __init__(self, state_dict: dict, *, device="cuda:0", max_pairs: int = 128, max_model_len: int = 1000,
+                 num_blocks: int | None = None, max_rows: int | None = None, cfg_scale: float | None = None,
+                 rms_eps: float = 1e-5, base_seed: int = 0, use_graph: bool = True,
+                 stop_token: int = STOP_SPEECH):
+        load()                                           # fail loudly if the CUDA library is missing
+        if not torch.cuda.is_available():
+            raise RuntimeError("T3Engine needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        self.max_pairs, self.max_model_len = max_pairs, max_model_len
+        # CHATTERBOX_CFG_SCALE is read once at model construction (t3.py:343)
+        self.cfg_scale = float(os.environ.get("CHATTERBOX_CFG_SCALE", "0.5")) if cfg_scale is None else cfg_scale
+        self.use_graph, self.base_seed, self._next_uid = use_graph, base_seed, 0
+        self._load_weights(state_dict, rms_eps)
+        self.bt_stride = -(-max_model_len // BLOCK_SIZE)
+        if num_blocks is None:
+            num_blocks = 2 * max_pairs * self.bt_stride + 1
+        self.num_blocks = num_blocks
+        self.max_rows = max_rows or max(2 * max_pairs, 8192)
+        self.kv_cache = torch.zeros(self.n_layers * num_blocks * PAGE_BYTES, dtype=torch.uint8, device=self.device)
+        self.block_table = torch.zeros(2 * max_pairs, self.bt_stride, dtype=torch.int32, device=self.device)
+        self.pool = ops.BlockPool(num_blocks)
+        self.sb = ops.SamplerBuffers(max_pairs, max_model_len, self.device, stop_token=stop_token,
+                                     cfg_scale=self.cfg_scale)
+        self._cfg = EngineCfg(max_pairs, self.max_rows, max_model_len, num_blocks, max_model_len)
+        nbytes = load().cbx_engine_workspace_bytes(C.byref(self._cfg))
+        self.workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
+        ws = (self.workspace.data_ptr() + 1023) // 1024 * 1024
+        self._st = self.sb.struct()
+        self._h = load().cbx_engine_create(C.byref(self._cfg), C.byref(self._w), self.kv_cache.data_ptr(),
+                                           self.block_table.data_ptr(), ws, C.byref(self._st))
+        if not self._h:
+            raise RuntimeError("cbx_engine_create: " + load().cbx_last_error().decode())
+        self.gpu_launches = 0
+
+    # ------------------------------------------------------------------ weights
+    def _load_weights(self, sd: dict, rms_eps: float) -> None:
+        """Checkpoint key layout of t3_cfg.safetensors; q/k/v and gate/up are
+        stacked as vLLM's loader does (vllm llama.py:433-441); gate/up then packed for the
+        fused SiLU·mul epilogue."""
+        dev = self.device
+        g = lambda k: sd[k].to(device=dev, dtype=BF16).contiguous()  # noqa: E731
+        L = 0
+        while f"tfmr.layers.{L}.self_attn.q_proj.weight" in sd:
+            L += 1
+        if L == 0:
+            raise KeyError("state_dict has no tfmr.layers.* keys")
+        self.n_layers = L
+        self.wqkv, self.wo, self.wgu, self.wd, self.ln1, self.ln2 = [], [], [], [], [], []
+        for i in range(L):
+            p = f"tfmr.layers.{i}."
+            self.wqkv.append(torch.cat([g(p + f"self_attn.{n}_proj.weight") for n in "qkv"], 0).contiguous())
+            self.wo.append(g(p + "self_attn.o_proj.weight"))
+            gu = torch.cat([g(p + "mlp.gate_proj.weight"), g(p + "mlp.up_proj.weight")], 0).contiguous()
+            self.wgu.append(ops.pack_gate_up(gu))
+            self.wd.append(g(p + "mlp.down_proj.weight"))
+            self.ln1.append(g(p + "input_layernorm.weight"))
+            self.ln2.append(g(p + "post_attention_layernorm.weight"))
+        self.norm = g("tfmr.norm.weight")
+        self.speech_emb, self.speech_head = g("speech_emb.weight"), g("speech_head.weight")
+        self.text_emb, self.text_pos = g("text_emb.weight"), g("text_pos_emb.emb.weight")
+        self.speech_pos = g("speech_pos_emb.emb.weight")
+        assert self.speech_emb.shape == (SPEECH_VOCAB, HIDDEN)
+        self.cos_sin = llama3_cos_sin(max(self.max_model_len + 8, 2048)).to(dev)
+        arr = lambda ts: (C.c_void_p * L)(*[t.data_ptr() for t in ts])  # noqa: E731
+        self._arrs = [arr(t) for t in (self.wqkv, self.wo, self.wgu, self.wd, self.ln1, self.ln2)]
+        self._w = Weights(L, *self._arrs, self.norm.data_ptr(), self.speech_emb.data_ptr(),
+                          self.speech_head.data_ptr(), self.cos_sin.data_ptr(), rms_eps)
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ helpers
+    def buffer(self, name: str, shape, dtype) -> torch.Tensor:
+        """Zero-copy torch view of an engine-internal device buffer."""
+        ptr = load().cbx_engine_buffer(self._h, name.encode())
+        if not ptr:
+            raise KeyError(name)
+        n = int(np.prod(shape))
+        esz = torch.empty(0, dtype=dtype).element_size()
+        off = ptr - self.workspace.data_ptr()
+        return self.workspace[off:off + n * esz].view(dtype).view(*shape)
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream().cuda_stream
+
+    def forward(self, T: int, max_kv_len: int) -> None:
+        check(load().cbx_engine_forward(self._h, T, max_kv_len, self._stream()), "engine_forward")
+
+    def sample(self, B: int) -> None:
+        check(load().cbx_engine_sample(self._h, B, self._stream()), "engine_sample")
+
+    def decode(self, B: int, n_steps: int, max_kv_len: int) -> None:
+        check(load().cbx_engine_decode(self._h, B, n_steps, max_kv_len, int(self.use_graph), self._stream()),
+              "engine_decode")
+        self.gpu_launches += load().cbx_engine_last_launch_count(self._h)
+
+    # ------------------------------------------------------------------ admission + prefill
+    def _admit(self, reqs: list[Request]) -> tuple[list[int], list[list[int]]]:
+        """Reserve KV blocks for prompt + max_tokens of both members of every pair (rows b and
+        B+b of the block table) and upload the table.  Returns prefix lengths and block lists."""
+        B = len(reqs)
+        bt = np.zeros((2 * B, self.bt_stride), np.int32)
+        P, held = [], []
+        for b, r in enumerate(reqs):
+            p = COND_LEN + len(r.text_ids) + 1
+            total = p + r.params.max_tokens
+            if total > self.max_model_len:
+                raise ValueError(f"prompt ({p}) + max_tokens ({r.params.max_tokens}) exceeds max_model_len")
+            P.append(p)
+        for half in range(2):
+            for b, r in enumerate(reqs):
+                blks = self.pool.alloc(-(-(P[b] + r.params.max_tokens) // BLOCK_SIZE))
+                bt[half * B + b, :len(blks)] = blks
+                held.append(blks)
+        self.block_table[:2 * B].copy_(torch.from_numpy(bt), non_blocking=False)
+        return P, held
+
+    def _release(self, held: list[list[int]]) -> None:
+        for blks in held:                                  # vLLM frees a request's blocks in reverse order
+            self.pool.free(list(reversed(blks)))
+
+    def _init_sampler_state(self, reqs: list[Request], P: list[int]) -> None:
+        B, sb, dev = len(reqs), self.sb, self.device
+        up = lambda vals, dt: torch.tensor(vals, dtype=dt).to(dev)  # noqa: E731
+        pr = [r.params for r in reqs]
+        sb.temperature[:B] = up([p.temperature for p in pr], torch.float32)
+        sb.top_p[:B] = up([p.top_p for p in pr], torch.float32)
+        sb.min_p[:B] = up([p.min_p for p in pr], torch.float32)
+        sb.rep_pen[:B] = up([p.repetition_penalty for p in pr], torch.float32)
+        sb.top_k[:B] = up([p.top_k for p in pr], torch.int32)
+        sb.ignore_eos[:B] = up([int(p.ignore_eos) for p in pr], torch.int32)
+        sb.max_out[:B] = up([p.max_tokens for p in pr], torch.int32)
+        seeds = [(p.seed if p.seed is not None else self.base_seed) & (2**63 - 1) for p in pr]
+        sb.seed[:B] = up(seeds, torch.int64)
+        sb.uid[:B] = up([r.uid for r in reqs], torch.int64)
+        sb.n_out[:B] = 0
+        sb.finished[:B] = 0
+        sb.n_finished.zero_()
+        # cache holds P tokens after prefill; the prefill-time sample call adds 1, so start at P-1
+        sb.seq_len[:2 * B] = up([p - 1 for p in P] * 2, torch.int32)
+        seen = np.zeros((B, ops.SEEN_WORDS), np.uint32)
+        for b, r in enumerate(reqs):
+            if r.penalize_prompt_ids:
+                for t in r.text_ids:
+                    if t >= SPEECH_TOKEN_OFFSET and t - SPEECH_TOKEN_OFFSET < SPEECH_VOCAB:
+                        s = t - SPEECH_TOKEN_OFFSET
+                        seen[b, s >> 5] |= np.uint32(1 << (s & 31))
+        sb.seen[:B] = torch.from_numpy(seen.view(np.int32)).to(dev)
+
+    def prefill(self, reqs: list[Request], P: list[int]) -> None:
+        """One-pass prefill of every pair's whole prefix (cond rows then uncond rows per pair),
+        chunked by max_rows; then the first speech token of every pair is sampled."""
+        B, dev = len(reqs), self.device
+        cond = torch.stack([r.cond_emb.to(torch.float32) for r in reqs]).to(dev).contiguous()
+        h_last = torch.empty(2 * B, HIDDEN, dtype=BF16, device=dev)
+        x = self.buffer("x", (self.max_rows, HIDDEN), BF16)
+        h = self.buffer("h", (self.max_rows, HIDDEN), BF16)
+        b0 = 0
+        while b0 < B:
+            b1, rows = b0, 0
+            while b1 < B and rows + 2 * P[b1] <= self.max_rows:
+                rows += 2 * P[b1]
+                b1 += 1
+            if b1 == b0:
+                raise ValueError("max_rows too small for one pair's prefix")
+            desc, pos, rseq, last = [], [], [], {}
+            for b in range(b0, b1):
+                ids, n = reqs[b].text_ids, len(reqs[b].text_ids)
+                for half in range(2):
+                    for i in range(COND_LEN):
+                        desc.append((0, b, i, 0))
+                    for i in range(n):
+                        desc.append((1, ids[i], i, 0) if half == 0 else (2, 0, 0, 0))
+                    desc.append((3, START_SPEECH, 0, 0))
+                    pos.extend(range(P[b]))
+                    rseq.extend([half * B + b] * P[b])
+                    last[half * B + b] = len(pos) - 1
+            T = len(pos)
+            d_desc = torch.tensor(desc, dtype=torch.int32).to(dev)
+            d_pos = torch.tensor(pos, dtype=torch.int32).to(dev)
+            d_rseq = torch.tensor(rseq, dtype=torch.int32).to(dev)
+            self.buffer("pos", (T,), torch.int32).copy_(d_pos)
+            self.buffer("row_seq", (T,), torch.int32).copy_(d_rseq)
+            self.buffer("kv_len", (T,), torch.int32).copy_(d_pos + 1)
+            self.buffer("slot", (T,), torch.int64).copy_(ops.slot_mapping(self.block_table, d_rseq, d_pos))
+            ops.prefill_embed(d_desc, cond, self.text_emb, self.text_pos, self.speech_emb, self.speech_pos, out=x[:T])
+            self.forward(T, max(P[b0:b1]))
+            seqs = sorted(last)
+            h_last[torch.tensor(seqs, device=dev)] = h[torch.tensor([last[s] for s in seqs], device=dev)]
+            b0 = b1
+        h[:2 * B].copy_(h_last)
+        self.buffer("head_rows", (2 * B,), torch.int32).copy_(torch.arange(2 * B, dtype=torch.int32, device=dev))
+        self.sample(B)
+
+    # ------------------------------------------------------------------ public entry
+    def generate(self, reqs: list[Request], poll_every: int = 32) -> list[list[int]]:
+        """Runs requests in static waves of ≤ max_pairs; returns speech-token ids per request in
+        vLLM id space (speech id + 1000), stop token included, like vLLM's output.token_ids."""
+        out: list[list[int]] = []
+        for w0 in range(0, len(reqs), self.max_pairs):
+            wave = reqs[w0:w0 + self.max_pairs]
+            for r in wave:
+                if r.uid == 0:
+                    self._next_uid += 1
+                    r.uid = self._next_uid
+            B = len(wave)
+            P, held = self._admit(wave)
+            try:
+                self._init_sampler_state(wave, P)
+                self.prefill(wave, P)
+                steps, max_steps, max_p = 1, max(r.params.max_tokens for r in wave), max(P)
+                while steps < max_steps:
+                    n = min(poll_every, max_steps - steps)
+                    self.decode(B, n, max_p + steps + n)
+                    steps += n
+                    if int(self.sb.n_finished.item()) >= B:      # the only host sync: every poll_every steps
+                        break
+                n_out = self.sb.n_out[:B].cpu().tolist()
+                toks = self.sb.out_tokens[:B].cpu().numpy()
+                out.extend([(toks[b, :n_out[b]] + SPEECH_TOKEN_OFFSET).tolist() for b in range(B)])
+            finally:
+                self._release(held)
+        return out
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize()
+            load().cbx_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,171 @@
+"""Per-kernel ops over torch CUDA tensors → libcbx_t3.so (C-ABI, include/cbx_t3.h).
+
+torch is plumbing only (device memory + the current stream); all arithmetic happens in the
+hand-written sm_100a kernels.  Every op validates device/dtype/contiguity and raises — there is
+no eager/CPU fallback."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import (BLOCK_SIZE, HIDDEN, INTER, LOGITS_LD, PAGE_BYTES, SEEN_WORDS, SPEECH_VOCAB,
+                   SamplerState, check, load)
+
+BF16 = torch.bfloat16
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: torch.Tensor | None, dtype=None) -> int | None:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("libcbx_t3 ops need CUDA tensors (no CPU fallback)")
+    if not t.is_contiguous():
+        raise RuntimeError("libcbx_t3 ops need contiguous tensors")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"expected dtype {dtype}, got {t.dtype}")
+    return t.data_ptr()
+
+
+def slot_mapping(block_table: torch.Tensor, req: torch.Tensor, pos: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(req.numel(), dtype=torch.int64, device=req.device)
+    check(load().cbx_slot_mapping(_p(block_table, torch.int32), block_table.stride(0), _p(req, torch.int32),
+                                  _p(pos, torch.int32), _p(out), req.numel(), _stream()), "slot_mapping")
+    return out
+
+
+def rmsnorm(x: torch.Tensor, w: torch.Tensor, residual: torch.Tensor | None = None, eps: float = 1e-5):
+    """out = norm(x)·w, or (residual += x in place; out = norm(residual)·w)."""
+    assert x.shape[-1] == HIDDEN
+    out = torch.empty_like(x)
+    check(load().cbx_rmsnorm(_p(x, BF16), _p(residual, BF16), _p(w, BF16), _p(out), x.shape[0], eps, _stream()),
+          "rmsnorm")
+    return out
+
+
+def pack_gate_up(wgu: torch.Tensor) -> torch.Tensor:
+    out = torch.empty_like(wgu)
+    check(load().cbx_pack_gate_up(_p(wgu, BF16), _p(out), wgu.shape[0] // 2, wgu.shape[1], _stream()), "pack_gate_up")
+    return out
+
+
+def linear(x: torch.Tensor, W: torch.Tensor, epilogue: int = 0, path: int = 0, out: torch.Tensor | None = None):
+    """y = x·Wᵀ ; epilogue=1: SiLU(gate)·up with W packed by pack_gate_up (y is [T, N/2])."""
+    T, K = x.shape
+    N = W.shape[0]
+    assert W.shape[1] == K
+    if out is None:
+        out = torch.empty(T, N // 2 if epilogue else N, dtype=BF16, device=x.device)
+    check(load().cbx_linear(_p(x, BF16), _p(W, BF16), _p(out, BF16), T, N, K, out.stride(0), epilogue, path,
+                            _stream()), "linear")
+    return out
+
+
+def rope_kv_append(qkv, pos, slot, cos_sin, kv_layer):
+    check(load().cbx_rope_kv_append(_p(qkv, BF16), _p(pos, torch.int32), _p(slot, torch.int64), _p(cos_sin, BF16),
+                                    _p(kv_layer), qkv.shape[0], _stream()), "rope_kv_append")
+
+
+def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: int):
+    T = qkv.shape[0]
+    out = torch.empty(T, HIDDEN, dtype=BF16, device=qkv.device)
+    nbytes = load().cbx_attn_scratch_bytes(T, max_kv_len)
+    scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=qkv.device)
+    check(load().cbx_paged_attn_decode(_p(qkv, BF16), _p(kv_layer), _p(block_table, torch.int32),
+                                       block_table.stride(0), _p(row_seq, torch.int32), _p(kv_len, torch.int32),
+                                       _p(out), _p(scratch), T, max_kv_len, _stream()), "paged_attn_decode")
+    return out
+
+
+class SamplerBuffers:
+    """Device-resident per-pair sampler state (cbx_sampler_state)."""
+
+    def __init__(self, B: int, out_stride: int, device, *, stop_token: int = 6562, cfg_scale: float = 0.5):
+        z = lambda *s, dt=torch.int32: torch.zeros(*s, dtype=dt, device=device)  # noqa: E731
+        self.B, self.out_stride = B, out_stride
+        self.last_tok, self.out_tokens, self.n_out = z(B), z(B, out_stride), z(B)
+        self.max_out, self.finished, self.seq_len = z(B), z(B), z(2 * B)
+        self.seen = z(B, SEEN_WORDS)
+        self.temperature, self.top_p = z(B, dt=torch.float32), torch.ones(B, dtype=torch.float32, device=device)
+        self.min_p, self.rep_pen = z(B, dt=torch.float32), torch.ones(B, dtype=torch.float32, device=device)
+        self.top_k, self.ignore_eos = z(B), z(B)
+        self.seed, self.uid = z(B, dt=torch.int64), z(B, dt=torch.int64)
+        self.n_finished = z(1)
+        self.stop_token, self.cfg_scale = stop_token, cfg_scale
+
+    def struct(self) -> SamplerState:
+        s = SamplerState()
+        for name in ("last_tok", "out_tokens", "n_out", "max_out", "finished", "seq_len", "seen", "temperature",
+                     "top_p", "min_p", "rep_pen", "top_k", "ignore_eos", "seed", "uid", "n_finished"):
+            setattr(s, name, getattr(self, name).data_ptr())
+        s.out_stride, s.stop_token, s.cfg_scale = self.out_stride, self.stop_token, self.cfg_scale
+        return s
+
+
+def cfg_sample(logits: torch.Tensor, sb: SamplerBuffers, B: int) -> None:
+    assert logits.shape[1] == LOGITS_LD and logits.shape[0] >= 2 * B
+    st = sb.struct()
+    check(load().cbx_cfg_sample(_p(logits, BF16), C.byref(st), B, _stream()), "cfg_sample")
+
+
+def decode_prepare(speech_emb, sb: SamplerBuffers, block_table, B: int):
+    dev = speech_emb.device
+    x = torch.empty(2 * B, HIDDEN, dtype=BF16, device=dev)
+    pos = torch.empty(2 * B, dtype=torch.int32, device=dev)
+    slot = torch.empty(2 * B, dtype=torch.int64, device=dev)
+    kv_len = torch.empty(2 * B, dtype=torch.int32, device=dev)
+    check(load().cbx_decode_prepare(_p(speech_emb, BF16), _p(sb.last_tok), _p(sb.finished), _p(sb.seq_len),
+                                    _p(block_table, torch.int32), block_table.stride(0), _p(x), _p(pos), _p(slot),
+                                    _p(kv_len), B, _stream()), "decode_prepare")
+    return x, pos, slot, kv_len
+
+
+def prefill_embed(desc, cond_emb, text_emb, text_pos, speech_emb, speech_pos, out=None):
+    T = desc.shape[0]
+    if out is None:
+        out = torch.empty(T, HIDDEN, dtype=BF16, device=desc.device)
+    check(load().cbx_prefill_embed(_p(desc, torch.int32), _p(cond_emb, torch.float32), _p(text_emb, BF16),
+                                   _p(text_pos, BF16), _p(speech_emb, BF16), _p(speech_pos, BF16), _p(out), T,
+                                   _stream()), "prefill_embed")
+    return out
+
+
+class BlockPool:
+    """Host block pool (C++ in libcbx_t3.so) with vLLM's allocation policy."""
+
+    def __init__(self, num_blocks: int):
+        self._h = load().cbx_pool_create(num_blocks)
+        if not self._h:
+            raise RuntimeError(load().cbx_last_error().decode())
+
+    def num_free(self) -> int:
+        return load().cbx_pool_num_free(self._h)
+
+    def alloc(self, n: int) -> list[int]:
+        buf = (C.c_int32 * max(n, 1))()
+        rc = load().cbx_pool_alloc(self._h, n, buf)
+        if rc != 0:
+            raise ValueError(load().cbx_last_error().decode())
+        return list(buf[:n])
+
+    def free(self, ids: list[int]) -> None:
+        buf = (C.c_int32 * max(len(ids), 1))(*ids)
+        check(load().cbx_pool_free(self._h, buf, len(ids)), "pool_free")
+
+    def __del__(self):
+        try:
+            if self._h:
+                load().cbx_pool_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+__all__ = ["slot_mapping", "rmsnorm", "pack_gate_up", "linear", "rope_kv_append", "paged_attn_decode",
+           "SamplerBuffers", "cfg_sample", "decode_prepare", "prefill_embed", "BlockPool", "BLOCK_SIZE", "HIDDEN",
+           "INTER", "LOGITS_LD", "PAGE_BYTES", "SEEN_WORDS", "SPEECH_VOCAB", "_lib"]

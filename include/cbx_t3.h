@@ -1,0 +1,181 @@
+/* cbx_t3.h — C-ABI of libcbx_t3.so: the B200 (sm_100a) implementation of the
+ * Chatterbox T3 speech-token decode path.
+ *
+ * The reference (iMash-io/chatterbox-vllm) is pure Python and has no FFI; the
+ * arithmetic of this path lives in vLLM / torch kernels it calls.  Each entry
+ * point below therefore cites the reference CALL SITE (relative to the reference
+ * repo root) or the vLLM-0.22 source ("vllm:" prefix) whose behaviour it replaces.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error (cbx_last_error() gives a
+ *     thread-local message); no C++ exception crosses this boundary;
+ *   - all tensor pointers are DEVICE pointers owned by the caller (bf16 unless
+ *     noted, row-major, innermost stride 1); nothing here allocates device memory
+ *     except cbx_engine_* scratch that the caller sizes via cbx_engine_workspace_bytes;
+ *   - every launch is asynchronous on the cudaStream_t passed as `void* stream`;
+ *   - one engine handle per device; not re-entrant (single submitting thread, as
+ *     vLLM's GPU worker is).
+ */
+#ifndef CBX_T3_H_
+#define CBX_T3_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Fixed model geometry (t3-model/config.json; models/t3/modules/t3_config.py:1-21). */
+#define CBX_HIDDEN      1024
+#define CBX_HEADS       16
+#define CBX_HEAD_DIM    64
+#define CBX_INTER       4096
+#define CBX_SPEECH_VOCAB 8194
+#define CBX_BLOCK_SIZE  16          /* vllm: KV block size the reference runs with   */
+#define CBX_LOGITS_LD   8256        /* padded row stride of the bf16 logits buffer   */
+#define CBX_SEEN_WORDS  257         /* ceil(8194 / 32) words of seen-token bitmap    */
+/* One KV page = one (layer, block): K[16 heads][16 tok][64] (16-byte chunks XOR-
+ * swizzled by tok&7) followed by V[16 heads][16 tok][64]; 65536 bytes. */
+#define CBX_PAGE_BYTES  65536
+
+const char* cbx_last_error(void);
+int cbx_abi_version(void);
+
+/* ---- integer bookkeeping (bit-exact) ------------------------------------------ */
+
+/* vllm: v1/worker/block_table.py:357-377.  slot[i] = bt[req[i]][pos[i]/16]*16 + pos[i]%16,
+ * or -1 when pos[i] < 0.  bt int32 [n_rows, bt_stride]; req,pos int32 [n]; slot int64 [n]. */
+int cbx_slot_mapping(const int32_t* block_table, int bt_stride, const int32_t* req,
+                     const int32_t* pos, int64_t* slot, int n, void* stream);
+
+/* Host-side block pool with vLLM's policy (vllm: v1/core/block_pool.py:162-177,333-347,
+ * 419-433; single_type_kv_cache_manager.py:120,350).  Pure CPU, no CUDA. */
+typedef struct cbx_pool cbx_pool;
+cbx_pool* cbx_pool_create(int num_blocks);                     /* block 0 reserved (null block) */
+void      cbx_pool_destroy(cbx_pool*);
+int       cbx_pool_num_free(const cbx_pool*);
+int       cbx_pool_alloc(cbx_pool*, int n, int32_t* out_ids);  /* popleft n; <0 if n > free     */
+int       cbx_pool_free(cbx_pool*, const int32_t* ids, int n); /* appended in the order given   */
+
+/* ---- per-kernel ops (unit-testable pieces of the step) ------------------------- */
+
+/* vllm: _C.rms_norm / fused_add_rms_norm as used by llama.py:316-333.
+ * residual == NULL: out = norm(x)·w.   Else: residual = bf16(x + residual) in place,
+ * out = norm(residual)·w.  x,out,residual [T,1024]; w [1024]. */
+int cbx_rmsnorm(const void* x, void* residual, const void* w, void* out, int T, float eps, void* stream);
+
+/* y[T,N] = x[T,K] · W[N,K]^T (bf16 in, fp32 accumulate, bf16 out).  Replaces the
+ * cuBLAS GEMMs behind vllm llama.py:117-120,221,225 and t3.py:729-730.
+ * epilogue: 0 = store; 1 = SiLU(gate)·up with W packed by cbx_pack_gate_up (y is [T,N/2]);
+ * path: 0 = auto, 1 = force SIMT GEMV (T ≤ 8), 2 = force tcgen05 GEMM.  ldy = row stride of y. */
+int cbx_linear(const void* x, const void* W, void* y, int T, int N, int K, int ldy,
+               int epilogue, int path, void* stream);
+/* Interleaves gate/up rows in groups of 16 ([g0..15,u0..15,g16..31,...]) so both land
+ * in one accumulator fragment.  src [2*I,K] (gate;up stacked, vllm llama.py:433-441). */
+int cbx_pack_gate_up(const void* src, void* dst, int I, int K, void* stream);
+
+/* vllm: _C.rotary_embedding (neox, llama.py:223) + reshape_and_cache_flash
+ * (flash_attn.py:850-874).  qkv [T,3072]: q rotated in place; rotated k and v are written
+ * to page slot[i] of `kv_layer` (base of this layer's pages).  cos_sin bf16 [max_pos,64]. */
+int cbx_rope_kv_append(void* qkv, const int32_t* pos, const int64_t* slot, const void* cos_sin,
+                       void* kv_layer, int T, void* stream);
+
+/* vllm: flash_attn_varlen_func over the paged cache (flash_attn.py:796-800), decode form:
+ * one query row per entry.  q rows are read from qkv [T,3072] (first 1024 columns);
+ * row i attends to positions [0, kv_len[i]) of block-table row row_seq[i].
+ * out bf16 [T,1024].  scratch: cbx_attn_scratch_bytes(T, max_kv_len). */
+int64_t cbx_attn_scratch_bytes(int T, int max_kv_len);
+int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* block_table,
+                          int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
+                          void* out, void* scratch, int T, int max_kv_len, void* stream);
+
+/* t3.py:732 (CFG merge) + vllm v1 Sampler (sampler.py:67-300) in one kernel, one CTA per
+ * pair.  logits bf16 [2B, CBX_LOGITS_LD] (rows b = cond, B+b = uncond).  Per-pair state
+ * arrays are documented in cbx_sampler_state.  Emits one token per active pair. */
+typedef struct cbx_sampler_state {
+  int32_t*  last_tok;     /* [B] out: sampled speech id (no +1000 offset)                   */
+  int32_t*  out_tokens;   /* [B, out_stride] emitted ids                                    */
+  int32_t*  n_out;        /* [B] in/out                                                     */
+  int32_t*  max_out;      /* [B] max_tokens per pair                                        */
+  int32_t*  finished;     /* [B] in/out: 1 once stop token or max_out reached               */
+  int32_t*  seq_len;      /* [2B] in/out: += 1 for rows of pairs that were active           */
+  uint32_t* seen;         /* [B, CBX_SEEN_WORDS] prompt∪output bitmap (speech-id space)     */
+  const float* temperature; const float* top_p; const float* min_p; const float* rep_pen; /* [B] */
+  const int32_t* top_k;   /* [B] 0 = off                                                     */
+  const int32_t* ignore_eos; /* [B]                                                          */
+  const uint64_t* seed;   /* [B] Philox key                                                  */
+  const uint64_t* uid;    /* [B] request uid (Philox counter words 2,3)                      */
+  int32_t*  n_finished;   /* [1] running count of finished pairs (host polls this)           */
+  int out_stride; int stop_token; float cfg_scale;
+} cbx_sampler_state;
+int cbx_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, void* stream);
+
+/* t3.py:503-514 (decode) — x[r] = speech_emb[last_tok[r % B]] for r in [0,2B), plus the
+ * per-step index work: pos[r] = seq_len[r]; slot[r] from the block table (-1 for finished
+ * pairs); kv_len[r] = seq_len[r]+1 (0 for finished pairs). */
+int cbx_decode_prepare(const void* speech_emb, const int32_t* last_tok, const int32_t* finished,
+                       const int32_t* seq_len, const int32_t* block_table, int bt_stride,
+                       void* x, int32_t* pos, int64_t* slot, int32_t* kv_len, int B, void* stream);
+
+/* t3.py:548-569 (full-block prefill embeds).  desc int32 [T,4] = {kind, a, b, c}:
+ * kind 0: cond_emb row  (a = request, b = row 0..33) from cond_emb fp32 [n_req,34,1024];
+ * kind 1: text row       text_emb[a] + text_pos[b]; kind 2: zero row (uncond text);
+ * kind 3: start-of-speech speech_emb[a] + speech_pos[b]. */
+int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, const void* text_emb,
+                      const void* text_pos, const void* speech_emb, const void* speech_pos,
+                      void* x, int T, void* stream);
+
+/* ---- engine: the whole T3 step behind one handle -------------------------------- */
+
+typedef struct cbx_weights {
+  int n_layers;
+  const void* const* wqkv;   /* [L] -> [3072,1024]                  */
+  const void* const* wo;     /* [L] -> [1024,1024]                  */
+  const void* const* wgu;    /* [L] -> [8192,1024] PACKED (cbx_pack_gate_up) */
+  const void* const* wd;     /* [L] -> [1024,4096]                  */
+  const void* const* ln1;    /* [L] -> [1024]                       */
+  const void* const* ln2;    /* [L] -> [1024]                       */
+  const void* norm;          /* [1024]                              */
+  const void* speech_emb;    /* [8194,1024]                         */
+  const void* speech_head;   /* [8194,1024]                         */
+  const void* cos_sin;       /* [max_pos,64] bf16                   */
+  float rms_eps;
+} cbx_weights;
+
+typedef struct cbx_engine_cfg {
+  int max_pairs;          /* B: CFG pair slots                                    */
+  int max_rows;           /* row capacity of activation buffers (≥ 2B; prefill T) */
+  int max_model_len;      /* tokens per sequence                                  */
+  int num_blocks;         /* KV pages per layer (block 0 is the null block)       */
+  int out_stride;         /* capacity of out_tokens per pair                      */
+} cbx_engine_cfg;
+
+typedef struct cbx_engine cbx_engine;
+int64_t cbx_engine_workspace_bytes(const cbx_engine_cfg* cfg);
+/* kv_cache: [n_layers][num_blocks] pages of CBX_PAGE_BYTES; block_table int32
+ * [2B, ceil(max_model_len/16)]; workspace: cbx_engine_workspace_bytes(cfg), 1024-aligned. */
+cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_weights* w, void* kv_cache,
+                              int32_t* block_table, void* workspace, const cbx_sampler_state* st);
+void cbx_engine_destroy(cbx_engine*);
+/* Device pointer of an internal buffer by name ("x","h","qkv","attn","act","logits","pos",
+ * "slot","kv_len","row_seq","head_rows") for tests / the Python façade; NULL if unknown. */
+void* cbx_engine_buffer(cbx_engine*, const char* name);
+
+/* Llama forward over T rows whose embeddings are already in buffer "x", with pos/slot/
+ * row_seq/kv_len filled (t3.py:742-778 + vllm llama.py:394-430).  Leaves final-norm hidden
+ * states in buffer "h". */
+int cbx_engine_forward(cbx_engine*, int T, int max_kv_len, void* stream);
+/* Head GEMM over the 2B rows listed in buffer "head_rows" (row index into "h"; cond rows
+ * first) + cbx_cfg_sample (t3.py:725-739 + sampler). */
+int cbx_engine_sample(cbx_engine*, int B, void* stream);
+/* n decode steps for pair slots [0,B): prepare → forward(2B rows) → sample, no host sync.
+ * use_graph != 0 replays a CUDA graph of one step (captured on first use per (B, max_kv_len
+ * bucket)). */
+int cbx_engine_decode(cbx_engine*, int B, int n_steps, int max_kv_len, int use_graph, void* stream);
+/* kernel launches issued by the last cbx_engine_decode call (for bench.py "gpu_launches"). */
+int64_t cbx_engine_last_launch_count(const cbx_engine*);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CBX_T3_H_ */

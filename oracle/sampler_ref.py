@@ -13,7 +13,7 @@ Restates, in numpy fp32, the vLLM v1 sampler chain the reference reaches through
 
 Two things are *specified here* because the reference leaves them to library
 accident: (1) ties — equal logits are ranked by ascending token id (lower id
-wins argmax and is kept first by top-p/top-k); (2) the random stream — torch's
+wins argmax and is kept first by top-p; top-k keeps every tie with the k-th value, as vLLM); (2) the random stream — torch's
 global Philox state is replaced by a counter-based Philox4x32-10 keyed by
 (seed, request uid, step, token id), so results do not depend on batch layout or
 on how many GPUs the requests are sharded over.
@@ -49,12 +49,12 @@ def philox4x32_10(ctr, key):
 
 
 def exp1_variates(seed: int, uid: int, step: int, token_ids) -> np.ndarray:
-    """Exp(1) draws e_i = −ln(u_i), u_i = ((x_i >> 8) + 0.5)·2⁻²⁴ ∈ (0,1), where
+    """Exp(1) draws e_i = −ln(u_i), u_i = ((x_i >> 9) + 0.5)·2⁻²³ ∈ (0,1) (exact in fp32), where
     x_i = word 0 of Philox(ctr=(token id, step, uid_lo, uid_hi), key=seed)."""
     tid = np.asarray(token_ids, dtype=np.uint32)
     x = philox4x32_10((tid, step & 0xFFFFFFFF, uid & 0xFFFFFFFF, (uid >> 32) & 0xFFFFFFFF),
                       (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF))[0]
-    u = ((x >> np.uint32(8)).astype(np.float32) + np.float32(0.5)) * np.float32(2.0 ** -24)
+    u = ((x >> np.uint32(9)).astype(np.float32) + np.float32(0.5)) * np.float32(2.0 ** -23)
     return -np.log(u, dtype=np.float32)
 
 
@@ -89,11 +89,9 @@ def kept_set(l: np.ndarray, temperature: float, min_p: float = 0.0, top_p: float
         e = np.exp(l - m, dtype=np.float32)
         probs = e / e.sum(dtype=np.float32)
         keep &= ~(probs < probs.max() * np.float32(min_p))
-    order = _rank_desc(np.where(keep, l, -np.inf))
-    if top_k and 0 < top_k < V:
-        kk = np.zeros(V, bool)
-        kk[order[:top_k]] = True
-        keep &= kk
+    if top_k and 0 < top_k < V:       # topk_topp_sampler.py:346-351: every tie with the k-th value stays
+        lm = np.where(keep, l, -np.inf)
+        keep &= lm >= np.sort(lm)[V - top_k]
     margin = np.full(V, np.inf, np.float64)
     if top_p < 1.0:
         lm = np.where(keep, l, -np.inf)

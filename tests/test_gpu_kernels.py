@@ -1,0 +1,210 @@
+"""GPU parity tests, kernel by kernel, through the C-ABI (chatterbox_vllm_b200.ops) against
+the CPU oracle.  Integer work is bit-exact; floating point has its tolerance written at the
+assert.  bf16 has an 8-bit significand: 1 ulp = 2^-8 relative."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import paging_ref, sampler_ref
+from oracle.t3_ref import T3ModelConfig, T3Oracle, T3Weights, apply_rope, rmsnorm, rope_cos_sin
+
+pytestmark = pytest.mark.gpu
+BF16 = torch.bfloat16
+ULP = 2.0 ** -8
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from chatterbox_vllm_b200 import ops as _ops
+    _ops._lib.load()
+    return _ops
+
+
+def dev(t):
+    return t.cuda()
+
+
+def assert_close_bf16(got, want, ulps=2.0, atol=1e-6, what=""):
+    got, want = got.float().cpu(), want.float().cpu()
+    err = (got - want).abs()
+    tol = ulps * ULP * want.abs() + atol
+    bad = err > tol
+    assert not bad.any(), f"{what}: {int(bad.sum())} elements off; max err {err.max():.3e} (|want| max {want.abs().max():.3e})"
+
+
+# ------------------------------------------------------------------ integer work: bit-exact
+def test_slot_mapping_bit_exact(ops):
+    rng = np.random.default_rng(0)
+    for occupancy in (0.25, 0.5, 0.95):
+        pool = paging_ref.BlockPool(4096)
+        bt = paging_ref.BlockTable(pool, max_seqs=64, max_model_len=1000)
+        lens = rng.integers(1, int(1000 * occupancy) + 2, size=64)
+        for r, n in enumerate(lens):
+            bt.ensure(r, int(n))
+        req = rng.integers(0, 64, size=5000).astype(np.int32)
+        pos = np.array([rng.integers(-1, lens[r]) for r in req], np.int32)      # -1 = padded row
+        want = paging_ref.slot_mapping(bt.table, req, pos)
+        got = ops.slot_mapping(dev(torch.from_numpy(bt.table)), dev(torch.from_numpy(req)), dev(torch.from_numpy(pos)))
+        assert got.dtype == torch.int64 and np.array_equal(got.cpu().numpy(), want)
+    assert ops.slot_mapping(dev(torch.zeros(1, 4, dtype=torch.int32)), dev(torch.zeros(0, dtype=torch.int32)),
+                            dev(torch.zeros(0, dtype=torch.int32))).numel() == 0          # empty input
+
+
+# ------------------------------------------------------------------ norms
+@pytest.mark.parametrize("T", [1, 2, 7, 256])
+def test_rmsnorm_and_fused_add(ops, T):
+    g = torch.Generator().manual_seed(T)
+    x = (torch.randn(T, 1024, generator=g) * 0.7).to(BF16)
+    res = (torch.randn(T, 1024, generator=g) * 1.3).to(BF16)
+    w = (1 + 0.1 * torch.randn(1024, generator=g)).to(BF16)
+    out = ops.rmsnorm(dev(x), dev(w))
+    assert_close_bf16(out, rmsnorm(x.float(), w, 1e-5, "bf16"), ulps=1.01, what="rmsnorm")
+    r = dev(res.clone())
+    out = ops.rmsnorm(dev(x), dev(w), residual=r)
+    z = (x.float() + res.float()).to(BF16)
+    assert torch.equal(r.cpu(), z), "residual stream must be bf16(x + res) exactly"
+    assert_close_bf16(out, rmsnorm(z.float(), w, 1e-5, "bf16"), ulps=1.01, what="add_rmsnorm")
+
+
+# ------------------------------------------------------------------ linear layers
+def _ref_linear(x, W):
+    return (x.double() @ W.double().T).float()
+
+
+@pytest.mark.parametrize("T", [1, 2, 3, 4])
+@pytest.mark.parametrize("N,K", [(3072, 1024), (1024, 4096), (8194, 1024)])
+def test_linear_gemv(ops, T, N, K):
+    g = torch.Generator().manual_seed(N + T)
+    x = torch.randn(T, K, generator=g).to(BF16)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(BF16)
+    y = ops.linear(dev(x), dev(W), path=1)
+    # fp32 accumulation of K products, then one bf16 rounding: 1 ulp + accumulation noise
+    assert_close_bf16(y, _ref_linear(x, W), ulps=1.0, atol=2e-3, what=f"gemv T={T} N={N} K={K}")
+
+
+@pytest.mark.parametrize("T", [1, 5, 64, 128, 200, 256, 300])
+@pytest.mark.parametrize("N,K", [(3072, 1024), (1024, 1024), (1024, 4096), (8194, 1024)])
+def test_linear_gemm_tcgen05(ops, T, N, K):
+    g = torch.Generator().manual_seed(N + 7 * T)
+    x = torch.randn(T, K, generator=g).to(BF16)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(BF16)
+    ld = 8256 if N == 8194 else N
+    out = torch.full((T, ld), 7.0, dtype=BF16).cuda()
+    ops.linear(dev(x), dev(W), path=2, out=out)
+    assert_close_bf16(out[:, :N], _ref_linear(x, W), ulps=1.0, atol=2e-3, what=f"gemm T={T} N={N} K={K}")
+    if ld > N:
+        assert (out[:, N:].float() == 7.0).all(), "columns >= N must not be written"
+
+
+@pytest.mark.parametrize("T,path", [(2, 1), (4, 1), (6, 2), (256, 2)])
+def test_linear_silu_mul_epilogue(ops, T, path):
+    g = torch.Generator().manual_seed(T)
+    x = torch.randn(T, 1024, generator=g).to(BF16)
+    Wgu = (torch.randn(8192, 1024, generator=g) * 0.05).to(BF16)
+    packed = ops.pack_gate_up(dev(Wgu))
+    # packing is a pure permutation: rows [g0..15,u0..15,g16..31,...]
+    j = torch.arange(4096)
+    assert torch.equal(packed.cpu()[(j // 16) * 32 + j % 16], Wgu[:4096])
+    assert torch.equal(packed.cpu()[(j // 16) * 32 + 16 + j % 16], Wgu[4096:])
+    y = ops.linear(dev(x), packed, epilogue=1, path=path)
+    gu = _ref_linear(x, Wgu).to(BF16).float()
+    want = torch.nn.functional.silu(gu[:, :4096]) * gu[:, 4096:]
+    # g,u may each differ by 1 ulp before the activation -> 3 ulps on the product
+    assert_close_bf16(y, want, ulps=3.0, atol=3e-3, what=f"silu_mul T={T}")
+
+
+# ------------------------------------------------------------------ RoPE + KV append + attention
+def _build_paged(ops, cfg, lens, seed, num_blocks=None):
+    """Random per-sequence K/V histories written through rope_kv_append into a paged cache."""
+    S = len(lens)
+    g = torch.Generator().manual_seed(seed)
+    max_len = max(lens)
+    nb = num_blocks or (sum(-(-n // 16) for n in lens) + 8)
+    pool = paging_ref.BlockPool(nb)
+    bt = paging_ref.BlockTable(pool, S, ((max_len + 15) // 16) * 16)
+    order = np.random.default_rng(seed).permutation(S)
+    for r in order:                                       # interleaved allocation -> scattered pages
+        bt.ensure(int(r), lens[r])
+    kv = torch.zeros(nb * 65536, dtype=torch.uint8).cuda()
+    cs = rope_cos_sin(cfg, max_len + 1)
+    cs_d = dev(cs.to(BF16))
+    bt_d = dev(torch.from_numpy(bt.table))
+    qkv_all = [(torch.randn(n, 3072, generator=g)).to(BF16) for n in lens]
+    for r in range(S):
+        n = lens[r]
+        pos = torch.arange(n, dtype=torch.int32)
+        slot = ops.slot_mapping(bt_d, dev(torch.full((n,), r, dtype=torch.int32)), dev(pos))
+        ops.rope_kv_append(dev(qkv_all[r]), dev(pos), slot, cs_d, kv)
+    return kv, bt_d, qkv_all, cs
+
+
+def _ref_attn(cfg, qkv_hist, q_row, L, cs):
+    """fp32 attention of one query (already rotated) over the first L tokens of a history."""
+    k = apply_rope(qkv_hist[:L, 1024:2048].float().view(L, 16, 64), torch.arange(L), cs, "bf16")
+    v = qkv_hist[:L, 2048:].float().view(L, 16, 64)
+    s = torch.einsum("hd,lhd->hl", q_row.view(16, 64), k) * 0.125
+    return torch.einsum("hl,lhd->hd", torch.softmax(s, -1), v).reshape(1024)
+
+
+def test_rope_q_in_place_and_kv_layout(ops):
+    cfg = T3ModelConfig()
+    kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, [37], seed=1)
+    n = 37
+    qkv = dev(qkv_all[0].clone())
+    pos = torch.arange(n, dtype=torch.int32)
+    slot = ops.slot_mapping(bt_d, dev(torch.zeros(n, dtype=torch.int32)), dev(pos))
+    ops.rope_kv_append(qkv, dev(pos), slot, dev(cs.to(BF16)), kv)
+    want_q = apply_rope(qkv_all[0][:, :1024].float().view(n, 16, 64), pos.long(), cs, "bf16").reshape(n, 1024)
+    assert_close_bf16(qkv[:, :1024], want_q, ulps=1.01, what="rotated q")
+    assert torch.equal(qkv[:, 2048:].cpu(), qkv_all[0][:, 2048:]), "v columns untouched"
+    # page layout: K[head][tok][chunk ^ (tok&7)], V[head][tok][chunk]
+    want_k = apply_rope(qkv_all[0][:, 1024:2048].float().view(n, 16, 64), pos.long(), cs, "bf16").to(BF16)
+    pages = kv.cpu().view(-1, 65536)
+    bt = bt_d.cpu().numpy()
+    for t in (0, 5, 16, 36):
+        page = pages[bt[0, t // 16]].view(torch.bfloat16)
+        for h in (0, 7, 15):
+            krow = page[(h * 16 + t % 16) * 64:(h * 16 + t % 16) * 64 + 64].view(8, 8)
+            unsw = torch.stack([krow[c ^ (t % 16 & 7)] for c in range(8)]).reshape(64)
+            assert_close_bf16(unsw, want_k[t, h], ulps=1.01, what="K page")
+            vrow = page[16384 + (h * 16 + t % 16) * 64:16384 + (h * 16 + t % 16) * 64 + 64]
+            assert torch.equal(vrow, qkv_all[0][t, 2048 + h * 64:2048 + h * 64 + 64])
+    # slot -1 rows must not touch the cache
+    before = kv.clone()
+    ops.rope_kv_append(dev(qkv_all[0][:3].clone()), dev(pos[:3]), dev(torch.full((3,), -1, dtype=torch.int64)),
+                       dev(cs.to(BF16)), kv)
+    assert torch.equal(before, kv)
+
+
+@pytest.mark.parametrize("lens", [[1], [15, 16, 17], [100, 3, 450, 64], [1000, 999], list(range(1, 70))])
+def test_paged_attention_vs_oracle(ops, lens):
+    cfg = T3ModelConfig()
+    kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, lens, seed=len(lens))
+    S = len(lens)
+    g = torch.Generator().manual_seed(99)
+    q = torch.randn(S, 3072, generator=g).to(BF16)
+    out = ops.paged_attn_decode(dev(q), kv, bt_d, dev(torch.arange(S, dtype=torch.int32)),
+                                dev(torch.tensor(lens, dtype=torch.int32)), max(lens))
+    for r in range(S):
+        want = _ref_attn(cfg, qkv_all[r], q[r, :1024].float(), lens[r], cs)
+        # fp32 softmax/accumulate, one bf16 rounding of the output
+        assert_close_bf16(out[r], want, ulps=1.0, atol=2e-3, what=f"attn row {r} L={lens[r]}")
+
+
+def test_paged_attention_many_rows_single_split_and_empty_rows(ops):
+    """Prefill-style use: many query rows, each attending to a prefix of a shared sequence;
+    kv_len = 0 rows (finished pairs) give zeros."""
+    cfg = T3ModelConfig()
+    lens = [200, 77]
+    kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, lens, seed=3)
+    rows = [(0, L) for L in range(1, 201, 1)] + [(1, L) for L in range(0, 78)] * 12   # > 148*6 rows -> nsplit 1
+    g = torch.Generator().manual_seed(5)
+    q = torch.randn(len(rows), 3072, generator=g).to(BF16)
+    out = ops.paged_attn_decode(dev(q), kv, bt_d, dev(torch.tensor([r for r, _ in rows], dtype=torch.int32)),
+                                dev(torch.tensor([L for _, L in rows], dtype=torch.int32)), 200)
+    for i in list(range(0, len(rows), 37)) + [200, 201]:
+        r, L = rows[i]
+        want = _ref_attn(cfg, qkv_all[r], q[i, :1024].float(), L, cs) if L else torch.zeros(1024)
+        assert_close_bf16(out[i], want, ulps=1.0, atol=2e-3, what=f"row {i} (seq {r}, L={L})")

@@ -1,0 +1,18 @@
+#!/bin/bash
+# Runs the GPU parity tests group by group, each in its own process under a timeout, so a
+# hung kernel in one group cannot take the rest (or the box) with it.  Logs -> gpurun_out/.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
+run() { # name, pytest args...
+  local name=$1; shift
+  timeout -k 5 ${TMO:-420} python -m pytest -q -m gpu -p no:cacheprovider "$@" > gpurun_out/test_$name.log 2>&1
+  echo "$name rc=$? $(tail -1 gpurun_out/test_$name.log)"
+}
+run ints    tests/test_gpu_kernels.py -k "slot_mapping or rmsnorm"
+run gemv    tests/test_gpu_kernels.py -k "gemv"
+run gemm    tests/test_gpu_kernels.py -k "gemm_tcgen05"
+run silu    tests/test_gpu_kernels.py -k "silu"
+run rope    tests/test_gpu_kernels.py -k "rope"
+run attn    tests/test_gpu_kernels.py -k "paged_attention"
+run sampler tests/test_gpu_engine.py -k "sampler or prefill_embed"
+run engine  tests/test_gpu_engine.py -k "engine"
