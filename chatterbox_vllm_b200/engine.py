@@ -74,6 +74,8 @@ class T3Engine:
         # CHATTERBOX_CFG_SCALE is read once at model construction (t3.py:343)
         self.cfg_scale = float(os.environ.get("CHATTERBOX_CFG_SCALE", "0.5")) if cfg_scale is None else cfg_scale
         self.use_graph, self.base_seed, self._next_uid = use_graph, base_seed, 0
+        # a dedicated non-default stream: CUDA graphs cannot be captured on the legacy stream
+        self.stream = torch.cuda.Stream(device=self.device)
         self._load_weights(state_dict, rms_eps)
         self.bt_stride = -(-max_model_len // BLOCK_SIZE)
         if num_blocks is None:
@@ -258,6 +260,13 @@ class T3Engine:
     def generate(self, reqs: list[Request], poll_every: int = 32) -> list[list[int]]:
         """Runs requests in static waves of ≤ max_pairs; returns speech-token ids per request in
         vLLM id space (speech id + 1000), stop token included, like vLLM's output.token_ids."""
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            out = self._generate(reqs, poll_every)
+        torch.cuda.current_stream().wait_stream(self.stream)
+        return out
+
+    def _generate(self, reqs: list[Request], poll_every: int) -> list[list[int]]:
         out: list[list[int]] = []
         for w0 in range(0, len(reqs), self.max_pairs):
             wave = reqs[w0:w0 + self.max_pairs]

@@ -10,7 +10,7 @@ from oracle.t3_ref import T3ModelConfig, T3Oracle, T3Weights, apply_rope, rmsnor
 
 pytestmark = pytest.mark.gpu
 BF16 = torch.bfloat16
-ULP = 2.0 ** -8
+ULP = 2.0 ** -7
 
 
 @pytest.fixture(scope="module")
