@@ -1,0 +1,271 @@
+#!/usr/bin/env python3
+"""bench.py — T3 speech tokens/s at 128 CFG pairs per GPU (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W          (torchrun for N > 1, one rank per GPU)
+    python bench.py --impl reference ...                   (reference arm: HF-transformers CPU path)
+
+A "step" is one decode step of the whole batch (128 CFG pairs = 256 sequences per GPU): embed →
+30 Llama layers over the paged KV cache → head → fused CFG sampler; it emits one speech token per
+pair.  Workload = SURVEY §8(d) "M1": 128 pairs, conditioning prefix P = 200, 500 speech tokens,
+bf16, random-init weights, synthetic prompts.  The K timed steps are placed so that their mean
+context equals the workload's mean context (P + 250 = 450) whenever K < 500; with the default
+K/W the timed region IS the decode phase of the 500-token job.
+Inputs are larger than L2 (KV alone is ~14 GB per step), so no L2 flush is needed between steps.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "t3_speech_tokens_per_sec_128_cfg_pairs"
+PAIRS, PREFIX, GEN = 128, 200, 500
+W_BYTES = 1_006_757_888 + 16_781_312          # backbone + speech head, bf16 (SURVEY §8 d)
+KV_TOKEN_BYTES = 122_880                      # per token per sequence, all 30 layers
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(index), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        load = [v for v in sm if v > 0.5 * max(sm)] if sm else []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": statistics.median(load) if load else None,
+                "sm_max_mhz": float(self.rows[0][1]) if self.rows else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_baseline_sample(pairs=2, prefix=450, steps=4, warmup=1, model=None):
+    """The original-Chatterbox-style HF-transformers CPU path (oracle/hf_baseline.py) on a bounded
+    sample of the workload: `pairs` CFG pairs at the workload's mean context, fp32, all host cores."""
+    from oracle import hf_baseline
+    r = hf_baseline.run(pairs, prefix, steps, warmup=warmup, model=model)
+    return {"value": r["tokens"] / r["decode_s"], "unit": "speech_tokens/s", "cores": r["cores"], "kind": "port",
+            "sample": f"{pairs} CFG pairs x {steps} decode steps at context {prefix} (workload mean), fp32 HF "
+                      f"LlamaModel + python sampler; prefill {r['prefill_s']:.1f}s excluded",
+            "ms_per_step": 1e3 * r["decode_s"] / steps}
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's CPU implementation of the path (no GPU code involved)."""
+    if rank != 0:
+        return
+    from oracle import hf_baseline
+    model = hf_baseline.build_model(30)
+    pairs = 2
+    r = hf_baseline.run(pairs, 450, args.steps, warmup=args.warmup, model=model)
+    val = r["tokens"] / r["decode_s"]
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "speech_tokens/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * r["decode_s"] / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{PAIRS} CFG pairs x prefix {PREFIX} x {GEN} speech tokens (M1); each step = "
+                                   f"one decode step of a {pairs}-pair sample at context 450"},
+            "cpu_baseline": {"value": val, "unit": "speech_tokens/s", "cores": r["cores"], "kind": "port",
+                             "sample": f"{pairs} CFG pairs per step, context 450, fp32 HF LlamaModel (original-"
+                                       "chatterbox-style path restated; source absent from the reference tree)"},
+            "e2e": {"value": val, "unit": "speech_tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=PAIRS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        args.steps, args.warmup = args.steps or 4, 1 if args.warmup is None else args.warmup
+        return run_reference(args, rank, world)
+    args.steps = args.steps or 480
+    args.warmup = max(3, 20 if args.warmup is None else args.warmup)
+
+    import torch
+    import torch.distributed as dist
+    from chatterbox_vllm_b200 import ops
+    from chatterbox_vllm_b200.engine import Request, SamplingParams, T3Engine
+    from chatterbox_vllm_b200.synthetic import random_cond_emb, random_prompt, random_state_dict
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, K, W = args.pairs, args.steps, args.warmup
+    L0 = max(PREFIX + 1 + W, PREFIX + GEN // 2 - K // 2)        # context at the first timed step
+    pre = L0 - PREFIX - 1                                       # untimed decode steps (>= W warm-up)
+    max_tokens = 1 + pre + K
+    max_len = PREFIX + max_tokens + 8
+    eng = T3Engine(random_state_dict(30, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
+                   max_rows=16384, base_seed=1234 + rank)
+    sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=max_tokens, ignore_eos=True)
+    # global prompt index keeps the Philox streams independent of how requests are sharded
+    reqs = [Request(random_prompt(PREFIX - 35, seed=rank * B + i), random_cond_emb(rank * B + i, pinned=True), sp,
+                    uid=1 + rank * B + i) for i in range(B)]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident arm: prefill + untimed steps, then EXACTLY K timed decode steps
+    with torch.cuda.stream(eng.stream):
+        P, held = eng._admit(reqs)
+        eng._init_sampler_state(reqs, P)
+        eng.prefill(reqs, P)
+        done = 0
+        while done < pre:
+            n = min(32, pre - done)
+            eng.decode(B, n, PREFIX + 1 + done + n)
+            done += n
+        barrier()
+        clocks = ClockSampler(local)
+        l0 = eng.gpu_launches
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(eng.stream)
+        done = 0
+        while done < K:
+            n = min(32, K - done)
+            eng.decode(B, n, L0 + done + n)
+            done += n
+        ev1.record(eng.stream)
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        clk = clocks.stop()
+        launches = eng.gpu_launches - l0
+        n_out = eng.sb.n_out[:B].cpu()
+        assert int(n_out.min()) == max_tokens and int(eng.sb.n_finished.item()) == B, "bench: wrong token count"
+        toks = eng.sb.out_tokens[:B, :max_tokens].contiguous()
+        if world > 1:                                           # gather emitted token streams (the only collective)
+            allt = torch.empty(world * B, max_tokens, dtype=toks.dtype, device=dev)
+            dist.all_gather_into_tensor(allt, toks)
+        # ---- roofline leg: the dominant kernel (paged decode attention) timed alone on its stream
+        mean_ctx = L0 + K // 2
+        kvl = torch.full((2 * B,), mean_ctx, dtype=torch.int32, device=dev)
+        rows = torch.arange(2 * B, dtype=torch.int32, device=dev)
+        qkv = eng.buffer("qkv", (2 * B, 3072), torch.bfloat16)
+        layer_bytes = eng.num_blocks * ops.PAGE_BYTES
+        reps = 3
+        for _ in range(2):
+            ops.paged_attn_decode(qkv, eng.kv_cache[:layer_bytes], eng.block_table, rows, kvl, mean_ctx)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(eng.stream)
+        for _ in range(reps):
+            for li in range(eng.n_layers):                      # a different layer's pages each launch: cold in L2
+                ops.paged_attn_decode(qkv, eng.kv_cache[li * layer_bytes:(li + 1) * layer_bytes], eng.block_table,
+                                      rows, kvl, mean_ctx)
+        a1.record(eng.stream)
+        torch.cuda.synchronize()
+        attn_ms = a0.elapsed_time(a1) / (reps * eng.n_layers)
+        eng._release(held)
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * B * K / (ms / 1e3)
+
+    # ---- end-to-end arm: public engine API, host buffers in, host token lists out
+    e2e = None
+    if not args.no_e2e:
+        gen_e2e = min(GEN, 1 + pre + K)
+        sp2 = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=gen_e2e, ignore_eos=True)
+        for r in reqs:
+            r.params = sp2
+        barrier()
+        t0 = time.perf_counter()
+        out = eng.generate(reqs)
+        torch.cuda.synchronize()
+        if world > 1:
+            mine = torch.tensor(out, dtype=torch.int32, device=dev)
+            allt = torch.empty(world * B, gen_e2e, dtype=torch.int32, device=dev)
+            dist.all_gather_into_tensor(allt, mine)
+            torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        h2d = B * 34 * 1024 * 4 + sum(2 * (35 + len(r.text_ids)) * (16 + 4 + 4 + 4 + 8) for r in reqs) + 2 * B * eng.bt_stride * 4
+        d2h = B * eng.max_model_len * 4 + B * 4 + 4 * (gen_e2e // 32 + 1)
+        e2e = {"value": world * B * gen_e2e / float(dt.item()), "unit": "speech_tokens/s",
+               "h2d_bytes_per_step": h2d / gen_e2e, "d2h_bytes_per_step": d2h / gen_e2e,
+               "what": f"T3Engine.generate: pinned-host prompts+cond_emb in, prefill + {gen_e2e} tokens/pair, token lists out"}
+        assert all(len(o) == gen_e2e for o in out)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    hbm, which = peaks()
+    attn_bytes = 2 * B * (mean_ctx * (KV_TOKEN_BYTES // 30) + 2048 + 2048)
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "attn_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    step_bytes = W_BYTES + 2 * B * (KV_TOKEN_BYTES * (mean_ctx + 1) + KV_TOKEN_BYTES + 2048)
+    line = {"metric": METRIC, "value": value, "unit": "speech_tokens/s", "n_gpus": world, "steps": K, "warmup": pre,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": f"M1: {B} CFG pairs ({2 * B} seqs) per GPU, prefix {PREFIX}, {GEN} speech tokens, "
+                                   f"T3 Llama-520M random-init; timed steps at context {L0}..{L0 + K - 1} (mean {mean_ctx})",
+                       "l2": "inputs larger than L2 (KV ~%.1f GB/step)" % (2 * B * mean_ctx * KV_TOKEN_BYTES / 1e9),
+                       "sampler": "T=0.5 top_p=0.5 rep=2.0 (tts.py defaults after clamp)", "cuda_graph": True},
+            "clocks": clk, "gpu_launches": int(launches), "e2e": e2e,
+            "roofline": {"kernel": "paged_attn_decode_kernel", "bound": "hbm",
+                         "achieved": attn_bytes / (attn_ms / 1e3) / 1e9, "peak": hbm, "unit": "GB/s",
+                         "frac": attn_bytes / (attn_ms / 1e3) / 1e9 / hbm, "traffic": traffic, "peak_source": which,
+                         "us_per_launch": attn_ms * 1e3, "algorithmic_bytes_per_launch": attn_bytes},
+            "step_roofline": {"bytes_per_step": step_bytes, "achieved_gbs": step_bytes / (ms / K / 1e3) / 1e9,
+                              "frac": step_bytes / (ms / K / 1e3) / 1e9 / hbm}}
+    if not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_baseline_sample()
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,7 +1,8 @@
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from tests.test_gpu_engine import _mk_engine, _requests, _oracle_stream
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+from test_gpu_engine import _mk_engine, _requests, _oracle_stream
 from oracle import sampler_ref
 n_steps = 24
 for graph in (False, True):
