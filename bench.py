@@ -115,6 +115,9 @@ def main():
     ap.add_argument("--pairs", type=int, default=PAIRS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-b1", action="store_true")
+    ap.add_argument("--ctx0", type=int, default=None,
+                    help="profiling aid: context length at the first timed step (default: centred on the workload mean)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -136,6 +139,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     B, K, W = args.pairs, args.steps, args.warmup
     L0 = max(PREFIX + 1 + W, PREFIX + GEN // 2 - K // 2)        # context at the first timed step
+    if args.ctx0 is not None:
+        L0 = max(PREFIX + 1 + W, args.ctx0)
     pre = L0 - PREFIX - 1                                       # untimed decode steps (>= W warm-up)
     max_tokens = 1 + pre + K
     max_len = PREFIX + max_tokens + 8
@@ -234,11 +239,41 @@ def main():
                "what": f"T3Engine.generate: pinned-host prompts+cond_emb in, prefill + {gen_e2e} tokens/pair, token lists out"}
         assert all(len(o) == gen_e2e for o in out)
 
+    # ---- M2 leg: p50 decode-step latency at B = 1 pair (config 1 shape: P = 75, 500 tokens)
+    b1 = None
+    if rank == 0 and not args.no_b1:
+        G1 = min(GEN, eng.max_model_len - 76)
+        sp1 = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=G1, ignore_eos=True)
+        r1 = [Request(random_prompt(40, seed=1), random_cond_emb(2, pinned=True), sp1, uid=999_983)]
+        with torch.cuda.stream(eng.stream):
+            P1, held1 = eng._admit(r1)
+            eng._init_sampler_state(r1, P1)
+            eng.prefill(r1, P1)
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(G1)]
+            for i in range(20):                                  # warm-up steps (graph capture of bucket 1)
+                eng.decode(1, 1, P1[0] + 2 + i)
+            evs[0].record(eng.stream)
+            for i in range(1, G1 - 20):
+                eng.decode(1, 1, P1[0] + 21 + i)
+                evs[i].record(eng.stream)
+            torch.cuda.synchronize()
+            eng._release(held1)
+        dts = sorted(evs[i - 1].elapsed_time(evs[i]) for i in range(1, G1 - 20))
+        p50, p95 = dts[len(dts) // 2], dts[int(len(dts) * 0.95)]
+        ctx1 = P1[0] + 20 + (G1 - 20) // 2
+        bytes1 = W_BYTES + 2 * (KV_TOKEN_BYTES * (ctx1 + 1) + KV_TOKEN_BYTES + 2048)
+        b1 = {"metric": "p50_decode_step_ms_b1", "p50_ms": p50, "p95_ms": p95, "steps": len(dts),
+              "workload": f"1 CFG pair (2 seqs), prefix {P1[0]}, context {P1[0] + 21}..{P1[0] + G1} (mean {ctx1})",
+              "bytes_per_step": bytes1, "achieved_gbs": bytes1 / (p50 / 1e3) / 1e9,
+              "tokens_per_s": 1e3 / p50}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     hbm, which = peaks()
+    if b1:
+        b1["frac_of_hbm_peak"] = b1["achieved_gbs"] / hbm
     attn_bytes = 2 * B * (mean_ctx * (KV_TOKEN_BYTES // 30) + 2048 + 2048)
     traffic = None
     try:
@@ -260,6 +295,8 @@ def main():
                          "us_per_launch": attn_ms * 1e3, "algorithmic_bytes_per_launch": attn_bytes},
             "step_roofline": {"bytes_per_step": step_bytes, "achieved_gbs": step_bytes / (ms / K / 1e3) / 1e9,
                               "frac": step_bytes / (ms / K / 1e3) / 1e9 / hbm}}
+    if b1:
+        line["b1"] = b1
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline_sample()
     print(json.dumps(line), flush=True)

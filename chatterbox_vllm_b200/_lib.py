@@ -54,6 +54,7 @@ _PROTOS = {
     "cbx_engine_create": (vp, [C.POINTER(EngineCfg), C.POINTER(Weights), vp, vp, vp, C.POINTER(SamplerState)]),
     "cbx_engine_destroy": (None, [vp]),
     "cbx_engine_buffer": (vp, [vp, C.c_char_p]),
+    "cbx_engine_set_trace": (C.c_int, [vp, vp]),
     "cbx_engine_forward": (C.c_int, [vp, C.c_int, C.c_int, vp]),
     "cbx_engine_sample": (C.c_int, [vp, C.c_int, vp]),
     "cbx_engine_decode": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),

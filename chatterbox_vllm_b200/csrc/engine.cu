@@ -45,6 +45,7 @@ struct cbx_engine {
   void* attn_scratch;
   std::map<std::pair<int, int>, std::pair<cudaGraphExec_t, int64_t>> graphs;   // (B, kv bucket) -> exec, nodes
   int64_t last_launches;
+  bf16* trace = nullptr;
 };
 
 static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
@@ -131,8 +132,19 @@ extern "C" int cbx_engine_forward(cbx_engine* e, int T, int max_kv_len, void* st
     if (cbx_rmsnorm(e->x, e->res, e->ln2[li], e->h, T, e->w.rms_eps, s)) return -1;
     if (linear(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s)) return -1;
     if (linear(e->act, e->wd[li], e->x, T, 1024, 4096, 1024, 0, s)) return -1;
+    if (e->trace) {
+      const size_t n = (size_t)T * CBX_HIDDEN;
+      cudaMemcpyAsync(e->trace + (size_t)(2 * li) * n, e->x, n * 2, cudaMemcpyDeviceToDevice, s);
+      cudaMemcpyAsync(e->trace + (size_t)(2 * li + 1) * n, e->res, n * 2, cudaMemcpyDeviceToDevice, s);
+    }
   }
   return cbx_rmsnorm(e->x, e->res, e->w.norm, e->h, T, e->w.rms_eps, s);
+}
+
+extern "C" int cbx_engine_set_trace(cbx_engine* e, void* trace) {
+  CBX_REQUIRE(e != nullptr, "cbx_engine_set_trace: NULL engine");
+  e->trace = (bf16*)trace;
+  return 0;
 }
 
 extern "C" int cbx_engine_sample(cbx_engine* e, int B, void* stream) {

@@ -147,6 +147,10 @@ class T3Engine:
     def _stream(self) -> int:
         return torch.cuda.current_stream().cuda_stream
 
+    def set_trace(self, trace: torch.Tensor | None) -> None:
+        """Parity hook: bf16 [n_layers, 2, T, 1024] receives (mlp_out, residual) of every layer."""
+        check(load().cbx_engine_set_trace(self._h, trace.data_ptr() if trace is not None else None), "set_trace")
+
     def forward(self, T: int, max_kv_len: int) -> None:
         check(load().cbx_engine_forward(self._h, T, max_kv_len, self._stream()), "engine_forward")
 

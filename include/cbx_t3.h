@@ -161,6 +161,12 @@ void cbx_engine_destroy(cbx_engine*);
  * "slot","kv_len","row_seq","head_rows") for tests / the Python façade; NULL if unknown. */
 void* cbx_engine_buffer(cbx_engine*, const char* name);
 
+/* Parity hook (tests only): while trace != NULL, cbx_engine_forward copies, after every layer
+ * li, the MLP output x and the residual stream res (vllm llama.py:316-333 convention:
+ * HF hidden state = x + res) to trace[(2*li+0)*T*1024] and trace[(2*li+1)*T*1024] (bf16).
+ * Not capturable state: set before the forward call, clear with NULL. */
+int cbx_engine_set_trace(cbx_engine*, void* trace);
+
 /* Llama forward over T rows whose embeddings are already in buffer "x", with pos/slot/
  * row_seq/kv_len filled (t3.py:742-778 + vllm llama.py:394-430).  Leaves final-norm hidden
  * states in buffer "h". */
