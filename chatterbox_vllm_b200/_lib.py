@@ -46,7 +46,12 @@ _PROTOS = {
     "cbx_pack_gate_up": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
     "cbx_rope_kv_append": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_attn_scratch_bytes": (C.c_int64, [C.c_int, C.c_int]),
-    "cbx_paged_attn_decode": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_attn_num_splits": (C.c_int, [C.c_int, C.c_int]),
+    "cbx_paged_attn_decode": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_layer_qkv": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_linear_residual": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_layer_gate_up": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_head_logits": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
     "cbx_cfg_sample": (C.c_int, [vp, C.POINTER(SamplerState), C.c_int, vp]),
     "cbx_decode_prepare": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_prefill_embed": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]),

@@ -32,6 +32,28 @@ int  count_launch();                       // ++ global launch counter; returns 
 
 typedef __nv_bfloat16 bf16;
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------
+// Every kernel of the decode step is launched with programmatic stream serialisation: it may
+// start while its predecessor is still running, prefetches what does not depend on the
+// predecessor (weights), then pdl_wait()s for the predecessor's memory.  Every kernel calls
+// pdl_wait() before touching activations, which keeps completion transitive along the chain.
+// Both instructions are no-ops when the launch did not carry the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+bool pdl_enabled();                        // env CBX_PDL != "0"
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 // ---- bf16 pack / unpack (bf16 -> fp32 is a 16-bit shift: one ALU op per element) ----
 __device__ __forceinline__ float bf_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }

@@ -12,7 +12,8 @@
 //   warps 0-15 consumers, warp = head: QK (lane = token x half-of-d, 128-bit swizzled
 //             LDS), warp-shuffle online softmax in the log2 domain, PV (lane = token-group
 //             x 16-byte chunk), mbarrier hand-back of the stage.
-// Partial (o, m, l) per (row, split) go to scratch; attn_merge_kernel combines them.
+// Partial (o, m, l) per (row, split) go to scratch; the CTA that publishes a row's LAST partial
+// (atomic ticket per row) merges them in the same launch — no second kernel.
 #include "common.cuh"
 
 using namespace cbx;
@@ -39,21 +40,28 @@ inline AttnPlan make_plan(int T, int max_kv_len) {
   return p;
 }
 
+// kTicket: every CTA owns at most one (row, split) item, so the CTA that publishes a row's last
+// partial merges the row in place (small batches: saves a launch on the latency-critical path).
+// Otherwise partials are merged by attn_merge_kernel (large batches: keeps the page stream busy).
+template <bool kTicket>
 __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
     const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt,
     int bt_stride, const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len,
-    bf16* __restrict__ out, float* __restrict__ o_part, float2* __restrict__ ml_part, int T, int pps,
-    int nsplit) {
+    bf16* __restrict__ out, float* __restrict__ o_part, float2* __restrict__ ml_part,
+    int32_t* __restrict__ counters, int T, int pps, int nsplit) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
   uint64_t* empty = full + kStages;
+  volatile int& s_last = *reinterpret_cast<volatile int*>(empty + kStages);   // after the 6 barriers
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+  pdl_trigger();
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
     fence_barrier_init();
   }
   __syncthreads();
+  pdl_wait();                                         // q, kv_len and this step's K/V rows come from the previous kernel
 
   const int n_items = T * nsplit;
   uint32_t it = 0;                                    // pages streamed so far by this CTA
@@ -96,7 +104,7 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
     const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
     const int p0 = split * pps, p1 = min(p0 + pps, n_pages);
     if (p0 >= p1) {
-      if (nsplit == 1 && lane < 8)                    // row with no KV (finished pair): zeros
+      if (split == 0 && lane < 8)                     // row with no KV (finished pair): zeros
         reinterpret_cast<uint4*>(out + (size_t)row * CBX_HIDDEN + h * 64)[lane] = make_uint4(0, 0, 0, 0);
       continue;
     }
@@ -186,9 +194,39 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
         dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
       }
       if (lane == 0) ml_part[pi * CBX_HEADS + h] = make_float2(m, lsum);
+      if (!kTicket) continue;
+      // ---- ticket: the CTA that publishes the row's last partial merges all of them
+      __threadfence();
+      asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+      if (threadIdx.x == 0) {
+        const int ns = min(nsplit, (n_pages + pps - 1) / pps);
+        const int ticket = atomicAdd(&counters[row], 1);
+        s_last = (ticket == ns - 1);
+        if (ticket == ns - 1) counters[row] = 0;      // self-reset for the next launch
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+      if (s_last) {
+        __threadfence();
+        const int ns = min(nsplit, (n_pages + pps - 1) / pps);
+        const int d2 = threadIdx.x * 2, hh = d2 >> 6;  // 512 threads x 2 consecutive d
+        float mx = -INFINITY;
+        for (int sp = 0; sp < ns; ++sp) mx = fmaxf(mx, __ldcg(&ml_part[((size_t)row * nsplit + sp) * CBX_HEADS + hh]).x);
+        float ox = 0.f, oy = 0.f, lt = 0.f;
+        for (int sp = 0; sp < ns; ++sp) {
+          const size_t pj = (size_t)row * nsplit + sp;
+          const float2 ml = __ldcg(&ml_part[pj * CBX_HEADS + hh]);
+          const float wgt = exp2f(ml.x - mx);
+          const float2 a = __ldcg(reinterpret_cast<const float2*>(o_part + pj * CBX_HIDDEN + d2));
+          ox = fmaf(wgt, a.x, ox); oy = fmaf(wgt, a.y, oy);
+          lt = fmaf(wgt, ml.y, lt);
+        }
+        const float inv = 1.f / lt;
+        *reinterpret_cast<uint32_t*>(out + (size_t)row * CBX_HIDDEN + d2) = pack_bf16(ox * inv, oy * inv);
+      }
     }
   }
 }
+
 
 // Combine split partials: 256 threads per row, thread = 4 consecutive d of one head.
 __global__ void __launch_bounds__(256) attn_merge_kernel(const float* __restrict__ o_part,
@@ -196,25 +234,26 @@ __global__ void __launch_bounds__(256) attn_merge_kernel(const float* __restrict
                                                          const int32_t* __restrict__ kv_len,
                                                          bf16* __restrict__ out, int pps, int nsplit) {
   const int row = blockIdx.x, t = threadIdx.x, h = t >> 4;
+  pdl_trigger();
+  pdl_wait();
   const int n_pages = (kv_len[row] + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
   const int ns = min(nsplit, (n_pages + pps - 1) / pps);
+  if (ns == 0) return;                                 // the attention kernel already wrote zeros
+  float mx = -INFINITY;
+  for (int s = 0; s < ns; ++s) mx = fmaxf(mx, ml_part[((size_t)row * nsplit + s) * CBX_HEADS + h].x);
   float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (ns > 0) {
-    float mx = -INFINITY;
-    for (int s = 0; s < ns; ++s) mx = fmaxf(mx, ml_part[((size_t)row * nsplit + s) * CBX_HEADS + h].x);
-    float lt = 0.f;
-    for (int s = 0; s < ns; ++s) {
-      const size_t pi = (size_t)row * nsplit + s;
-      const float2 ml = ml_part[pi * CBX_HEADS + h];
-      const float wgt = exp2f(ml.x - mx);
-      const float4 a = reinterpret_cast<const float4*>(o_part + pi * CBX_HIDDEN)[t];
-      o.x = fmaf(wgt, a.x, o.x); o.y = fmaf(wgt, a.y, o.y); o.z = fmaf(wgt, a.z, o.z); o.w = fmaf(wgt, a.w, o.w);
-      lt = fmaf(wgt, ml.y, lt);
-    }
-    const float inv = 1.f / lt;
-    o.x *= inv; o.y *= inv; o.z *= inv; o.w *= inv;
+  float lt = 0.f;
+  for (int s = 0; s < ns; ++s) {
+    const size_t pi = (size_t)row * nsplit + s;
+    const float2 ml = ml_part[pi * CBX_HEADS + h];
+    const float wgt = exp2f(ml.x - mx);
+    const float4 a = reinterpret_cast<const float4*>(o_part + pi * CBX_HIDDEN)[t];
+    o.x = fmaf(wgt, a.x, o.x); o.y = fmaf(wgt, a.y, o.y); o.z = fmaf(wgt, a.z, o.z); o.w = fmaf(wgt, a.w, o.w);
+    lt = fmaf(wgt, ml.y, lt);
   }
-  reinterpret_cast<uint2*>(out + (size_t)row * CBX_HIDDEN)[t] = make_uint2(pack_bf16(o.x, o.y), pack_bf16(o.z, o.w));
+  const float inv = 1.f / lt;
+  reinterpret_cast<uint2*>(out + (size_t)row * CBX_HIDDEN)[t] =
+      make_uint2(pack_bf16(o.x * inv, o.y * inv), pack_bf16(o.z * inv, o.w * inv));
 }
 }  // namespace
 
@@ -222,8 +261,10 @@ namespace cbx {
 int init_attn() {
   static bool done = false;
   if (done) return 0;
-  cudaError_t e = cudaFuncSetAttribute(paged_attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaError_t e = cudaFuncSetAttribute(paged_attn_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        kSmemBytes);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(paged_attn_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   done = true;
   return 0;
@@ -235,25 +276,48 @@ extern "C" int64_t cbx_attn_scratch_bytes(int T, int max_kv_len) {
   const AttnPlan p = make_plan(T, max_kv_len);
   return (int64_t)T * p.nsplit * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256;
 }
+extern "C" int cbx_attn_num_splits(int T, int max_kv_len) { return T <= 0 ? 0 : make_plan(T, max_kv_len).nsplit; }
 
+namespace cbx {
+int paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
+                         const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch, int32_t* counters,
+                         int T, int max_kv_len, int max_ctas, void* stream);
+}
 extern "C" int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* block_table,
                                      int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
-                                     void* scratch, int T, int max_kv_len, void* stream) {
+                                     void* scratch, int32_t* counters, int T, int max_kv_len, void* stream) {
+  return cbx::paged_attn_decode_ex(qkv, kv_layer, block_table, bt_stride, row_seq, kv_len, out, scratch, counters, T,
+                                   max_kv_len, 148, stream);
+}
+// max_ctas < 148 leaves SMs free for another stream's GEMMs (two-microbatch overlap).
+int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
+                              const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch,
+                              int32_t* counters, int T, int max_kv_len, int max_ctas, void* stream) {
   if (T <= 0) return 0;
   if (cbx::init_attn()) return -1;
   const AttnPlan p = make_plan(T, max_kv_len);
   float* o_part = reinterpret_cast<float*>(scratch);
   float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)T * p.nsplit * CBX_HIDDEN);
-  CBX_REQUIRE(p.nsplit == 1 || scratch != nullptr, "cbx_paged_attn_decode: scratch is NULL");
+  CBX_REQUIRE(p.nsplit == 1 || (scratch != nullptr && counters != nullptr),
+              "cbx_paged_attn_decode: scratch / counters is NULL");
   const int n_items = T * p.nsplit;
-  const int grid = n_items < 148 ? n_items : 148;
-  paged_attn_decode_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
-      (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out, o_part,
-      ml_part, T, p.pps, p.nsplit);
-  CBX_CHECK_LAUNCH("paged_attn_decode");
-  if (p.nsplit > 1) {
-    attn_merge_kernel<<<T, 256, 0, (cudaStream_t)stream>>>(o_part, ml_part, kv_len, (bf16*)out, p.pps, p.nsplit);
-    CBX_CHECK_LAUNCH("attn_merge");
+  const int grid = n_items < max_ctas ? n_items : max_ctas;
+  const bool ticket = p.nsplit > 1 && n_items <= grid;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e =
+      ticket ? launch_pdl(paged_attn_decode_kernel<true>, dim3(grid), dim3(kThreads), kSmemBytes, st, (const bf16*)qkv,
+                          (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out, o_part, ml_part,
+                          counters, T, p.pps, p.nsplit)
+             : launch_pdl(paged_attn_decode_kernel<false>, dim3(grid), dim3(kThreads), kSmemBytes, st, (const bf16*)qkv,
+                          (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out, o_part, ml_part,
+                          counters, T, p.pps, p.nsplit);
+  CBX_REQUIRE(e == cudaSuccess, "paged_attn_decode launch failed: %s", cudaGetErrorString(e));
+  count_launch();
+  if (p.nsplit > 1 && !ticket) {
+    e = launch_pdl(attn_merge_kernel, dim3(T), dim3(256), 0, st, (const float*)o_part, (const float2*)ml_part, kv_len,
+                   (bf16*)out, p.pps, p.nsplit);
+    CBX_REQUIRE(e == cudaSuccess, "attn_merge launch failed: %s", cudaGetErrorString(e));
+    count_launch();
   }
   return 0;
 }

@@ -10,7 +10,12 @@
 //                           (M=128, N=BN, K=16) x4 per stage, accumulator in TMEM;
 //                           tcgen05.commit frees the stage / signals the epilogue;
 //   warp 2  TMEM allocator;
-//   warps 4-7 epilogue    : tcgen05.ld 32x32b -> registers -> (SiLU·mul) -> bf16 -> global.
+//   warps 4-7 epilogue    : tcgen05.ld 32x32b -> registers -> bf16 -> one of
+//                             0 store | 1 SiLU(gate)·up | 2 RoPE + q store + KV-page append (one
+//                             64-wide tile = one head) | 3 residual add in place.
+// Programmatic dependent launch: the producer issues the WEIGHT tiles of the first kStages
+// k-blocks before griddepcontrol.wait, so the weight stream overlaps the previous kernel's tail;
+// activation tiles follow after the wait.
 #include <cuda.h>
 
 #include <map>
@@ -34,10 +39,15 @@ struct Cfg {
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+struct EpiArgs {               // EPI 2 only
+  const bf16* cos_sin; const int32_t* pos; const int64_t* slot; uint8_t* kv_layer;
+};
+
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                               const __grid_constant__ CUtensorMap tma_b,
-                                                              bf16* __restrict__ y, int M, int N, int K, int ldy) {
+                                                              bf16* __restrict__ y, int M, int N, int K, int ldy,
+                                                              const EpiArgs ea) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -50,6 +60,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
   const int n_kb = K / BK;
 
+  pdl_trigger();
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
@@ -70,7 +81,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < n_kb; ++kb) {
+      // weights of the first ring fill do not depend on the previous kernel
+      const int n_pre = n_kb < C::kStages ? n_kb : C::kStages;
+      for (int kb = 0; kb < n_pre; ++kb) {
+        mbar_arrive_expect_tx(&full[kb], C::kStageBytes);
+        tma_load_2d(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kb * BK, n0, &full[kb]);
+      }
+      pdl_wait();
+      for (int kb = 0; kb < n_pre; ++kb)
+        tma_load_2d(smem + kb * C::kStageBytes, &tma_a, kb * BK, m0, &full[kb]);
+      for (int kb = n_pre; kb < n_kb; ++kb) {
         const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_arrive_expect_tx(&full[s], C::kStageBytes);
@@ -78,8 +98,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         tma_load_2d(sa, &tma_a, kb * BK, m0, &full[s]);
         tma_load_2d(sa + C::kABytes, &tma_b, kb * BK, n0, &full[s]);
       }
+    } else {
+      pdl_wait();
     }
   } else if (warp == 1) {
+    pdl_wait();
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
       for (int kb = 0; kb < n_kb; ++kb) {
@@ -97,9 +120,66 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     }
   } else if (warp >= 4) {
     const int ew = warp - 4;                           // == warp % 4: TMEM lane quarter
+    pdl_wait();
     mbar_wait(tmem_full, 0);
     tc_fence_after();
     const int row = m0 + ew * 32 + lane;
+    if (EPI == 2) {
+      // ---- RoPE + q store + KV append: this 64-wide tile is head (n0/64) % 16 of q (0), k (1) or v (2)
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16), r0);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + 32, r1);
+      tmem_ld_wait();
+      if (row < M) {
+        const int head48 = n0 >> 6, which = head48 >> 4, h = head48 & 15;
+        uint32_t o1[16], o2[16];
+        if (which < 2) {
+          const int p = ea.pos[row];
+          const uint4* cs = reinterpret_cast<const uint4*>(ea.cos_sin + (size_t)p * 64);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const uint4 cv = cs[c], sv = cs[4 + c];
+            const uint32_t cw[4] = {cv.x, cv.y, cv.z, cv.w}, sw[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int e = c * 8 + i * 2;
+              const float x1l = round_bf16(__uint_as_float(r0[e])), x1h = round_bf16(__uint_as_float(r0[e + 1]));
+              const float x2l = round_bf16(__uint_as_float(r1[e])), x2h = round_bf16(__uint_as_float(r1[e + 1]));
+              const float cl = bf_lo(cw[i]), ch = bf_hi(cw[i]), sl = bf_lo(sw[i]), sh = bf_hi(sw[i]);
+              o1[c * 4 + i] = pack_bf16(x1l * cl - x2l * sl, x1h * ch - x2h * sh);
+              o2[c * 4 + i] = pack_bf16(x2l * cl + x1l * sl, x2h * ch + x1h * sh);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            o1[i] = pack_bf16(__uint_as_float(r0[2 * i]), __uint_as_float(r0[2 * i + 1]));
+            o2[i] = pack_bf16(__uint_as_float(r1[2 * i]), __uint_as_float(r1[2 * i + 1]));
+          }
+        }
+        if (which == 0) {
+          uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + h * 64);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            dst[c] = make_uint4(o1[4 * c], o1[4 * c + 1], o1[4 * c + 2], o1[4 * c + 3]);
+            dst[4 + c] = make_uint4(o2[4 * c], o2[4 * c + 1], o2[4 * c + 2], o2[4 * c + 3]);
+          }
+        } else {
+          const int64_t sl = ea.slot[row];
+          if (sl >= 0) {
+            uint8_t* page = ea.kv_layer + (size_t)(sl / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
+            const int tok = (int)(sl % CBX_BLOCK_SIZE);
+            const int sw = which == 1 ? (tok & 7) : 0;   // K chunks are XOR-swizzled, V chunks are not
+            uint4* dst = reinterpret_cast<uint4*>(page + (which == 2 ? 32768 : 0) + h * 2048 + tok * 128);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              dst[c ^ sw] = make_uint4(o1[4 * c], o1[4 * c + 1], o1[4 * c + 2], o1[4 * c + 3]);
+              dst[(4 + c) ^ sw] = make_uint4(o2[4 * c], o2[4 * c + 1], o2[4 * c + 2], o2[4 * c + 3]);
+            }
+          }
+        }
+      }
+    } else {
 #pragma unroll 1
     for (int cb = 0; cb < BN / 32; ++cb) {
       uint32_t r[32];
@@ -121,6 +201,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
             dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
           }
+        } else if (EPI == 3) {
+          // residual stream in place: res = bf16(bf16(acc) + res)   (N % 32 == 0)
+          uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + col);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint4 q = dst[i];
+            const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+            uint32_t ow[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              ow[j] = pack_bf16(round_bf16(__uint_as_float(r[8 * i + 2 * j])) + bf_lo(qw[j]),
+                                round_bf16(__uint_as_float(r[8 * i + 2 * j + 1])) + bf_hi(qw[j]));
+            dst[i] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+          }
         } else {
           if (col + 32 <= N) {
             uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + col);
@@ -137,6 +231,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           }
         }
       }
+    }
     }
     tc_fence_before();
   }
@@ -196,7 +291,8 @@ namespace cbx {
 int init_gemm() {
   static bool done = false;
   if (done) return 0;
-  if (set_attr<64, 0>() || set_attr<64, 1>() || set_attr<128, 0>() || set_attr<128, 1>()) return -1;
+  if (set_attr<64, 0>() || set_attr<64, 1>() || set_attr<128, 0>() || set_attr<128, 1>() || set_attr<64, 2>() ||
+      set_attr<64, 3>() || set_attr<128, 3>()) return -1;
   CBX_REQUIRE(get_encode() != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   done = true;
   return 0;
@@ -204,15 +300,18 @@ int init_gemm() {
 }  // namespace cbx
 namespace {
 template <int BN, int EPI>
-int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s) {
+int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s,
+           const EpiArgs& ea = EpiArgs()) {
   using C = Cfg<BN>;
   if (cbx::init_gemm()) return -1;
   CUtensorMap ma, mb;
   if (make_map(&ma, x, M, K, BM)) return -1;
   if (make_map(&mb, W, N, K, BN)) return -1;
   dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
-  gemm_tc_kernel<BN, EPI><<<grid, kThreads, C::kSmem, s>>>(ma, mb, (bf16*)y, M, N, K, ldy);
-  CBX_CHECK_LAUNCH("gemm_tc");
+  cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI>, grid, dim3(kThreads), C::kSmem, s, ma, mb, (bf16*)y, M, N, K,
+                             ldy, ea);
+  CBX_REQUIRE(e == cudaSuccess, "gemm_tc launch failed: %s", cudaGetErrorString(e));
+  count_launch();
   return 0;
 }
 }  // namespace
@@ -229,6 +328,18 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
   const bool narrow = (int64_t)m_tiles * ((N + 127) / 128) < 148;
   if (epilogue == 1) return narrow ? launch<64, 1>(x, W, y, M, N, K, ldy, s) : launch<128, 1>(x, W, y, M, N, K, ldy, s);
   return narrow ? launch<64, 0>(x, W, y, M, N, K, ldy, s) : launch<128, 0>(x, W, y, M, N, K, ldy, s);
+}
+// EPI 2: y = qkv buffer [M, 3072]; q rotated into its first 1024 columns, k/v into the KV pages.
+int gemm_qkv_rope(const void* h, const void* Wqkv, void* qkv, const void* cos_sin, const int32_t* pos,
+                  const int64_t* slot, void* kv_layer, int M, cudaStream_t s) {
+  EpiArgs ea = {(const bf16*)cos_sin, pos, slot, (uint8_t*)kv_layer};
+  return launch<64, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
+}
+// EPI 3: res[M, N] = bf16(bf16(x·W^T) + res), N % 32 == 0.
+int gemm_residual(const void* x, const void* W, void* res, int M, int N, int K, cudaStream_t s) {
+  CBX_REQUIRE(N % 128 == 0 && K % BK == 0, "gemm_residual: bad shape N=%d K=%d", N, K);
+  const bool narrow = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
+  return narrow ? launch<64, 3>(x, W, res, M, N, K, N, s) : launch<128, 3>(x, W, res, M, N, K, N, s);
 }
 int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
 }  // namespace cbx

@@ -1,57 +1,138 @@
-// k_gemv.cu — weight-streaming GEMV for T <= 4 rows (the b=1 / b=2 CFG-pair decode case).
+// k_gemv.cu — fused weight-streaming GEMV family for T <= 4 rows (the b=1 / b=2 CFG-pair decode
+// regime), one kernel per projection of a Llama layer:
 //
-// y[T,N] = x[T,K] · W[N,K]^T.  Replaces the cuBLAS GEMM vLLM would launch for
-// llama.py:117-120,221,225 at tiny batch.  HBM-bound: every weight byte is read once with
-// 128-bit L1-bypassing loads, two output features per warp in flight with the next K-segment
-// prefetched into registers; x (T*K bf16, <= 32 KB) is staged once per CTA in shared memory.
+//   QKV   : RMSNorm(res)·ln1 -> x·Wqkv^T -> RoPE -> q to the qkv buffer, k/v into the KV page
+//           (vllm llama.py:316-320,221-223 + reshape_and_cache_flash, flash_attn.py:850-874)
+//   O     : attn·Wo^T, epilogue res = bf16(bf16(y) + res)            (llama.py:225,323-326)
+//   GU    : RMSNorm(res)·ln2 -> x·Wgu^T -> SiLU(gate)·up            (llama.py:117-119)
+//   DOWN  : act·Wd^T (K = 4096, split over 4 warps), epilogue res += (llama.py:120,316)
+//   HEAD  : RMSNorm(res)·norm -> x·Whead^T -> bf16 logits           (llama.py:430, t3.py:729-730)
+//
+// HBM-bound: every weight byte is read exactly once with 128-bit L1-bypassing loads; a warp owns
+// two output features (the RoPE pair i / i+32, the gate/up pair, or two adjacent rows) over a
+// 1024-element K segment = 4 KB in flight per warp, all of it issued BEFORE griddepcontrol.wait
+// so the weight stream of kernel n+1 overlaps the tail of kernel n (programmatic dependent
+// launch).  The T x 1024 activation rows are normalised redundantly by every CTA (2-8 KB from
+// L2) — cheaper than a separate launch.
 #include "common.cuh"
 
 using namespace cbx;
 
 namespace {
-constexpr int kWarps = 8;
+enum { PRO_COPY = 0, PRO_NORM = 1 };
+enum { EPI_STORE = 0, EPI_SILU = 1, EPI_ROPE = 2, EPI_RES = 3 };
+
+struct GemvArgs {
+  const bf16* x;          // PRO_COPY: [T, K] input rows;  PRO_NORM: residual stream [T, 1024]
+  const bf16* ln_w;       // PRO_NORM: RMSNorm weight [1024]
+  const bf16* W;          // [N, K]
+  bf16* y;                // STORE/SILU: out [T, ldy];  RES: residual stream [T, 1024];  ROPE: qkv [T, 3072]
+  const bf16* cos_sin;    // ROPE: [max_pos, 64] = cos(32) | sin(32)
+  const int32_t* pos;     // ROPE: [T]
+  const int64_t* slot;    // ROPE: [T] (-1 = do not cache)
+  uint8_t* kv_layer;      // ROPE: this layer's pages
+  int T, N, ldy;
+  float eps;
+};
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
   f[0] = bf_lo(v.x); f[1] = bf_hi(v.x); f[2] = bf_lo(v.y); f[3] = bf_hi(v.y);
   f[4] = bf_lo(v.z); f[5] = bf_hi(v.z); f[6] = bf_lo(v.w); f[7] = bf_hi(v.w);
 }
 
-// TT = padded row count (1,2,4); SEGS = K / 1024; EPI: 0 store, 1 SiLU(gate)*up (packed W).
-template <int TT, int SEGS, int EPI>
-__global__ void __launch_bounds__(kWarps * 32, 2) gemv_kernel(const bf16* __restrict__ x,
-                                                              const bf16* __restrict__ W, bf16* __restrict__ y,
-                                                              int T, int N, int ldy) {
-  constexpr int K = SEGS * 1024;
+template <int EPI>
+__device__ __forceinline__ void item_rows(int item, int& ra, int& rb) {
+  if (EPI == EPI_SILU)      { ra = (item >> 4) * 32 + (item & 15); rb = ra + 16; }   // packed gate/up
+  else if (EPI == EPI_ROPE) { ra = (item >> 5) * 64 + (item & 31); rb = ra + 32; }   // rotation partners
+  else                      { ra = 2 * item; rb = ra + 1; }
+}
+
+// TT = padded row count (1,2,4); KSEG = K / 1024 (1 or 4); NW = warps per CTA.
+template <int TT, int KSEG, int PRO, int EPI, int NW>
+__global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a) {
+  constexpr int K = KSEG * 1024;
+  constexpr int IPC = NW / KSEG;                      // items per CTA per round
+  static_assert(NW % KSEG == 0, "warps must cover whole K-segment groups");
+  static_assert(PRO == PRO_COPY || KSEG == 1, "norm prologue is over hidden = 1024");
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  uint4* xs = reinterpret_cast<uint4*>(smem_raw);            // [TT][K/8]
-  for (int i = threadIdx.x; i < TT * (K / 8); i += blockDim.x) {
-    const int t = i / (K / 8);
-    xs[i] = t < T ? reinterpret_cast<const uint4*>(x)[(size_t)t * (K / 8) + (i - t * (K / 8))] : make_uint4(0, 0, 0, 0);
+  uint4* xs = reinterpret_cast<uint4*>(smem_raw);     // [TT][K/8] bf16x8
+  float* part = reinterpret_cast<float*>(smem_raw + TT * K * 2);   // [NW][2*TT] (KSEG > 1)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kseg = warp % KSEG;
+  const int n_items = a.N / 2;
+  const int T = a.T;
+
+  pdl_trigger();
+  // ---- weight prefetch of this warp's first item: independent of the previous kernel
+  int item = blockIdx.x * IPC + warp / KSEG;
+  const int stride = gridDim.x * IPC;
+  uint4 cur[2][4];
+  if (item < n_items) {
+    int ra, rb;
+    item_rows<EPI>(item, ra, rb);
+    const uint4* wa = reinterpret_cast<const uint4*>(a.W + (size_t)ra * K + kseg * 1024) + lane;
+    const uint4* wb = reinterpret_cast<const uint4*>(a.W + (size_t)rb * K + kseg * 1024) + lane;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
+  }
+  pdl_wait();
+
+  // ---- prologue: activation rows -> shared memory (bf16)
+  if (PRO == PRO_NORM) {
+    if (warp < TT) {
+      uint4 o[4] = {};
+      if (warp < T) {
+        const uint4* xr = reinterpret_cast<const uint4*>(a.x + (size_t)warp * 1024);
+        const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
+        float f[4][8];
+        float ss = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          unpack8(xr[lane + 32 * i], f[i]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ss += f[i][e] * f[i][e];
+        }
+        ss = warp_sum(ss);
+        const float rstd = rsqrtf(ss * (1.0f / 1024.f) + a.eps);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float w[8];
+          unpack8(wr[lane + 32 * i], w);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[i][e] = round_bf16(f[i][e] * rstd) * w[e];
+          o[i] = make_uint4(pack_bf16(f[i][0], f[i][1]), pack_bf16(f[i][2], f[i][3]), pack_bf16(f[i][4], f[i][5]),
+                            pack_bf16(f[i][6], f[i][7]));
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xs[warp * 128 + lane + 32 * i] = o[i];
+    }
+  } else {
+    for (int i = threadIdx.x; i < TT * (K / 8); i += NW * 32) {
+      const int t = i / (K / 8);
+      xs[i] = t < T ? reinterpret_cast<const uint4*>(a.x)[i] : make_uint4(0, 0, 0, 0);
+    }
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_pairs = N / 2;
-  for (int pr = blockIdx.x * kWarps + warp; pr < n_pairs; pr += gridDim.x * kWarps) {
-    int ra, rb;
-    if (EPI == 1) { ra = (pr >> 4) * 32 + (pr & 15); rb = ra + 16; }
-    else          { ra = 2 * pr; rb = ra + 1; }
-    const uint4* wa = reinterpret_cast<const uint4*>(W + (size_t)ra * K) + lane;
-    const uint4* wb = reinterpret_cast<const uint4*>(W + (size_t)rb * K) + lane;
+
+  // ---- main loop over this warp's items (CTA-uniform trip count when KSEG > 1)
+  for (int base = blockIdx.x * IPC; base < n_items; base += stride) {
+    item = base + warp / KSEG;
+    const bool valid = item < n_items;
+    uint4 nxt[2][4];
+    const int nitem = item + stride;
+    if (nitem < n_items) {
+      int ra, rb;
+      item_rows<EPI>(nitem, ra, rb);
+      const uint4* wa = reinterpret_cast<const uint4*>(a.W + (size_t)ra * K + kseg * 1024) + lane;
+      const uint4* wb = reinterpret_cast<const uint4*>(a.W + (size_t)rb * K + kseg * 1024) + lane;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { nxt[0][j] = ld_stream(wa + j * 32); nxt[1][j] = ld_stream(wb + j * 32); }
+    }
     float acc[2][TT];
 #pragma unroll
     for (int t = 0; t < TT; ++t) acc[0][t] = acc[1][t] = 0.f;
-    uint4 cur[2][4], nxt[2][4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
-#pragma unroll
-    for (int sg = 0; sg < SEGS; ++sg) {
-      if (sg + 1 < SEGS) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          nxt[0][j] = ld_stream(wa + (sg + 1) * 128 + j * 32);
-          nxt[1][j] = ld_stream(wb + (sg + 1) * 128 + j * 32);
-        }
-      }
+    if (valid) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float fa[8], fb[8];
@@ -60,7 +141,7 @@ __global__ void __launch_bounds__(kWarps * 32, 2) gemv_kernel(const bf16* __rest
 #pragma unroll
         for (int t = 0; t < TT; ++t) {
           float fx[8];
-          unpack8(xs[t * (K / 8) + sg * 128 + j * 32 + lane], fx);
+          unpack8(xs[t * (K / 8) + kseg * 128 + j * 32 + lane], fx);
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
             acc[0][t] = fmaf(fa[e], fx[e], acc[0][t]);
@@ -68,60 +149,153 @@ __global__ void __launch_bounds__(kWarps * 32, 2) gemv_kernel(const bf16* __rest
           }
         }
       }
-      if (sg + 1 < SEGS) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
-      }
     }
 #pragma unroll
     for (int t = 0; t < TT; ++t) { acc[0][t] = warp_sum(acc[0][t]); acc[1][t] = warp_sum(acc[1][t]); }
-    if (lane == 0) {
+    if (KSEG > 1) {                                     // combine the K segments of one item
+      if (lane == 0) {
 #pragma unroll
-      for (int t = 0; t < TT; ++t) {
-        if (t < T) {
-          if (EPI == 1) {
-            const float g = round_bf16(acc[0][t]), u = round_bf16(acc[1][t]);
-            y[(size_t)t * ldy + pr] = __float2bfloat16_rn(g / (1.f + __expf(-g)) * u);
+        for (int t = 0; t < TT; ++t) { part[warp * 2 * TT + t] = acc[0][t]; part[warp * 2 * TT + TT + t] = acc[1][t]; }
+      }
+      __syncthreads();
+      if (kseg == 0) {
+#pragma unroll
+        for (int t = 0; t < TT; ++t) {
+          float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+          for (int q = 0; q < KSEG; ++q) { s0 += part[(warp + q) * 2 * TT + t]; s1 += part[(warp + q) * 2 * TT + TT + t]; }
+          acc[0][t] = s0; acc[1][t] = s1;
+        }
+      }
+      __syncthreads();
+    }
+    // ---- epilogue: lane t finishes row t
+    if (valid && kseg == 0) {
+      int ra, rb;
+      item_rows<EPI>(item, ra, rb);
+      float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+      for (int t = 0; t < TT; ++t) if (lane == t) { v0 = acc[0][t]; v1 = acc[1][t]; }
+      if (lane < T) {
+        const int t = lane;
+        if (EPI == EPI_STORE) {
+          *reinterpret_cast<uint32_t*>(a.y + (size_t)t * a.ldy + ra) = pack_bf16(v0, v1);
+        } else if (EPI == EPI_SILU) {
+          const float g = round_bf16(v0), u = round_bf16(v1);
+          a.y[(size_t)t * a.ldy + item] = __float2bfloat16_rn(g / (1.f + __expf(-g)) * u);
+        } else if (EPI == EPI_RES) {
+          uint32_t* rp = reinterpret_cast<uint32_t*>(a.y + (size_t)t * 1024 + ra);
+          const uint32_t r = *rp;
+          *rp = pack_bf16(round_bf16(v0) + bf_lo(r), round_bf16(v1) + bf_hi(r));
+        } else {                                        // EPI_ROPE
+          const int head48 = item >> 5, i = item & 31, which = head48 >> 4, h = head48 & 15;
+          float o1 = round_bf16(v0), o2 = round_bf16(v1);
+          if (which < 2) {
+            const int p = a.pos[t];
+            const float c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
+            const float s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
+            const float x1 = o1, x2 = o2;
+            o1 = x1 * c - x2 * s;
+            o2 = x2 * c + x1 * s;
+          }
+          const bf16 b1 = __float2bfloat16_rn(o1), b2 = __float2bfloat16_rn(o2);
+          if (which == 0) {
+            bf16* q = a.y + (size_t)t * 3072 + h * 64;
+            q[i] = b1; q[i + 32] = b2;
           } else {
-            *reinterpret_cast<uint32_t*>(y + (size_t)t * ldy + ra) = pack_bf16(acc[0][t], acc[1][t]);
+            const int64_t sl = a.slot[t];
+            if (sl >= 0) {
+              uint8_t* page = a.kv_layer + (size_t)(sl / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
+              const int tok = (int)(sl % CBX_BLOCK_SIZE);
+              if (which == 1) {                         // K: 16-byte chunks XOR-swizzled by tok & 7
+                uint8_t* kt = page + h * 2048 + tok * 128;
+                const int c1 = (i >> 3) ^ (tok & 7), c2 = ((i + 32) >> 3) ^ (tok & 7);
+                *reinterpret_cast<bf16*>(kt + c1 * 16 + (i & 7) * 2) = b1;
+                *reinterpret_cast<bf16*>(kt + c2 * 16 + (i & 7) * 2) = b2;
+              } else {
+                bf16* vt = reinterpret_cast<bf16*>(page + 32768 + h * 2048 + tok * 128);
+                vt[i] = b1; vt[i + 32] = b2;
+              }
+            }
           }
         }
       }
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
   }
 }
 
-template <int TT, int SEGS, int EPI>
-int launch(const void* x, const void* W, void* y, int T, int N, int ldy, cudaStream_t s) {
-  const int smem = TT * SEGS * 1024 * 2;
-  static_assert(TT * SEGS * 1024 * 2 <= 48 * 1024, "x tile must fit the default dynamic smem limit");
-  int grid = (N / 2 + kWarps - 1) / kWarps;
-  if (grid > 296) grid = 296;
-  gemv_kernel<TT, SEGS, EPI><<<grid, kWarps * 32, smem, s>>>((const bf16*)x, (const bf16*)W, (bf16*)y, T, N, ldy);
-  CBX_CHECK_LAUNCH("gemv");
+template <int TT, int KSEG, int PRO, int EPI, int NW>
+int launch(const GemvArgs& a, int grid, cudaStream_t s) {
+  constexpr int smem = TT * KSEG * 1024 * 2 + (KSEG > 1 ? NW * 2 * TT * 4 : 0);
+  static_assert(smem <= 48 * 1024, "x tile must fit the default dynamic smem limit");
+  cudaError_t e = launch_pdl(gemv_fused_kernel<TT, KSEG, PRO, EPI, NW>, dim3(grid), dim3(NW * 32), smem, s, a);
+  if (e != cudaSuccess) { set_error("gemv launch failed: %s", cudaGetErrorString(e)); return -2; }
+  count_launch();
   return 0;
 }
 
-template <int SEGS, int EPI>
-int dispatch_t(const void* x, const void* W, void* y, int T, int N, int ldy, cudaStream_t s) {
-  if (T == 1) return launch<1, SEGS, EPI>(x, W, y, T, N, ldy, s);
-  if (T == 2) return launch<2, SEGS, EPI>(x, W, y, T, N, ldy, s);
-  return launch<4, SEGS, EPI>(x, W, y, T, N, ldy, s);
+template <int KSEG, int PRO, int EPI, int NW>
+int dispatch_t(const GemvArgs& a, int grid, cudaStream_t s) {
+  if (a.T == 1) return launch<1, KSEG, PRO, EPI, NW>(a, grid, s);
+  if (a.T == 2) return launch<2, KSEG, PRO, EPI, NW>(a, grid, s);
+  return launch<4, KSEG, PRO, EPI, NW>(a, grid, s);
+}
+
+// one warp per item when that needs <= one CTA per SM, else 148 CTAs looping
+inline int grid_for(int n_items, int items_per_cta) {
+  const int g = (n_items + items_per_cta - 1) / items_per_cta;
+  return g < 148 ? g : 148;
 }
 }  // namespace
 
 namespace cbx {
-// T <= 4, K in {1024, 4096}, N even (N % 32 == 0 for the SiLU epilogue).
-int gemv_bf16(const void* x, const void* W, void* y, int T, int N, int K, int ldy, int epilogue,
-              cudaStream_t s) {
+// Plain y = x·W^T (epilogue 0) or SiLU(gate)·up (epilogue 1).  T <= 4, K in {1024, 4096}.
+int gemv_bf16(const void* x, const void* W, void* y, int T, int N, int K, int ldy, int epilogue, cudaStream_t s) {
   CBX_REQUIRE(T >= 1 && T <= 4, "gemv: T=%d not in [1,4]", T);
   CBX_REQUIRE(K == 1024 || K == 4096, "gemv: K=%d unsupported", K);
   CBX_REQUIRE(N % 2 == 0 && (epilogue == 0 || N % 32 == 0), "gemv: N=%d unsupported", N);
+  GemvArgs a = {};
+  a.x = (const bf16*)x; a.W = (const bf16*)W; a.y = (bf16*)y; a.T = T; a.N = N; a.ldy = ldy;
   if (K == 1024) {
-    if (epilogue == 1) return dispatch_t<1, 1>(x, W, y, T, N, ldy, s);
-    return dispatch_t<1, 0>(x, W, y, T, N, ldy, s);
+    if (epilogue == 1) return dispatch_t<1, PRO_COPY, EPI_SILU, 14>(a, grid_for(N / 2, 14), s);
+    if (N <= 2048) return dispatch_t<1, PRO_COPY, EPI_STORE, 4>(a, grid_for(N / 2, 4), s);
+    return dispatch_t<1, PRO_COPY, EPI_STORE, 14>(a, grid_for(N / 2, 14), s);
   }
   CBX_REQUIRE(epilogue == 0, "gemv: SiLU epilogue only for K=1024");
-  return dispatch_t<4, 0>(x, W, y, T, N, ldy, s);
+  return dispatch_t<4, PRO_COPY, EPI_STORE, 16>(a, grid_for(N / 2, 4), s);
+}
+
+// RMSNorm(res)·ln_w -> ·Wqkv^T -> RoPE -> q into qkv[:, :1024], k/v into the page of slot[t].
+int gemv_qkv_rope(const void* res, const void* ln_w, const void* Wqkv, const void* cos_sin, const int32_t* pos,
+                  const int64_t* slot, void* qkv, void* kv_layer, int T, float eps, cudaStream_t s) {
+  GemvArgs a = {};
+  a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = (const bf16*)Wqkv; a.y = (bf16*)qkv;
+  a.cos_sin = (const bf16*)cos_sin; a.pos = pos; a.slot = slot; a.kv_layer = (uint8_t*)kv_layer;
+  a.T = T; a.N = 3072; a.ldy = 3072; a.eps = eps;
+  return dispatch_t<1, PRO_NORM, EPI_ROPE, 12>(a, grid_for(1536, 12), s);
+}
+// res = bf16(bf16(x·W^T) + res), N = 1024, K in {1024, 4096}.
+int gemv_residual(const void* x, const void* W, void* res, int T, int K, cudaStream_t s) {
+  GemvArgs a = {};
+  a.x = (const bf16*)x; a.W = (const bf16*)W; a.y = (bf16*)res; a.T = T; a.N = 1024; a.ldy = 1024;
+  if (K == 1024) return dispatch_t<1, PRO_COPY, EPI_RES, 4>(a, grid_for(512, 4), s);
+  return dispatch_t<4, PRO_COPY, EPI_RES, 16>(a, grid_for(512, 4), s);
+}
+// act = SiLU(g)·u of RMSNorm(res)·ln_w · Wgu^T (packed gate/up), act [T, 4096].
+int gemv_norm_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, int T, float eps, cudaStream_t s) {
+  GemvArgs a = {};
+  a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = (const bf16*)Wgu; a.y = (bf16*)act;
+  a.T = T; a.N = 8192; a.ldy = 4096; a.eps = eps;
+  return dispatch_t<1, PRO_NORM, EPI_SILU, 14>(a, grid_for(4096, 14), s);
+}
+// logits = RMSNorm(res)·norm_w · Whead^T, N even.
+int gemv_norm_head(const void* res, const void* norm_w, const void* Whead, void* logits, int T, int N, int ldy,
+                   float eps, cudaStream_t s) {
+  GemvArgs a = {};
+  a.x = (const bf16*)res; a.ln_w = (const bf16*)norm_w; a.W = (const bf16*)Whead; a.y = (bf16*)logits;
+  a.T = T; a.N = N; a.ldy = ldy; a.eps = eps;
+  return dispatch_t<1, PRO_NORM, EPI_STORE, 14>(a, grid_for(N / 2, 14), s);
 }
 }  // namespace cbx

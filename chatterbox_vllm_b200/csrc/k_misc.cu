@@ -2,6 +2,7 @@
 //   slot mapping, decode_prepare, prefill_embed, (add+)RMSNorm, RoPE + KV append,
 //   gate/up weight packing.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <deque>
 
@@ -18,6 +19,11 @@ void set_error(const char* fmt, ...) {
 }
 int count_launch() { ++g_launches; return 0; }
 int64_t launches() { return g_launches; }
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CBX_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
 }  // namespace cbx
 using namespace cbx;
 
@@ -83,6 +89,8 @@ __global__ void __launch_bounds__(128) decode_prepare_kernel(
     int64_t* __restrict__ slot, int32_t* __restrict__ kv_len, int32_t* __restrict__ row_seq,
     int32_t* __restrict__ head_rows, int B) {
   const int r = blockIdx.x, b = r % B;
+  pdl_trigger();
+  pdl_wait();
   const int tok = last_tok[b];
   x[(size_t)r * 128 + threadIdx.x] = speech_emb[(size_t)tok * 128 + threadIdx.x];
   if (threadIdx.x == 0) {
@@ -102,9 +110,10 @@ int launch_decode_prepare(const void* speech_emb, const int32_t* last_tok, const
                           const int32_t* seq_len, const int32_t* bt, int bt_stride, void* x, int32_t* pos,
                           int64_t* slot, int32_t* kv_len, int32_t* row_seq, int32_t* head_rows, int B,
                           cudaStream_t s) {
-  decode_prepare_kernel<<<2 * B, 128, 0, s>>>((const uint4*)speech_emb, last_tok, finished, seq_len, bt,
-                                               bt_stride, (uint4*)x, pos, slot, kv_len, row_seq, head_rows, B);
-  CBX_CHECK_LAUNCH("decode_prepare");
+  cudaError_t e = launch_pdl(decode_prepare_kernel, dim3(2 * B), dim3(128), 0, s, (const uint4*)speech_emb, last_tok,
+                             finished, seq_len, bt, bt_stride, (uint4*)x, pos, slot, kv_len, row_seq, head_rows, B);
+  CBX_REQUIRE(e == cudaSuccess, "decode_prepare launch failed: %s", cudaGetErrorString(e));
+  count_launch();
   return 0;
 }
 }  // namespace cbx
@@ -159,6 +168,9 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* __restrict__ 
                                                       const uint4* __restrict__ w, uint4* __restrict__ out,
                                                       float eps) {
   const int r = blockIdx.x, t = threadIdx.x;
+  pdl_trigger();
+  const uint4 wv = w[t];                               // weights: independent of the previous kernel
+  pdl_wait();
   uint4 v = x[(size_t)r * 128 + t];
   float f[8] = {bf_lo(v.x), bf_hi(v.x), bf_lo(v.y), bf_hi(v.y), bf_lo(v.z), bf_hi(v.z), bf_lo(v.w), bf_hi(v.w)};
   if (kAdd) {
@@ -177,7 +189,6 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* __restrict__ 
   if ((t & 31) == 0) part[t >> 5] = ss;
   __syncthreads();
   const float rstd = rsqrtf((part[0] + part[1] + part[2] + part[3]) * (1.0f / CBX_HIDDEN) + eps);
-  uint4 wv = w[t];
   float wf[8] = {bf_lo(wv.x), bf_hi(wv.x), bf_lo(wv.y), bf_hi(wv.y), bf_lo(wv.z), bf_hi(wv.z), bf_lo(wv.w), bf_hi(wv.w)};
 #pragma unroll
   for (int i = 0; i < 8; ++i) f[i] = round_bf16(f[i] * rstd) * wf[i];
@@ -187,13 +198,15 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* __restrict__ 
 extern "C" int cbx_rmsnorm(const void* x, void* residual, const void* w, void* out, int T, float eps,
                            void* stream) {
   if (T <= 0) return 0;
+  cudaError_t e;
   if (residual)
-    rmsnorm_kernel<true><<<T, 128, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)residual,
-                                                               (const uint4*)w, (uint4*)out, eps);
+    e = launch_pdl(rmsnorm_kernel<true>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)x,
+                   (uint4*)residual, (const uint4*)w, (uint4*)out, eps);
   else
-    rmsnorm_kernel<false><<<T, 128, 0, (cudaStream_t)stream>>>((const uint4*)x, nullptr, (const uint4*)w,
-                                                                (uint4*)out, eps);
-  CBX_CHECK_LAUNCH("rmsnorm");
+    e = launch_pdl(rmsnorm_kernel<false>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)x,
+                   (uint4*)nullptr, (const uint4*)w, (uint4*)out, eps);
+  CBX_REQUIRE(e == cudaSuccess, "rmsnorm launch failed: %s", cudaGetErrorString(e));
+  count_launch();
   return 0;
 }
 

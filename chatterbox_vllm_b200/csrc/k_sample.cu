@@ -21,6 +21,14 @@ constexpr int kThreads = 256;
 constexpr int kPer = (V + kThreads - 1) / kThreads;     // 33 contiguous ids per thread
 constexpr float kSamplingEps = 1e-5f;
 constexpr int kSampleSmem = (2 * V + 4) * sizeof(float);
+}  // namespace
+namespace cbx {
+struct NextStep {             // optional fused "decode_prepare" for the following step (engine only)
+  const uint4* speech_emb; uint4* res; int32_t* pos; int64_t* slot; int32_t* kv_len; int32_t* row_seq;
+  const int32_t* bt; int bt_stride;
+};
+}  // namespace cbx
+namespace {
 
 __device__ __forceinline__ uint32_t fkey(float f) {
   const uint32_t u = __float_as_uint(f);
@@ -73,44 +81,151 @@ __device__ __forceinline__ uint32_t philox_word0(uint32_t c0, uint32_t c1, uint3
   return c0;
 }
 
-// minimal key k in [0, 2^32) with F(k) < target, F(k) = sum of weight(i) over live ids with key_i > k
+// Minimal key k in [0, 2^32) with F(k) < target, where F(k) = total weight of live ids whose key
+// is > k  (== the key of the pivot element at which the descending cumulative weight reaches
+// target).  MSB-first 8-bit radix select: 4 histogram passes instead of a 32-step bisection.
+// Weights are integers — 1 for top-k, e_i·2^40 for top-p — so the shared-memory atomics commute and
+// the result is bit-reproducible.  Each thread owns a contiguous id range and run-length-merges
+// equal digits before touching a bin (the top byte of a logit key is almost constant).
+struct Radix {
+  uint32_t lo[256], hi[256];          // 64-bit bins as two words: 32-bit shared atomics are native, 64-bit ones CAS-loop
+  unsigned long long above, target;
+  int digit;
+};
+__device__ __forceinline__ void bin_add(Radix& rx, int d, unsigned long long w) {
+  const uint32_t wl = (uint32_t)w, wh = (uint32_t)(w >> 32);
+  const uint32_t old = atomicAdd(&rx.lo[d], wl);
+  const uint32_t carry = (old + wl < old) ? 1u : 0u;   // exactly one adder sees each wrap
+  if (wh | carry) atomicAdd(&rx.hi[d], wh + carry);
+}
+__device__ __forceinline__ unsigned long long quant40(float e) { return __float2ull_rz(e * 1099511627776.f); }
+
+// kCount: weights 1 and `target` given; else weights quant40(e[i]) and target = top_p · total.
 template <bool kCount>
-__device__ uint32_t bisect(const float* l, const float* e, int i0, int i1, float target, Red& red) {
-  uint64_t lo = 0, hi = 0xffffffffull;
-  while (lo < hi) {
-    const uint32_t mid = (uint32_t)((lo + hi) >> 1);
-    float s = 0.f;
+__device__ uint32_t radix_select(const float* l, const float* e, int i0, int i1, unsigned long long target_in,
+                                 float top_p, Radix& rx) {
+  uint32_t prefix = 0;
+  if (threadIdx.x == 0) { rx.above = 0; rx.target = target_in; }
+#pragma unroll 1
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 24 - 8 * pass;
+    rx.lo[threadIdx.x] = 0; rx.hi[threadIdx.x] = 0;     // kThreads == 256 bins
+    __syncthreads();
+    int run_d = -1;
+    unsigned long long run_w = 0;
     for (int i = i0; i < i1; ++i) {
       const float li = l[i];
-      if (fkey(li) > mid && li != -INFINITY) s += kCount ? 1.f : e[i];
+      if (li == -INFINITY) continue;
+      const uint32_t key = fkey(li);
+      if (pass > 0 && (key >> (shift + 8)) != prefix) continue;
+      const int d = (key >> shift) & 255;
+      const unsigned long long w = kCount ? 1ull : quant40(e[i]);
+      if (d != run_d) {
+        if (run_w) bin_add(rx, run_d, run_w);
+        run_d = d; run_w = 0;
+      }
+      run_w += w;
     }
-    s = block_sum(s, red);
-    if (s < target) hi = mid; else lo = (uint64_t)mid + 1;
+    if (run_w) bin_add(rx, run_d, run_w);
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      // lane owns bins 255-8*lane .. 248-8*lane (descending digits)
+      const int lane = threadIdx.x;
+      unsigned long long b8[8], tot = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int d = 255 - 8 * lane - j;
+        b8[j] = ((unsigned long long)rx.hi[d] << 32) | rx.lo[d];
+        tot += b8[j];
+      }
+      unsigned long long incl = tot;                   // inclusive scan over lanes
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      unsigned long long target = rx.target;
+      if (!kCount && pass == 0) {                      // total weight is known only now
+        const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
+        target = (unsigned long long)((double)top_p * (double)total);
+        if (target < 1) target = 1;
+      }
+      unsigned long long running = rx.above + incl - tot;
+      int found = -1;
+      unsigned long long found_above = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (found < 0 && running < target && running + b8[j] >= target) { found = 255 - 8 * lane - j; found_above = running; }
+        running += b8[j];
+      }
+      const unsigned ball = __ballot_sync(0xffffffffu, found >= 0);
+      __syncwarp();
+      if (ball == 0) {                                 // fewer live weights than the target: keep everything
+        if (lane == 0) { rx.digit = 0; rx.above = running; rx.target = target; }
+      } else if (lane == __ffs(ball) - 1) {
+        rx.digit = found; rx.above = found_above; rx.target = target;
+      }
+    }
+    __syncthreads();
+    prefix = (prefix << 8) | (uint32_t)rx.digit;
+    __syncthreads();
   }
-  return (uint32_t)lo;
+  return prefix;
 }
 
 __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __restrict__ logits,
-                                                              cbx_sampler_state st, int B) {
+                                                              cbx_sampler_state st, int B, const NextStep nx) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   float* l = reinterpret_cast<float*>(smem_raw);          // [V] working logits
   float* e = l + V + 2;                                   // [V] exp(l - max)
   __shared__ Red red;
+  __shared__ Radix rx;
   __shared__ int s_scan[kThreads];
   const int b = blockIdx.x, tid = threadIdx.x;
+  pdl_trigger();
+  pdl_wait();
   if (st.finished[b]) return;
+  const int n_prev = st.n_out[b];
+  const int len_c = st.seq_len[b], len_u = st.seq_len[B + b];
 
   const bf16* lc = logits + (size_t)b * CBX_LOGITS_LD;
   const bf16* lu = logits + (size_t)(B + b) * CBX_LOGITS_LD;
   const uint32_t* seen = st.seen + (size_t)b * CBX_SEEN_WORDS;
   const float rep = st.rep_pen[b], cfg = st.cfg_scale;
   const float inv_rep = 1.0f / rep;
-  // ---- CFG merge (bf16 op-by-op) + repetition penalty; strided (coalesced) pass
-  for (int i = tid; i < V; i += kThreads) {
-    const float c = __bfloat162float(lc[i]), u = __bfloat162float(lu[i]);
-    float v = round_bf16(c + round_bf16(cfg * round_bf16(c - u)));
-    if ((seen[i >> 5] >> (i & 31)) & 1u) v = v * (v > 0.f ? inv_rep : rep);
-    l[i] = v;
+  // ---- CFG merge (bf16 op-by-op) + repetition penalty: 128-bit loads, all issued before first use
+  {
+    constexpr int kChunks = V / 8;                       // 1024 full chunks + 2 tail ids
+    uint4 vc[4], vu[4];
+    uint32_t sb[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int c = tid + k * kThreads;
+      vc[k] = reinterpret_cast<const uint4*>(lc)[c];
+      vu[k] = reinterpret_cast<const uint4*>(lu)[c];
+      sb[k] = (seen[c >> 2] >> ((c & 3) * 8)) & 0xffu;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int c = tid + k * kThreads;
+      const uint32_t cw[4] = {vc[k].x, vc[k].y, vc[k].z, vc[k].w}, uw[4] = {vu[k].x, vu[k].y, vu[k].z, vu[k].w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float cc = (j & 1) ? bf_hi(cw[j >> 1]) : bf_lo(cw[j >> 1]);
+        const float uu = (j & 1) ? bf_hi(uw[j >> 1]) : bf_lo(uw[j >> 1]);
+        float v = round_bf16(cc + round_bf16(cfg * round_bf16(cc - uu)));
+        if ((sb[k] >> j) & 1u) v = v * (v > 0.f ? inv_rep : rep);
+        l[c * 8 + j] = v;
+      }
+    }
+    static_assert(kChunks == 4 * kThreads, "chunk loop assumes 1024 chunks");
+    if (tid < V - kChunks * 8) {
+      const int i = kChunks * 8 + tid;
+      const float cc = __bfloat162float(lc[i]), uu = __bfloat162float(lu[i]);
+      float v = round_bf16(cc + round_bf16(cfg * round_bf16(cc - uu)));
+      if ((seen[i >> 5] >> (i & 31)) & 1u) v = v * (v > 0.f ? inv_rep : rep);
+      l[i] = v;
+    }
   }
   __syncthreads();
   const int i0 = tid * kPer, i1 = min(V, i0 + kPer);
@@ -144,7 +259,7 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
     // ---- top-k: keep every token >= the k-th largest value
     const int top_k = st.top_k[b];
     if (top_k > 0 && top_k < V) {
-      const uint32_t kk = bisect<true>(l, e, i0, i1, (float)top_k, red);
+      const uint32_t kk = radix_select<true>(l, e, i0, i1, (unsigned long long)top_k, 0.f, rx);
       float z2 = 0.f;
       for (int i = i0; i < i1; ++i) {
         if (fkey(l[i]) < kk) { l[i] = -INFINITY; e[i] = 0.f; }
@@ -156,7 +271,7 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
     const float top_p = st.top_p[b];
     if (top_p < 1.0f) {
       const float target = top_p * z;
-      const uint32_t kp = bisect<false>(l, e, i0, i1, target, red);
+      const uint32_t kp = radix_select<false>(l, e, i0, i1, 0ull, top_p, rx);
       float g = 0.f, pv = 0.f; int nt = 0;
       for (int i = i0; i < i1; ++i) {
         const uint32_t k = fkey(l[i]);
@@ -190,7 +305,7 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
     }
     // ---- exponential race over survivors: argmax (e_i / z) / Exp(1)_i
     const uint64_t seed = st.seed[b], uid = st.uid[b];
-    const uint32_t step = (uint32_t)st.n_out[b];
+    const uint32_t step = (uint32_t)n_prev;
     float best = -1.f; int bi = V;
     for (int i = i0; i < i1; ++i) {
       if (e[i] > 0.f) {
@@ -205,15 +320,30 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
     tok = bi;
   }
   // ---- emit + bookkeeping (one thread)
+  const bool fin = (tok == st.stop_token && !st.ignore_eos[b]) || n_prev + 1 >= st.max_out[b];
+  if (nx.res != nullptr) {
+    // ---- next decode step's inputs (t3.py:503-514 + block_table.py:357-377): both pair members are
+    // fed speech_emb[tok]; position = the slot this token's K/V will occupy.
+    const int half = tid >> 7, r = half * B + b;
+    nx.res[(size_t)r * 128 + (tid & 127)] = nx.speech_emb[(size_t)tok * 128 + (tid & 127)];
+    if ((tid & 127) == 0) {
+      const int p = (half ? len_u : len_c) + 1;
+      nx.pos[r] = p;
+      nx.row_seq[r] = r;
+      nx.kv_len[r] = fin ? 0 : p + 1;
+      nx.slot[r] = fin ? (int64_t)-1
+                       : (int64_t)nx.bt[(int64_t)r * nx.bt_stride + p / CBX_BLOCK_SIZE] * CBX_BLOCK_SIZE + p % CBX_BLOCK_SIZE;
+    }
+  }
   if (tid == 0) {
-    const int n = st.n_out[b];
+    const int n = n_prev;
     st.out_tokens[(size_t)b * st.out_stride + n] = tok;
     st.n_out[b] = n + 1;
     st.last_tok[b] = tok;
     st.seen[(size_t)b * CBX_SEEN_WORDS + (tok >> 5)] |= 1u << (tok & 31);
-    st.seq_len[b] += 1;
-    st.seq_len[B + b] += 1;
-    if ((tok == st.stop_token && !st.ignore_eos[b]) || n + 1 >= st.max_out[b]) {
+    st.seq_len[b] = len_c + 1;
+    st.seq_len[B + b] = len_u + 1;
+    if (fin) {
       st.finished[b] = 1;
       atomicAdd(st.n_finished, 1);
     }
@@ -232,11 +362,17 @@ int init_sample() {
 }
 }  // namespace cbx
 
-extern "C" int cbx_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, void* stream) {
+namespace cbx {
+int launch_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, const NextStep& nx, cudaStream_t s) {
   if (B <= 0) return 0;
-  const int smem = kSampleSmem;
-  if (cbx::init_sample()) return -1;
-  cfg_sample_kernel<<<B, kThreads, smem, (cudaStream_t)stream>>>((const bf16*)logits, *st, B);
-  CBX_CHECK_LAUNCH("cfg_sample");
+  if (init_sample()) return -1;
+  cudaError_t e = launch_pdl(cfg_sample_kernel, dim3(B), dim3(kThreads), kSampleSmem, s, (const bf16*)logits, *st, B, nx);
+  CBX_REQUIRE(e == cudaSuccess, "cfg_sample launch failed: %s", cudaGetErrorString(e));
+  count_launch();
   return 0;
+}
+}  // namespace cbx
+
+extern "C" int cbx_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, void* stream) {
+  return cbx::launch_cfg_sample(logits, st, B, cbx::NextStep(), (cudaStream_t)stream);
 }

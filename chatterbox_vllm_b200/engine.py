@@ -89,7 +89,7 @@ class T3Engine:
                                      cfg_scale=self.cfg_scale)
         self._cfg = EngineCfg(max_pairs, self.max_rows, max_model_len, num_blocks, max_model_len)
         nbytes = load().cbx_engine_workspace_bytes(C.byref(self._cfg))
-        self.workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
+        self.workspace = torch.zeros(nbytes + 1024, dtype=torch.uint8, device=self.device)
         ws = (self.workspace.data_ptr() + 1023) // 1024 * 1024
         self._st = self.sb.struct()
         self._h = load().cbx_engine_create(C.byref(self._cfg), C.byref(self._w), self.kv_cache.data_ptr(),
@@ -148,7 +148,7 @@ class T3Engine:
         return torch.cuda.current_stream().cuda_stream
 
     def set_trace(self, trace: torch.Tensor | None) -> None:
-        """Parity hook: bf16 [n_layers, 2, T, 1024] receives (mlp_out, residual) of every layer."""
+        """Parity hook: bf16 [n_layers, T, 1024] receives the residual stream after every layer."""
         check(load().cbx_engine_set_trace(self._h, trace.data_ptr() if trace is not None else None), "set_trace")
 
     def forward(self, T: int, max_kv_len: int) -> None:

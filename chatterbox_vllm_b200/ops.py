@@ -71,15 +71,62 @@ def rope_kv_append(qkv, pos, slot, cos_sin, kv_layer):
                                     _p(kv_layer), qkv.shape[0], _stream()), "rope_kv_append")
 
 
-def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: int):
+_attn_ws: dict = {}
+
+
+def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: int, out=None):
     T = qkv.shape[0]
-    out = torch.empty(T, HIDDEN, dtype=BF16, device=qkv.device)
+    if out is None:
+        out = torch.empty(T, HIDDEN, dtype=BF16, device=qkv.device)
     nbytes = load().cbx_attn_scratch_bytes(T, max_kv_len)
-    scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=qkv.device)
+    key = (qkv.device, torch.cuda.current_stream().cuda_stream)
+    ws = _attn_ws.get(key)
+    if ws is None or ws[0].numel() < nbytes or ws[1].numel() < T:     # cached: tickets stay zero between calls
+        ws = (torch.empty(max(nbytes, 16), dtype=torch.uint8, device=qkv.device),
+              torch.zeros(max(T, 1024), dtype=torch.int32, device=qkv.device))
+        _attn_ws[key] = ws
     check(load().cbx_paged_attn_decode(_p(qkv, BF16), _p(kv_layer), _p(block_table, torch.int32),
                                        block_table.stride(0), _p(row_seq, torch.int32), _p(kv_len, torch.int32),
-                                       _p(out), _p(scratch), T, max_kv_len, _stream()), "paged_attn_decode")
+                                       _p(out), _p(ws[0]), _p(ws[1], torch.int32), T, max_kv_len, _stream()),
+          "paged_attn_decode")
     return out
+
+
+def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5):
+    """RMSNorm → QKV → RoPE → KV append.  Returns the qkv buffer [T,3072] whose first 1024 columns hold
+    the rotated q (the k/v columns are not written: they went to the cache)."""
+    T = res.shape[0]
+    qkv = torch.zeros(T, 3 * HIDDEN, dtype=BF16, device=res.device)
+    h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device) if T > 4 else None
+    check(load().cbx_layer_qkv(_p(res, BF16), _p(ln_w, BF16), _p(wqkv, BF16), _p(cos_sin, BF16), _p(pos, torch.int32),
+                               _p(slot, torch.int64), _p(qkv), _p(kv_layer), _p(h), T, eps, _stream()), "layer_qkv")
+    return qkv
+
+
+def linear_residual(x, W, res):
+    """res += x·Wᵀ in place (N = 1024)."""
+    T, K = x.shape
+    assert W.shape == (HIDDEN, K) and res.shape == (T, HIDDEN)
+    check(load().cbx_linear_residual(_p(x, BF16), _p(W, BF16), _p(res, BF16), T, K, _stream()), "linear_residual")
+    return res
+
+
+def layer_gate_up(res, ln_w, wgu_packed, eps: float = 1e-5):
+    T = res.shape[0]
+    act = torch.empty(T, INTER, dtype=BF16, device=res.device)
+    h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device) if T > 4 else None
+    check(load().cbx_layer_gate_up(_p(res, BF16), _p(ln_w, BF16), _p(wgu_packed, BF16), _p(act), _p(h), T, eps,
+                                   _stream()), "layer_gate_up")
+    return act
+
+
+def head_logits(res, norm_w, whead, eps: float = 1e-5):
+    T = res.shape[0]
+    logits = torch.zeros(T, LOGITS_LD, dtype=BF16, device=res.device)
+    h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device) if T > 4 else None
+    check(load().cbx_head_logits(_p(res, BF16), _p(norm_w, BF16), _p(whead, BF16), _p(logits), _p(h), T, eps,
+                                 _stream()), "head_logits")
+    return logits
 
 
 class SamplerBuffers:
@@ -167,5 +214,6 @@ class BlockPool:
 
 
 __all__ = ["slot_mapping", "rmsnorm", "pack_gate_up", "linear", "rope_kv_append", "paged_attn_decode",
+           "layer_qkv", "linear_residual", "layer_gate_up", "head_logits",
            "SamplerBuffers", "cfg_sample", "decode_prepare", "prefill_embed", "BlockPool", "BLOCK_SIZE", "HIDDEN",
            "INTER", "LOGITS_LD", "PAGE_BYTES", "SEEN_WORDS", "SPEECH_VOCAB", "_lib"]

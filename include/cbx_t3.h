@@ -85,9 +85,32 @@ int cbx_rope_kv_append(void* qkv, const int32_t* pos, const int64_t* slot, const
  * row i attends to positions [0, kv_len[i]) of block-table row row_seq[i].
  * out bf16 [T,1024].  scratch: cbx_attn_scratch_bytes(T, max_kv_len). */
 int64_t cbx_attn_scratch_bytes(int T, int max_kv_len);
+int cbx_attn_num_splits(int T, int max_kv_len);
+/* counters: int32 [T], zero before first use; the kernel leaves them zero (split-K tickets: the
+ * CTA that publishes a row's last partial merges the row, so there is no second launch). */
 int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* block_table,
                           int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
-                          void* out, void* scratch, int T, int max_kv_len, void* stream);
+                          void* out, void* scratch, int32_t* counters, int T, int max_kv_len, void* stream);
+
+/* ---- fused layer pieces: what cbx_engine_forward launches per layer ------------------------
+ * The residual stream `res` [T,1024] is updated in place by the projections that close a
+ * residual branch (vllm llama.py:316-333 fused_add_rms_norm convention, rounding points kept:
+ * res = bf16(bf16(y) + res); h = bf16(bf16(res·rstd)·w)).  T <= 4 takes the weight-streaming
+ * GEMV kernels (norm fused as prologue), T > 4 the tcgen05 GEMM (h_scratch [T,1024] receives the
+ * normalised rows).  All launches carry programmatic stream serialisation. */
+/* RMSNorm(res)·ln_w -> ·Wqkv^T -> RoPE(q,k) -> q into qkv[:, 0:1024] (qkv is [T,3072]); k, v into
+ * page slot[t] of kv_layer (llama.py:221-223 + flash_attn.py:850-874). */
+int cbx_layer_qkv(const void* res, const void* ln_w, const void* Wqkv, const void* cos_sin,
+                  const int32_t* pos, const int64_t* slot, void* qkv, void* kv_layer, void* h_scratch,
+                  int T, float eps, void* stream);
+/* res += x[T,K]·W[1024,K]^T  (o_proj: K = 1024, llama.py:225; down_proj: K = 4096, llama.py:120). */
+int cbx_linear_residual(const void* x, const void* W, void* res, int T, int K, void* stream);
+/* act[T,4096] = SiLU(g)·u of RMSNorm(res)·ln_w·Wgu^T, Wgu packed by cbx_pack_gate_up (llama.py:117-119). */
+int cbx_layer_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, void* h_scratch, int T,
+                      float eps, void* stream);
+/* logits[T, CBX_LOGITS_LD] = RMSNorm(res)·norm_w · Whead[8194,1024]^T (llama.py:430 + t3.py:729-730). */
+int cbx_head_logits(const void* res, const void* norm_w, const void* Whead, void* logits, void* h_scratch,
+                    int T, float eps, void* stream);
 
 /* t3.py:732 (CFG merge) + vllm v1 Sampler (sampler.py:67-300) in one kernel, one CTA per
  * pair.  logits bf16 [2B, CBX_LOGITS_LD] (rows b = cond, B+b = uncond).  Per-pair state
@@ -161,20 +184,21 @@ void cbx_engine_destroy(cbx_engine*);
  * "slot","kv_len","row_seq","head_rows") for tests / the Python façade; NULL if unknown. */
 void* cbx_engine_buffer(cbx_engine*, const char* name);
 
-/* Parity hook (tests only): while trace != NULL, cbx_engine_forward copies, after every layer
- * li, the MLP output x and the residual stream res (vllm llama.py:316-333 convention:
- * HF hidden state = x + res) to trace[(2*li+0)*T*1024] and trace[(2*li+1)*T*1024] (bf16).
- * Not capturable state: set before the forward call, clear with NULL. */
+/* Parity hook (tests only): while trace != NULL, cbx_engine_forward / cbx_engine_decode copy,
+ * after every layer li, the residual stream (= the HF hidden state after the layer) to
+ * trace[li*T*1024] (bf16).  Set before the call, clear with NULL; do not use with graphs. */
 int cbx_engine_set_trace(cbx_engine*, void* trace);
 
-/* Llama forward over T rows whose embeddings are already in buffer "x", with pos/slot/
- * row_seq/kv_len filled (t3.py:742-778 + vllm llama.py:394-430).  Leaves final-norm hidden
- * states in buffer "h". */
+/* Llama forward over T rows whose embeddings are already in buffer "res" (alias "x"), with
+ * pos/slot/row_seq/kv_len filled (t3.py:742-778 + vllm llama.py:394-430).  Leaves final-norm
+ * hidden states in buffer "h". */
 int cbx_engine_forward(cbx_engine*, int T, int max_kv_len, void* stream);
 /* Head GEMM over the 2B rows listed in buffer "head_rows" (row index into "h"; cond rows
  * first) + cbx_cfg_sample (t3.py:725-739 + sampler). */
 int cbx_engine_sample(cbx_engine*, int B, void* stream);
-/* n decode steps for pair slots [0,B): prepare → forward(2B rows) → sample, no host sync.
+/* n decode steps for pair slots [0,B): forward(2B rows) → head → sample, no host sync.  The
+ * step's inputs (embedding rows, positions, slots, kv lengths) were staged on the device by the
+ * previous cbx_engine_sample / decode step's sampler launch.
  * use_graph != 0 replays a CUDA graph of one step (captured on first use per (B, max_kv_len
  * bucket)). */
 int cbx_engine_decode(cbx_engine*, int B, int n_steps, int max_kv_len, int use_graph, void* stream);

@@ -223,6 +223,23 @@ def test_engine_greedy_stream_matches_oracle_2layers(ops, use_graph):
     eng.close()
 
 
+@pytest.mark.parametrize("overlap", ["64", "0"])
+def test_engine_two_microbatch_overlap_parity(ops, overlap, monkeypatch):
+    """T = 64 rows: the decode step runs cond and uncond rows as two microbatches on two streams
+    (attention of one overlapping the GEMMs of the other).  Same parity bar as the single-stream
+    step, with and without CUDA-graph replay of the forked step."""
+    monkeypatch.setenv("CBX_OVERLAP_MIN_ROWS", overlap)
+    n_steps = 10
+    for use_graph in (True, False):
+        cfg, w, eng = _mk_engine(2, 32, use_graph=use_graph)
+        reqs = _requests(32, n_steps, temperature=0.0, repetition_penalty=2.0)
+        got = eng.generate(reqs, poll_every=4)
+        assert eng.generate(reqs, poll_every=3) == got, "same batch must give the same bits"
+        assert_stream_parity(got, w, reqs, eng.cfg_scale, n_steps, first_exact=0, temperature=0.0,
+                             repetition_penalty=2.0)
+        eng.close()
+
+
 def test_engine_logits_tolerance_30layers(ops):
     """Full-depth (30-layer) model, oracle teacher-forced with the engine's own tokens: every
     engine token is the oracle's argmax or within 8 bf16 ulps of its top logit, and >= 80 % of
@@ -247,11 +264,12 @@ LAYER_REL_L2_BF16, LAYER_REL_L2_FP32, LAYER_MAX_ABS, HEAD_MAX_ABS = 2e-2, 3e-2, 
 
 
 def _layer_errors(tr_eng, tr_orc):
-    """tr_eng bf16 [L, 2, T, 1024] (cuda); tr_orc list of (mlp_out, residual) fp32 [T, 1024]."""
+    """tr_eng bf16 [L, T, 1024] (cuda): residual stream after each layer = HF hidden state;
+    tr_orc list of (mlp_out, residual) fp32 [T, 1024]."""
     out = []
     for li, (dn, res) in enumerate(tr_orc):
         want = dn + res
-        got = tr_eng[li, 0].float().cpu() + tr_eng[li, 1].float().cpu()
+        got = tr_eng[li].float().cpu()
         d = got - want
         out.append((float(d.norm() / want.norm()), float(d.abs().max() / want.abs().max())))
     return out
@@ -275,7 +293,7 @@ def test_engine_per_layer_error_30layers(ops):
         P, held = eng._admit(reqs)
         eng._init_sampler_state(reqs, P)
         T = 2 * sum(P)
-        tr = torch.zeros(30, 2, T, 1024, dtype=BF16, device="cuda")
+        tr = torch.zeros(30, T, 1024, dtype=BF16, device="cuda")
         eng.set_trace(tr)
         with torch.cuda.stream(eng.stream):
             eng.prefill(reqs, P)
@@ -293,7 +311,7 @@ def test_engine_per_layer_error_30layers(ops):
                 pairs[m].append(pair)
                 c, u = o.prefill_embeds(r.cond_emb, torch.tensor(r.text_ids))
                 h = o.forward_rows(torch.cat((c, u), 0), [(pair[0], P[b]), (pair[1], P[b])])
-                errs = _layer_errors(tr[:, :, r0:r0 + 2 * P[b]], o.trace["layers"])
+                errs = _layer_errors(tr[:, r0:r0 + 2 * P[b]], o.trace["layers"])
                 lim = LAYER_REL_L2_BF16 if m == "bf16" else LAYER_REL_L2_FP32
                 assert max(e[0] for e in errs) <= lim, f"prefill {m} rel-L2 per layer: {errs}"
                 assert max(e[1] for e in errs) <= LAYER_MAX_ABS, f"prefill {m} max-abs per layer: {errs}"
@@ -304,7 +322,7 @@ def test_engine_per_layer_error_30layers(ops):
                 report[f"prefill_B{n_req}_req{b}_{m}"] = {"layers": errs, "head_max_abs": herr}
             r0 += 2 * P[b]
         # one decode step, teacher-forced with the engine's first tokens
-        tr = torch.zeros(30, 2, 2 * n_req, 1024, dtype=BF16, device="cuda")
+        tr = torch.zeros(30, 2 * n_req, 1024, dtype=BF16, device="cuda")
         eng.set_trace(tr)
         with torch.cuda.stream(eng.stream):
             eng.decode(n_req, 1, max(P) + 2)

@@ -208,3 +208,109 @@ def test_paged_attention_many_rows_single_split_and_empty_rows(ops):
         r, L = rows[i]
         want = _ref_attn(cfg, qkv_all[r], q[i, :1024].float(), L, cs) if L else torch.zeros(1024)
         assert_close_bf16(out[i], want, ulps=1.0, atol=2e-3, what=f"row {i} (seq {r}, L={L})")
+
+
+def test_paged_attention_split_tickets_reset(ops):
+    """Split-K rows are merged by the last-arriving CTA; the ticket counters must return to zero so
+    a second launch over the same workspace gives identical bits."""
+    cfg = T3ModelConfig()
+    lens = [700, 650, 33, 512]
+    kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, lens, seed=8)
+    g = torch.Generator().manual_seed(4)
+    q = dev(torch.randn(4, 3072, generator=g).to(BF16))
+    args = (q, kv, bt_d, dev(torch.arange(4, dtype=torch.int32)), dev(torch.tensor(lens, dtype=torch.int32)), 700)
+    assert ops._lib.load().cbx_attn_num_splits(4, 700) > 1
+    a = ops.paged_attn_decode(*args).clone()
+    for _ in range(3):
+        assert torch.equal(ops.paged_attn_decode(*args), a)
+    for r in range(4):
+        want = _ref_attn(cfg, qkv_all[r], q[r, :1024].float().cpu(), lens[r], cs)
+        assert_close_bf16(a[r], want, ulps=1.0, atol=2e-3, what=f"split attn row {r}")
+
+
+# ------------------------------------------------------------------ fused layer pieces
+def _unswizzled_k(page_bf16, h, tok):
+    krow = page_bf16[(h * 16 + tok) * 64:(h * 16 + tok) * 64 + 64].view(8, 8)
+    return torch.stack([krow[c ^ (tok & 7)] for c in range(8)]).reshape(64)
+
+
+@pytest.mark.parametrize("T", [1, 2, 4, 6, 200])
+def test_layer_qkv_fused_norm_rope_append(ops, T):
+    """[RMSNorm → QKV → RoPE → KV append] in one op (GEMV kernel for T <= 4, rmsnorm + tcgen05 GEMM
+    with the RoPE/append epilogue above) against the oracle's op-by-op bf16 chain."""
+    cfg = T3ModelConfig()
+    g = torch.Generator().manual_seed(100 + T)
+    res = (torch.randn(T, 1024, generator=g) * 1.5).to(BF16)
+    ln = (1 + 0.1 * torch.randn(1024, generator=g)).to(BF16)
+    W = (torch.randn(3072, 1024, generator=g) * 0.03).to(BF16)
+    pos = torch.randint(0, 900, (T,), generator=g, dtype=torch.int32)
+    n_blocks = T + 2
+    blk = torch.randperm(n_blocks - 1, generator=g)[:T] + 1
+    slot = (blk * 16 + torch.randint(0, 16, (T,), generator=g)).to(torch.int64)
+    if T > 1:
+        slot[T - 1] = -1                                   # finished pair: nothing may be cached
+    kv = torch.zeros(n_blocks * 65536, dtype=torch.uint8).cuda()
+    cs = rope_cos_sin(cfg, 1024)
+    qkv = ops.layer_qkv(dev(res), dev(ln), dev(W), dev(cs.to(BF16)), dev(pos), dev(slot), kv)
+    h = rmsnorm(res.float(), ln, 1e-5, "bf16")
+    y = _ref_linear(h, W).to(BF16).float()
+    want_q = apply_rope(y[:, :1024].view(T, 16, 64), pos.long(), cs, "bf16").reshape(T, 1024)
+    want_k = apply_rope(y[:, 1024:2048].view(T, 16, 64), pos.long(), cs, "bf16").reshape(T, 1024)
+    want_v = y[:, 2048:]
+    # y carries <= 1 ulp of accumulation-order noise per element; rotation mixes two of them
+    tol = dict(ulps=3.0, atol=0.03)
+    assert_close_bf16(qkv[:, :1024], want_q, what="fused q", **tol)
+    pages = kv.cpu().view(-1, 65536)
+    touched = set()
+    for t in range(T):
+        if slot[t] < 0:
+            continue
+        b, tok = int(slot[t]) // 16, int(slot[t]) % 16
+        touched.add(b)
+        page = pages[b].view(torch.bfloat16)
+        for hd in range(16):
+            assert_close_bf16(_unswizzled_k(page, hd, tok), want_k[t, hd * 64:hd * 64 + 64], what="fused K", **tol)
+            vrow = page[16384 + (hd * 16 + tok) * 64:16384 + (hd * 16 + tok) * 64 + 64]
+            assert_close_bf16(vrow, want_v[t, hd * 64:hd * 64 + 64], ulps=1.01, atol=0.02, what="fused V")
+    for b in range(n_blocks):
+        if b not in touched:
+            assert not pages[b].any(), f"page {b} must stay untouched"
+
+
+@pytest.mark.parametrize("T", [1, 3, 4, 5, 256])
+@pytest.mark.parametrize("K", [1024, 4096])
+def test_linear_residual_in_place(ops, T, K):
+    g = torch.Generator().manual_seed(T * 7 + K)
+    x = torch.randn(T, K, generator=g).to(BF16)
+    W = (torch.randn(1024, K, generator=g) * 0.03).to(BF16)
+    res = (torch.randn(T, 1024, generator=g) * 2).to(BF16)
+    got = ops.linear_residual(dev(x), dev(W), dev(res.clone()))
+    y = _ref_linear(x, W).to(BF16).float()
+    want = (y + res.float()).to(BF16).float()
+    err = (got.float().cpu() - want).abs()
+    tol = 2.0 * ULP * y.abs() + 1.01 * ULP * want.abs() + 1e-6     # 2 ulps on the GEMM term + the final rounding
+    assert (err <= tol).all(), f"max err {err.max():.3e}"
+
+
+@pytest.mark.parametrize("T", [1, 2, 4, 7, 256])
+def test_layer_gate_up_fused_norm_silu(ops, T):
+    g = torch.Generator().manual_seed(T + 31)
+    res = (torch.randn(T, 1024, generator=g) * 1.2).to(BF16)
+    ln = (1 + 0.1 * torch.randn(1024, generator=g)).to(BF16)
+    Wgu = (torch.randn(8192, 1024, generator=g) * 0.03).to(BF16)
+    act = ops.layer_gate_up(dev(res), dev(ln), ops.pack_gate_up(dev(Wgu)))
+    h = rmsnorm(res.float(), ln, 1e-5, "bf16")
+    gu = _ref_linear(h, Wgu).to(BF16).float()
+    want = torch.nn.functional.silu(gu[:, :4096]) * gu[:, 4096:]
+    assert_close_bf16(act, want, ulps=3.0, atol=3e-3, what=f"fused gate_up T={T}")
+
+
+@pytest.mark.parametrize("T", [2, 4, 6, 256])
+def test_head_logits_fused_final_norm(ops, T):
+    g = torch.Generator().manual_seed(T + 77)
+    res = (torch.randn(T, 1024, generator=g) * 1.2).to(BF16)
+    nw = (1 + 0.1 * torch.randn(1024, generator=g)).to(BF16)
+    Wh = (torch.randn(8194, 1024, generator=g) * 0.05).to(BF16)
+    lg = ops.head_logits(dev(res), dev(nw), dev(Wh))
+    h = rmsnorm(res.float(), nw, 1e-5, "bf16")
+    assert_close_bf16(lg[:, :8194], _ref_linear(h, Wh), ulps=2.0, atol=0.02, what=f"head T={T}")

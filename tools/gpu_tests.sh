@@ -12,7 +12,8 @@ run ints    tests/test_gpu_kernels.py -k "slot_mapping or rmsnorm"
 run gemv    tests/test_gpu_kernels.py -k "gemv"
 run gemm    tests/test_gpu_kernels.py -k "gemm_tcgen05"
 run silu    tests/test_gpu_kernels.py -k "silu"
-run rope    tests/test_gpu_kernels.py -k "rope"
+run rope    tests/test_gpu_kernels.py -k "rope and not fused"
 run attn    tests/test_gpu_kernels.py -k "paged_attention"
+run fused   tests/test_gpu_kernels.py -k "fused or residual"
 run sampler tests/test_gpu_engine.py -k "sampler or prefill_embed"
 run engine  tests/test_gpu_engine.py -k "engine"
