@@ -6,7 +6,9 @@
 // (utils.py:51-89) → greedy argmax | temperature → min-p (builtin.py:101-112) → top-k /
 // top-p (topk_topp_sampler.py:328-369) → exponential race (…:395-416), plus the scheduler's
 // stop / max_tokens check — with all per-request state resident on the device, so the decode
-// loop never synchronises with the host.  One CTA (256 threads) per CFG pair.
+// loop never synchronises with the host.  One CTA of 1024 threads per CFG pair; every
+// thread keeps its 8 contiguous vocabulary ids (one 16-byte chunk of each logits row) in registers
+// for the whole chain — no shared-memory copy of the row.
 //
 // Specified tie rules (the reference leaves them to sort order): argmax → lowest id; top-p
 // boundary ties → lowest ids kept first; top-k keeps every token tied with the k-th value.
@@ -15,12 +17,12 @@
 using namespace cbx;
 namespace cbx { int init_sample(); }
 
+
 namespace {
 constexpr int V = CBX_SPEECH_VOCAB;
-constexpr int kThreads = 256;
-constexpr int kPer = (V + kThreads - 1) / kThreads;     // 33 contiguous ids per thread
+constexpr int kThreads = 1024, kWarps = 32;
+constexpr int NP = 10;                         // ids per thread: 8 (+2 tail ids on the last thread)
 constexpr float kSamplingEps = 1e-5f;
-constexpr int kSampleSmem = (2 * V + 4) * sizeof(float);
 }  // namespace
 namespace cbx {
 struct NextStep {             // optional fused "decode_prepare" for the following step (engine only)
@@ -30,65 +32,100 @@ struct NextStep {             // optional fused "decode_prepare" for the followi
 }  // namespace cbx
 namespace {
 
-__device__ __forceinline__ uint32_t fkey(float f) {
+__device__ __forceinline__ uint32_t fkey(float f) {      // order-preserving float -> uint32
   const uint32_t u = __float_as_uint(f);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
 struct Red {
-  float f[8];
-  int i[8];
+  float f[kWarps];
+  int i[kWarps];
+  uint32_t u[kWarps];
 };
 
+// Fixed-order (deterministic) block reductions: warp shuffle, then every warp re-reduces the 32
+// warp partials, so all threads hold the result after one barrier pair.
 __device__ __forceinline__ float block_sum(float v, Red& red) {
   v = warp_sum(v);
   if ((threadIdx.x & 31) == 0) red.f[threadIdx.x >> 5] = v;
   __syncthreads();
-  float s = 0.f;
-#pragma unroll
-  for (int w = 0; w < 8; ++w) s += red.f[w];
+  const float s = warp_sum(red.f[threadIdx.x & 31]);
   __syncthreads();
   return s;
 }
-// max value, ties -> lowest index
-__device__ __forceinline__ void block_argmax(float& v, int& idx, Red& red) {
+__device__ __forceinline__ uint32_t block_min_u32(uint32_t v, Red& red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if ((threadIdx.x & 31) == 0) red.u[threadIdx.x >> 5] = v;
+  __syncthreads();
+  v = red.u[threadIdx.x & 31];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+  __syncthreads();
+  return v;
+}
+__device__ __forceinline__ void warp_argmax(float& v, int& idx) {   // ties -> lowest index
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, v, o);
     const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
     if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
   }
+}
+__device__ __forceinline__ void block_argmax(float& v, int& idx, Red& red) {
+  warp_argmax(v, idx);
   if ((threadIdx.x & 31) == 0) { red.f[threadIdx.x >> 5] = v; red.i[threadIdx.x >> 5] = idx; }
   __syncthreads();
-  v = red.f[0]; idx = red.i[0];
-#pragma unroll
-  for (int w = 1; w < 8; ++w)
-    if (red.f[w] > v || (red.f[w] == v && red.i[w] < idx)) { v = red.f[w]; idx = red.i[w]; }
+  v = red.f[threadIdx.x & 31]; idx = red.i[threadIdx.x & 31];
+  warp_argmax(v, idx);
   __syncthreads();
 }
+// exclusive prefix sum of one int per thread in thread order; also returns the block total
+__device__ __forceinline__ int block_excl_scan(int v, int& total, Red& red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) red.i[w] = incl;
+  __syncthreads();
+  int wt = red.i[lane], winc = wt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, winc, o);
+    if (lane >= o) winc += t;
+  }
+  total = __shfl_sync(0xffffffffu, winc, 31);
+  const int before_warp = __shfl_sync(0xffffffffu, winc - wt, w);
+  __syncthreads();
+  return before_warp + incl - v;
+}
 
-__device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) { return __umulhi(a, b); }
 // Philox-4x32-10, returns word 0
 __device__ __forceinline__ uint32_t philox_word0(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
                                                  uint32_t k1) {
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
-    const uint32_t hi0 = mulhi32(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-    const uint32_t hi1 = mulhi32(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
     c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
     k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
   }
   return c0;
 }
 
-// Minimal key k in [0, 2^32) with F(k) < target, where F(k) = total weight of live ids whose key
-// is > k  (== the key of the pivot element at which the descending cumulative weight reaches
-// target).  MSB-first 8-bit radix select: 4 histogram passes instead of a 32-step bisection.
-// Weights are integers — 1 for top-k, e_i·2^40 for top-p — so the shared-memory atomics commute and
-// the result is bit-reproducible.  Each thread owns a contiguous id range and run-length-merges
-// equal digits before touching a bin (the top byte of a logit key is almost constant).
+// ---- radix select ---------------------------------------------------------------------------
+// Minimal key k with F(k) < target, where F(k) = total weight of live ids whose key is > k (== the
+// key of the pivot at which the descending cumulative weight reaches target).  MSB-first 8-bit
+// digits over the bits in which the live keys actually differ (the common prefix of min and max
+// key is skipped, typically leaving 3 passes of which only the first touches every element).
+// Weights are integers — 1 for top-k, e_i·2^40 for top-p — so the shared-memory atomics commute
+// and the result is bit-reproducible; bins are (lo, hi) 32-bit pairs because 32-bit shared
+// atomics are native while 64-bit ones are CAS loops.
 struct Radix {
-  uint32_t lo[256], hi[256];          // 64-bit bins as two words: 32-bit shared atomics are native, 64-bit ones CAS-loop
+  uint32_t lo[256], hi[256];
   unsigned long long above, target;
   int digit;
 };
@@ -100,37 +137,41 @@ __device__ __forceinline__ void bin_add(Radix& rx, int d, unsigned long long w) 
 }
 __device__ __forceinline__ unsigned long long quant40(float e) { return __float2ull_rz(e * 1099511627776.f); }
 
-// kCount: weights 1 and `target` given; else weights quant40(e[i]) and target = top_p · total.
 template <bool kCount>
-__device__ uint32_t radix_select(const float* l, const float* e, int i0, int i1, unsigned long long target_in,
-                                 float top_p, Radix& rx) {
-  uint32_t prefix = 0;
+__device__ uint32_t radix_select(const float (&l)[NP], const float (&e)[NP], uint32_t kmax, unsigned long long target_in,
+                                 float top_p, Radix& rx, Red& red) {
+  uint32_t kmin = 0xffffffffu;
+#pragma unroll
+  for (int j = 0; j < NP; ++j) if (l[j] != -INFINITY) kmin = min(kmin, fkey(l[j]));
+  kmin = block_min_u32(kmin, red);
+  const int nbits = 32 - __clz(kmin ^ kmax);           // low bits in which live keys differ (clz(0) = 32)
+  const int top = (nbits + 7) & ~7, n_pass = top >> 3;
+  uint32_t prefix = top >= 32 ? 0u : (kmax >> top);
   if (threadIdx.x == 0) { rx.above = 0; rx.target = target_in; }
 #pragma unroll 1
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 24 - 8 * pass;
-    rx.lo[threadIdx.x] = 0; rx.hi[threadIdx.x] = 0;     // kThreads == 256 bins
+  for (int pass = 0; pass < n_pass; ++pass) {
+    const int shift = top - 8 * (pass + 1);
+    if (threadIdx.x < 256) { rx.lo[threadIdx.x] = 0; rx.hi[threadIdx.x] = 0; }
     __syncthreads();
     int run_d = -1;
     unsigned long long run_w = 0;
-    for (int i = i0; i < i1; ++i) {
-      const float li = l[i];
-      if (li == -INFINITY) continue;
-      const uint32_t key = fkey(li);
-      if (pass > 0 && (key >> (shift + 8)) != prefix) continue;
-      const int d = (key >> shift) & 255;
-      const unsigned long long w = kCount ? 1ull : quant40(e[i]);
-      if (d != run_d) {
-        if (run_w) bin_add(rx, run_d, run_w);
-        run_d = d; run_w = 0;
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      const uint32_t key = fkey(l[j]);
+      const bool in = l[j] != -INFINITY && (shift + 8 >= 32 || (key >> (shift + 8)) == prefix);
+      if (in) {
+        const int d = (key >> shift) & 255;
+        if (d != run_d) {
+          if (run_w) bin_add(rx, run_d, run_w);
+          run_d = d; run_w = 0;
+        }
+        run_w += kCount ? 1ull : quant40(e[j]);
       }
-      run_w += w;
     }
     if (run_w) bin_add(rx, run_d, run_w);
     __syncthreads();
     if (threadIdx.x < 32) {
-      // lane owns bins 255-8*lane .. 248-8*lane (descending digits)
-      const int lane = threadIdx.x;
+      const int lane = threadIdx.x;                    // lane owns bins 255-8*lane .. 248-8*lane
       unsigned long long b8[8], tot = 0;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -138,7 +179,7 @@ __device__ uint32_t radix_select(const float* l, const float* e, int i0, int i1,
         b8[j] = ((unsigned long long)rx.hi[d] << 32) | rx.lo[d];
         tot += b8[j];
       }
-      unsigned long long incl = tot;                   // inclusive scan over lanes
+      unsigned long long incl = tot;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const unsigned long long v = __shfl_up_sync(0xffffffffu, incl, o);
@@ -159,7 +200,6 @@ __device__ uint32_t radix_select(const float* l, const float* e, int i0, int i1,
         running += b8[j];
       }
       const unsigned ball = __ballot_sync(0xffffffffu, found >= 0);
-      __syncwarp();
       if (ball == 0) {                                 // fewer live weights than the target: keep everything
         if (lane == 0) { rx.digit = 0; rx.above = running; rx.target = target; }
       } else if (lane == __ffs(ball) - 1) {
@@ -170,122 +210,109 @@ __device__ uint32_t radix_select(const float* l, const float* e, int i0, int i1,
     prefix = (prefix << 8) | (uint32_t)rx.digit;
     __syncthreads();
   }
-  return prefix;
+  return n_pass == 0 ? kmax : prefix;
 }
 
-__global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __restrict__ logits,
-                                                              cbx_sampler_state st, int B, const NextStep nx) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  float* l = reinterpret_cast<float*>(smem_raw);          // [V] working logits
-  float* e = l + V + 2;                                   // [V] exp(l - max)
+__device__ __forceinline__ float cfg_pen(float cc, float uu, float cfg, bool seen, float rep, float inv_rep) {
+  float v = round_bf16(cc + round_bf16(cfg * round_bf16(cc - uu)));   // t3.py:732, one bf16 rounding per op
+  if (seen) v = v * (v > 0.f ? inv_rep : rep);                         // _custom_ops.py:360-373
+  return v;
+}
+
+__global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* __restrict__ logits,
+                                                                 cbx_sampler_state st, int B, const NextStep nx) {
   __shared__ Red red;
   __shared__ Radix rx;
-  __shared__ int s_scan[kThreads];
   const int b = blockIdx.x, tid = threadIdx.x;
   pdl_trigger();
   pdl_wait();
   if (st.finished[b]) return;
   const int n_prev = st.n_out[b];
   const int len_c = st.seq_len[b], len_u = st.seq_len[B + b];
+  const float rep = st.rep_pen[b], cfg = st.cfg_scale, inv_rep = 1.0f / rep;
+  const float temp = st.temperature[b], min_p = st.min_p[b], top_p = st.top_p[b];
+  const int top_k = st.top_k[b];
 
+  // ---- load: ids [8·tid, 8·tid+8) (+ 8192, 8193 on the last thread); CFG merge + repetition penalty
   const bf16* lc = logits + (size_t)b * CBX_LOGITS_LD;
   const bf16* lu = logits + (size_t)(B + b) * CBX_LOGITS_LD;
   const uint32_t* seen = st.seen + (size_t)b * CBX_SEEN_WORDS;
-  const float rep = st.rep_pen[b], cfg = st.cfg_scale;
-  const float inv_rep = 1.0f / rep;
-  // ---- CFG merge (bf16 op-by-op) + repetition penalty: 128-bit loads, all issued before first use
+  const int id0 = tid * 8;
+  float l[NP], e[NP];
   {
-    constexpr int kChunks = V / 8;                       // 1024 full chunks + 2 tail ids
-    uint4 vc[4], vu[4];
-    uint32_t sb[4];
+    const uint4 vc = reinterpret_cast<const uint4*>(lc)[tid], vu = reinterpret_cast<const uint4*>(lu)[tid];
+    const uint32_t sb = (seen[tid >> 2] >> ((tid & 3) * 8)) & 0xffu;
+    const uint32_t cw[4] = {vc.x, vc.y, vc.z, vc.w}, uw[4] = {vu.x, vu.y, vu.z, vu.w};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int c = tid + k * kThreads;
-      vc[k] = reinterpret_cast<const uint4*>(lc)[c];
-      vu[k] = reinterpret_cast<const uint4*>(lu)[c];
-      sb[k] = (seen[c >> 2] >> ((c & 3) * 8)) & 0xffu;
+    for (int j = 0; j < 8; ++j) {
+      const float cc = (j & 1) ? bf_hi(cw[j >> 1]) : bf_lo(cw[j >> 1]);
+      const float uu = (j & 1) ? bf_hi(uw[j >> 1]) : bf_lo(uw[j >> 1]);
+      l[j] = cfg_pen(cc, uu, cfg, (sb >> j) & 1u, rep, inv_rep);
     }
+    l[8] = l[9] = -INFINITY;
+    if (tid == kThreads - 1) {
+      const uint32_t sw = seen[CBX_SEEN_WORDS - 1];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int c = tid + k * kThreads;
-      const uint32_t cw[4] = {vc[k].x, vc[k].y, vc[k].z, vc[k].w}, uw[4] = {vu[k].x, vu[k].y, vu[k].z, vu[k].w};
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float cc = (j & 1) ? bf_hi(cw[j >> 1]) : bf_lo(cw[j >> 1]);
-        const float uu = (j & 1) ? bf_hi(uw[j >> 1]) : bf_lo(uw[j >> 1]);
-        float v = round_bf16(cc + round_bf16(cfg * round_bf16(cc - uu)));
-        if ((sb[k] >> j) & 1u) v = v * (v > 0.f ? inv_rep : rep);
-        l[c * 8 + j] = v;
-      }
-    }
-    static_assert(kChunks == 4 * kThreads, "chunk loop assumes 1024 chunks");
-    if (tid < V - kChunks * 8) {
-      const int i = kChunks * 8 + tid;
-      const float cc = __bfloat162float(lc[i]), uu = __bfloat162float(lu[i]);
-      float v = round_bf16(cc + round_bf16(cfg * round_bf16(cc - uu)));
-      if ((seen[i >> 5] >> (i & 31)) & 1u) v = v * (v > 0.f ? inv_rep : rep);
-      l[i] = v;
+      for (int j = 0; j < 2; ++j)
+        l[8 + j] = cfg_pen(__bfloat162float(lc[8192 + j]), __bfloat162float(lu[8192 + j]), cfg, (sw >> j) & 1u, rep, inv_rep);
     }
   }
-  __syncthreads();
-  const int i0 = tid * kPer, i1 = min(V, i0 + kPer);
+  // ---- greedy argmax on the penalised logits (ties -> lowest id)
   float mx = -INFINITY; int amx = V;
-  for (int i = i0; i < i1; ++i) if (l[i] > mx) { mx = l[i]; amx = i; }
+#pragma unroll
+  for (int j = 0; j < NP; ++j) if (l[j] > mx) { mx = l[j]; amx = id0 + j; }
   block_argmax(mx, amx, red);
-
   int tok = amx;
-  const float temp = st.temperature[b];
+
   if (temp >= kSamplingEps) {
     // ---- temperature, softmax numerators
     const float mt = mx / temp;
     float z = 0.f;
-    for (int i = i0; i < i1; ++i) {
-      const float v = l[i] / temp;
-      const float ev = expf(v - mt);
-      l[i] = v; e[i] = ev; z += ev;
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      l[j] = l[j] / temp;
+      e[j] = l[j] == -INFINITY ? 0.f : expf(l[j] - mt);
+      z += e[j];
     }
     z = block_sum(z, red);
-    // ---- min-p: drop p_i < p_max * min_p
-    const float min_p = st.min_p[b];
+    const uint32_t kmax = fkey(mt);
+    // ---- min-p: drop p_i < p_max · min_p   (builtin.py:101-112)
     if (min_p > 0.f) {
       const float thr = (1.0f / z) * min_p;
       float z2 = 0.f;
-      for (int i = i0; i < i1; ++i) {
-        if (e[i] / z < thr) { l[i] = -INFINITY; e[i] = 0.f; }
-        z2 += e[i];
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        if (e[j] / z < thr) { l[j] = -INFINITY; e[j] = 0.f; }
+        z2 += e[j];
       }
       z = block_sum(z2, red);
     }
     // ---- top-k: keep every token >= the k-th largest value
-    const int top_k = st.top_k[b];
     if (top_k > 0 && top_k < V) {
-      const uint32_t kk = radix_select<true>(l, e, i0, i1, (unsigned long long)top_k, 0.f, rx);
+      const uint32_t kk = radix_select<true>(l, e, kmax, (unsigned long long)top_k, 0.f, rx, red);
       float z2 = 0.f;
-      for (int i = i0; i < i1; ++i) {
-        if (fkey(l[i]) < kk) { l[i] = -INFINITY; e[i] = 0.f; }
-        z2 += e[i];
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        if (fkey(l[j]) < kk) { l[j] = -INFINITY; e[j] = 0.f; }
+        z2 += e[j];
       }
       z = block_sum(z2, red);
     }
     // ---- top-p: keep token iff the mass ranked strictly above it is < p
-    const float top_p = st.top_p[b];
     if (top_p < 1.0f) {
       const float target = top_p * z;
-      const uint32_t kp = radix_select<false>(l, e, i0, i1, 0ull, top_p, rx);
+      const uint32_t kp = radix_select<false>(l, e, kmax, 0ull, top_p, rx, red);
       float g = 0.f, pv = 0.f; int nt = 0;
-      for (int i = i0; i < i1; ++i) {
-        const uint32_t k = fkey(l[i]);
-        if (k > kp && l[i] != -INFINITY) g += e[i];
-        else if (k == kp) { ++nt; pv += e[i]; }
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        const uint32_t k = fkey(l[j]);
+        if (k > kp && l[j] != -INFINITY) g += e[j];
+        else if (k == kp) { ++nt; pv += e[j]; }
       }
       g = block_sum(g, red);
-      pv = block_sum(pv, red);                            // = (#ties)·e(v*) ; divide below
-      // exclusive scan of tie counts in id order (threads own contiguous id ranges)
-      s_scan[tid] = nt;
-      __syncthreads();
-      int before = 0, total = 0;
-      for (int t = 0; t < kThreads; ++t) { const int c = s_scan[t]; if (t < tid) before += c; total += c; }
-      __syncthreads();
+      pv = block_sum(pv, red);                            // = (#ties)·e(v*)
+      int total;
+      const int before = block_excl_scan(nt, total, red);  // tie rank in id order
       const float ev = total > 0 ? pv / (float)total : 0.f;
       int n_keep = total;
       if (ev > 0.f) {
@@ -294,34 +321,37 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
       }
       float z2 = 0.f;
       int rank = before;
-      for (int i = i0; i < i1; ++i) {
-        const uint32_t k = fkey(l[i]);
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        const uint32_t k = fkey(l[j]);
         bool drop = k < kp;
         if (k == kp) { drop = rank >= n_keep; ++rank; }
-        if (drop) { l[i] = -INFINITY; e[i] = 0.f; }
-        z2 += e[i];
+        if (drop) { l[j] = -INFINITY; e[j] = 0.f; }
+        z2 += e[j];
       }
       z = block_sum(z2, red);
     }
-    // ---- exponential race over survivors: argmax (e_i / z) / Exp(1)_i
+    // ---- exponential race over survivors: argmax (e_i / z) / Exp(1)_i   (topk_topp_sampler.py:395-416)
     const uint64_t seed = st.seed[b], uid = st.uid[b];
     const uint32_t step = (uint32_t)n_prev;
     float best = -1.f; int bi = V;
-    for (int i = i0; i < i1; ++i) {
-      if (e[i] > 0.f) {
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      if (e[j] > 0.f) {
+        const int i = id0 + j;
         const uint32_t x = philox_word0((uint32_t)i, step, (uint32_t)uid, (uint32_t)(uid >> 32), (uint32_t)seed,
                                         (uint32_t)(seed >> 32));
         const float uu = ((float)(x >> 9) + 0.5f) * 1.1920928955078125e-07f;   // (0,1), exact in fp32
-        const float sc = (e[i] / z) / (-logf(uu));
+        const float sc = (e[j] / z) / (-logf(uu));
         if (sc > best) { best = sc; bi = i; }
       }
     }
     block_argmax(best, bi, red);
     tok = bi;
   }
-  // ---- emit + bookkeeping (one thread)
+
   const bool fin = (tok == st.stop_token && !st.ignore_eos[b]) || n_prev + 1 >= st.max_out[b];
-  if (nx.res != nullptr) {
+  if (nx.res != nullptr && tid < 256) {
     // ---- next decode step's inputs (t3.py:503-514 + block_table.py:357-377): both pair members are
     // fed speech_emb[tok]; position = the slot this token's K/V will occupy.
     const int half = tid >> 7, r = half * B + b;
@@ -335,10 +365,10 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
                        : (int64_t)nx.bt[(int64_t)r * nx.bt_stride + p / CBX_BLOCK_SIZE] * CBX_BLOCK_SIZE + p % CBX_BLOCK_SIZE;
     }
   }
+  // ---- emit + bookkeeping (one thread)
   if (tid == 0) {
-    const int n = n_prev;
-    st.out_tokens[(size_t)b * st.out_stride + n] = tok;
-    st.n_out[b] = n + 1;
+    st.out_tokens[(size_t)b * st.out_stride + n_prev] = tok;
+    st.n_out[b] = n_prev + 1;
     st.last_tok[b] = tok;
     st.seen[(size_t)b * CBX_SEEN_WORDS + (tok >> 5)] |= 1u << (tok & 31);
     st.seq_len[b] = len_c + 1;
@@ -352,21 +382,11 @@ __global__ void __launch_bounds__(kThreads) cfg_sample_kernel(const bf16* __rest
 }  // namespace
 
 namespace cbx {
-int init_sample() {
-  static bool done = false;
-  if (done) return 0;
-  cudaError_t er = cudaFuncSetAttribute(cfg_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSampleSmem);
-  CBX_REQUIRE(er == cudaSuccess, "sampler smem attribute: %s", cudaGetErrorString(er));
-  done = true;
-  return 0;
-}
-}  // namespace cbx
+int init_sample() { return 0; }
 
-namespace cbx {
 int launch_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, const NextStep& nx, cudaStream_t s) {
   if (B <= 0) return 0;
-  if (init_sample()) return -1;
-  cudaError_t e = launch_pdl(cfg_sample_kernel, dim3(B), dim3(kThreads), kSampleSmem, s, (const bf16*)logits, *st, B, nx);
+  cudaError_t e = launch_pdl(cfg_sample_kernel, dim3(B), dim3(kThreads), 0, s, (const bf16*)logits, *st, B, nx);
   CBX_REQUIRE(e == cudaSuccess, "cfg_sample launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;

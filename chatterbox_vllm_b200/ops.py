@@ -92,12 +92,14 @@ def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: i
     return out
 
 
-def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5):
+def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5, qkv=None, h=None):
     """RMSNorm → QKV → RoPE → KV append.  Returns the qkv buffer [T,3072] whose first 1024 columns hold
     the rotated q (the k/v columns are not written: they went to the cache)."""
     T = res.shape[0]
-    qkv = torch.zeros(T, 3 * HIDDEN, dtype=BF16, device=res.device)
-    h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device) if T > 4 else None
+    if qkv is None:
+        qkv = torch.zeros(T, 3 * HIDDEN, dtype=BF16, device=res.device)
+    if h is None and T > 4:
+        h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device)
     check(load().cbx_layer_qkv(_p(res, BF16), _p(ln_w, BF16), _p(wqkv, BF16), _p(cos_sin, BF16), _p(pos, torch.int32),
                                _p(slot, torch.int64), _p(qkv), _p(kv_layer), _p(h), T, eps, _stream()), "layer_qkv")
     return qkv
@@ -111,19 +113,23 @@ def linear_residual(x, W, res):
     return res
 
 
-def layer_gate_up(res, ln_w, wgu_packed, eps: float = 1e-5):
+def layer_gate_up(res, ln_w, wgu_packed, eps: float = 1e-5, act=None, h=None):
     T = res.shape[0]
-    act = torch.empty(T, INTER, dtype=BF16, device=res.device)
-    h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device) if T > 4 else None
+    if act is None:
+        act = torch.empty(T, INTER, dtype=BF16, device=res.device)
+    if h is None and T > 4:
+        h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device)
     check(load().cbx_layer_gate_up(_p(res, BF16), _p(ln_w, BF16), _p(wgu_packed, BF16), _p(act), _p(h), T, eps,
                                    _stream()), "layer_gate_up")
     return act
 
 
-def head_logits(res, norm_w, whead, eps: float = 1e-5):
+def head_logits(res, norm_w, whead, eps: float = 1e-5, logits=None, h=None):
     T = res.shape[0]
-    logits = torch.zeros(T, LOGITS_LD, dtype=BF16, device=res.device)
-    h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device) if T > 4 else None
+    if logits is None:
+        logits = torch.zeros(T, LOGITS_LD, dtype=BF16, device=res.device)
+    if h is None and T > 4:
+        h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device)
     check(load().cbx_head_logits(_p(res, BF16), _p(norm_w, BF16), _p(whead, BF16), _p(logits), _p(h), T, eps,
                                  _stream()), "head_logits")
     return logits
