@@ -42,6 +42,8 @@ _PROTOS = {
     "cbx_pool_alloc": (C.c_int, [vp, C.c_int, C.POINTER(C.c_int32)]),
     "cbx_pool_free": (C.c_int, [vp, C.POINTER(C.c_int32), C.c_int]),
     "cbx_rmsnorm": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_rmsnorm_reduce": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_linear_partials": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "cbx_linear": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "cbx_pack_gate_up": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
     "cbx_rope_kv_append": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp]),

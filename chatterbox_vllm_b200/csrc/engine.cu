@@ -31,8 +31,7 @@ int gemm_residual(const void*, const void*, void*, int, int, int, cudaStream_t);
 int launch_decode_prepare(const void*, const int32_t*, const int32_t*, const int32_t*, const int32_t*, int, void*,
                           int32_t*, int64_t*, int32_t*, int32_t*, int32_t*, int, cudaStream_t);
 int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t);
-int paged_attn_decode_ex(const void*, const void*, const int32_t*, int, const int32_t*, const int32_t*, void*, void*,
-                         int32_t*, int, int, int, void*);
+int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t);
 }  // namespace cbx
 using namespace cbx;
 
@@ -60,16 +59,12 @@ struct cbx_engine {
   int32_t *pos, *kv_len, *row_seq, *head_rows, *attn_counters;
   int64_t* slot;
   void* attn_scratch;
-  // two-microbatch overlap (decode, T >= overlap_min_rows): the halves run on two streams so one
-  // half's latency-bound GEMMs hide under the other half's HBM-bound attention
-  void* attn_scratch2; int32_t* attn_counters2;
-  cudaStream_t aux = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-  int overlap_min_rows = 64, overlap_attn_ctas = 104;
+  float* part;                 // split-K partials [4][split_max_rows][1024] fp32
+  int split_max_rows = 512;
   int skip = 0;   // profiling aid (env CBX_SKIP bitmask: 1 qkv, 2 attn, 4 o, 8 gate_up, 16 down): results are garbage
   std::map<std::pair<int, int>, std::pair<cudaGraphExec_t, int64_t>> graphs;   // (B, kv bucket) -> exec, nodes
   int64_t last_launches;
   bf16* trace = nullptr;
-  int trace_rows = 0;
 };
 
 static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
@@ -91,8 +86,7 @@ static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
   p = take(R * 8); if (e) e->slot = (int64_t*)p;
   p = take(R * 4); if (e) e->attn_counters = (int32_t*)p;
   p = take((R + 1024) * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256); if (e) e->attn_scratch = p;
-  p = take(B2 * 4); if (e) e->attn_counters2 = (int32_t*)p;
-  p = take((B2 + 1024) * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256); if (e) e->attn_scratch2 = p;
+  p = take((size_t)4 * 512 * 1024 * 4); if (e) e->part = (float*)p;
   return off;
 }
 
@@ -118,26 +112,14 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   carve(cfg, e, (uint8_t*)workspace);
   // split-K attention tickets start at zero and reset themselves
   cudaMemset(e->attn_counters, 0, (size_t)cfg->max_rows * 4);
-  cudaMemset(e->attn_counters2, 0, (size_t)2 * cfg->max_pairs * 4);
   if (const char* v = getenv("CBX_SKIP")) e->skip = atoi(v);
-  if (const char* v = getenv("CBX_OVERLAP_MIN_ROWS")) e->overlap_min_rows = atoi(v);      // 0 disables
-  if (const char* v = getenv("CBX_OVERLAP_ATTN_CTAS")) e->overlap_attn_ctas = atoi(v);
-  if (cudaStreamCreateWithFlags(&e->aux, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming) != cudaSuccess) {
-    set_error("cbx_engine_create: stream/event creation failed");
-    delete e;
-    return nullptr;
-  }
+  if (const char* v = getenv("CBX_SPLIT_MAX_ROWS")) { e->split_max_rows = atoi(v); if (e->split_max_rows > 512) e->split_max_rows = 512; }
   return e;
 }
 
 extern "C" void cbx_engine_destroy(cbx_engine* e) {
   if (!e) return;
   for (auto& g : e->graphs) cudaGraphExecDestroy(g.second.first);
-  if (e->aux) cudaStreamDestroy(e->aux);
-  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
-  if (e->ev_join) cudaEventDestroy(e->ev_join);
   delete e;
 }
 
@@ -167,6 +149,10 @@ extern "C" int cbx_linear_residual(const void* x, const void* W, void* res, int 
   if (T <= 4) return gemv_residual(x, W, res, T, K, (cudaStream_t)stream);
   return gemm_residual(x, W, res, T, 1024, K, (cudaStream_t)stream);
 }
+extern "C" int cbx_linear_partials(const void* x, const void* W, void* partials, int T, int K, int splits, void* stream) {
+  if (T <= 0) return 0;
+  return gemm_partials(x, W, partials, T, 1024, K, splits, (cudaStream_t)stream);
+}
 extern "C" int cbx_layer_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, void* h_scratch, int T,
                                  float eps, void* stream) {
   if (T <= 0) return 0;
@@ -189,36 +175,55 @@ extern "C" int cbx_head_logits(const void* res, const void* norm_w, const void* 
 // Every projection that closes a residual branch adds into res in its epilogue, so a layer is
 //   T <= 4 (GEMV regime, 5 kernels): [norm+QKV+RoPE+KV-append] [attention] [O+res] [norm+gate_up+SiLU] [down+res]
 //   T  > 4 (tcgen05 regime, 7)     : [norm] [QKV+RoPE+KV-append] [attention] [O+res] [norm] [gate_up+SiLU] [down+res]
-static int forward_layers(cbx_engine* e, int r0, int T, int max_kv_len, cudaStream_t s, int attn_ctas = 148,
-                          bool second = false) {
+static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, bool final_norm) {
   const size_t layer_bytes = (size_t)e->cfg.num_blocks * CBX_PAGE_BYTES;
   const float eps = e->w.rms_eps;
-  bf16 *res = e->res + (size_t)r0 * 1024, *h = e->h + (size_t)r0 * 1024, *qkv = e->qkv + (size_t)r0 * 3072;
-  bf16 *attn = e->attn + (size_t)r0 * 1024, *act = e->act + (size_t)r0 * 4096;
-  void* scratch = second ? e->attn_scratch2 : e->attn_scratch;
-  int32_t* counters = second ? e->attn_counters2 : e->attn_counters;
+  const int sk = e->skip;
+  // split-K for the two N = 1024 projections when their 16 column tiles would leave most SMs idle
+  const int m_tiles = (T + 127) / 128;
+  int splits = 1;
+  if (T > 4 && !e->trace && T <= e->split_max_rows) splits = m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1);
+  bool pending = false;                                // down-proj partials not yet folded into res
   for (int li = 0; li < e->w.n_layers; ++li) {
     uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;
-    const int sk = e->skip;
-    if (!(sk & 1) && cbx_layer_qkv(res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos + r0, e->slot + r0, qkv, kv, h, T, eps, s)) return -1;
-    if (!(sk & 2) && paged_attn_decode_ex(qkv, kv, e->block_table, e->bt_stride, e->row_seq + r0, e->kv_len + r0, attn, scratch,
-                             counters, T, max_kv_len, attn_ctas, s)) return -1;
-    if (!(sk & 4) && cbx_linear_residual(attn, e->wo[li], res, T, 1024, s)) return -1;
-    if (!(sk & 8) && cbx_layer_gate_up(res, e->ln2[li], e->wgu[li], act, h, T, eps, s)) return -1;
-    if (!(sk & 16) && cbx_linear_residual(act, e->wd[li], res, T, 4096, s)) return -1;
+    if (T <= 4) {
+      if (!(sk & 1) && gemv_qkv_rope(e->res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos, e->slot, e->qkv, kv, T, eps, s)) return -1;
+    } else {
+      if (pending ? cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln1[li], e->h, T, eps, s)
+                  : cbx_rmsnorm(e->res, nullptr, e->ln1[li], e->h, T, eps, s)) return -1;
+      pending = false;
+      if (!(sk & 1) && gemm_qkv_rope(e->h, e->wqkv[li], e->qkv, e->w.cos_sin, e->pos, e->slot, kv, T, s)) return -1;
+    }
+    if (!(sk & 2) && cbx_paged_attn_decode(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
+                                           e->attn_scratch, e->attn_counters, T, max_kv_len, s)) return -1;
+    if (T <= 4) {
+      if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s)) return -1;
+      if (!(sk & 8) && gemv_norm_gate_up(e->res, e->ln2[li], e->wgu[li], e->act, T, eps, s)) return -1;
+      if (!(sk & 16) && gemv_residual(e->act, e->wd[li], e->res, T, 4096, s)) return -1;
+    } else if (splits > 1) {
+      if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s)) return -1;
+      if (cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
+      if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s)) return -1;
+      if (!(sk & 16) && gemm_partials(e->act, e->wd[li], e->part, T, 1024, 4096, splits, s)) return -1;
+      pending = true;
+    } else {
+      if (!(sk & 4) && gemm_residual(e->attn, e->wo[li], e->res, T, 1024, 1024, s)) return -1;
+      if (cbx_rmsnorm(e->res, nullptr, e->ln2[li], e->h, T, eps, s)) return -1;
+      if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s)) return -1;
+      if (!(sk & 16) && gemm_residual(e->act, e->wd[li], e->res, T, 1024, 4096, s)) return -1;
+    }
     if (e->trace)
-      cudaMemcpyAsync(e->trace + ((size_t)li * e->trace_rows + r0) * CBX_HIDDEN, res, (size_t)T * CBX_HIDDEN * 2,
+      cudaMemcpyAsync(e->trace + (size_t)li * T * CBX_HIDDEN, e->res, (size_t)T * CBX_HIDDEN * 2,
                       cudaMemcpyDeviceToDevice, s);
   }
+  if (pending) return cbx_rmsnorm_reduce(e->part, splits, e->res, e->w.norm, e->h, T, eps, s);
+  if (final_norm || T > 4) return cbx_rmsnorm(e->res, nullptr, e->w.norm, e->h, T, eps, s);
   return 0;
 }
 
 extern "C" int cbx_engine_forward(cbx_engine* e, int T, int max_kv_len, void* stream) {
   CBX_REQUIRE(T >= 1 && T <= e->cfg.max_rows, "cbx_engine_forward: T=%d out of range", T);
-  cudaStream_t s = (cudaStream_t)stream;
-  e->trace_rows = T;
-  if (forward_layers(e, 0, T, max_kv_len, s)) return -1;
-  return cbx_rmsnorm(e->res, nullptr, e->w.norm, e->h, T, e->w.rms_eps, s);
+  return forward_layers(e, T, max_kv_len, (cudaStream_t)stream, true);
 }
 
 extern "C" int cbx_engine_set_trace(cbx_engine* e, void* trace) {
@@ -250,17 +255,11 @@ extern "C" int cbx_engine_sample(cbx_engine* e, int B, void* stream) {
 // One decode step for pair slots [0,B): inputs were staged by the previous sampler launch.
 static int decode_step(cbx_engine* e, int B, int max_kv_len, cudaStream_t s) {
   const int T = 2 * B;
-  e->trace_rows = T;
-  if (e->overlap_min_rows > 0 && T >= e->overlap_min_rows && !e->trace) {
-    // cond rows [0,B) on s, uncond rows [B,2B) on the aux stream; join before the head
-    CBX_REQUIRE(cudaEventRecord(e->ev_fork, s) == cudaSuccess && cudaStreamWaitEvent(e->aux, e->ev_fork, 0) == cudaSuccess,
-                "decode_step: fork failed");
-    if (forward_layers(e, 0, B, max_kv_len, s, e->overlap_attn_ctas, false)) return -1;
-    if (forward_layers(e, B, B, max_kv_len, e->aux, e->overlap_attn_ctas, true)) return -1;
-    CBX_REQUIRE(cudaEventRecord(e->ev_join, e->aux) == cudaSuccess && cudaStreamWaitEvent(s, e->ev_join, 0) == cudaSuccess,
-                "decode_step: join failed");
-  } else if (forward_layers(e, 0, T, max_kv_len, s)) return -1;
-  if (cbx_head_logits(e->res, e->w.norm, e->w.speech_head, e->logits, e->h, T, e->w.rms_eps, s)) return -1;
+  if (forward_layers(e, T, max_kv_len, s, false)) return -1;
+  if (T <= 4) {                                         // final norm fused into the head GEMV
+    if (gemv_norm_head(e->res, e->w.norm, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD,
+                       e->w.rms_eps, s)) return -1;
+  } else if (gemm_bf16_tc(e->h, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1;
   return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s);
 }
 

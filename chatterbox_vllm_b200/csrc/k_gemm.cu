@@ -17,6 +17,7 @@
 // k-blocks before griddepcontrol.wait, so the weight stream overlaps the previous kernel's tail;
 // activation tiles follow after the wait.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <map>
 #include <tuple>
@@ -58,7 +59,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
-  const int n_kb = K / BK;
+  const int n_kb = K / BK / gridDim.z;                 // k-blocks of this CTA's K slice (split-K over blockIdx.z)
+  const int kb0 = blockIdx.z * n_kb;
 
   pdl_trigger();
   if (warp == 0 && lane == 0) {
@@ -81,22 +83,27 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 
   if (warp == 0) {
     if (lane == 0) {
+      // Each CTA walks K starting at a different k-block (rotated by its tile index): all CTAs of a
+      // row of tiles read the SAME activation k-slices, and in lockstep they would hammer the same
+      // few L2 slices; the rotation spreads them over the whole activation panel.
+      const int rot = (blockIdx.x + blockIdx.y * 7) % n_kb;
+      auto kc = [&](int kb) { int k = kb + rot; return kb0 + (k >= n_kb ? k - n_kb : k); };
       // weights of the first ring fill do not depend on the previous kernel
       const int n_pre = n_kb < C::kStages ? n_kb : C::kStages;
       for (int kb = 0; kb < n_pre; ++kb) {
         mbar_arrive_expect_tx(&full[kb], C::kStageBytes);
-        tma_load_2d(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kb * BK, n0, &full[kb]);
+        tma_load_2d(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kc(kb) * BK, n0, &full[kb]);
       }
       pdl_wait();
       for (int kb = 0; kb < n_pre; ++kb)
-        tma_load_2d(smem + kb * C::kStageBytes, &tma_a, kb * BK, m0, &full[kb]);
+        tma_load_2d(smem + kb * C::kStageBytes, &tma_a, kc(kb) * BK, m0, &full[kb]);
       for (int kb = n_pre; kb < n_kb; ++kb) {
         const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_arrive_expect_tx(&full[s], C::kStageBytes);
         uint8_t* sa = smem + s * C::kStageBytes;
-        tma_load_2d(sa, &tma_a, kb * BK, m0, &full[s]);
-        tma_load_2d(sa + C::kABytes, &tma_b, kb * BK, n0, &full[s]);
+        tma_load_2d(sa, &tma_a, kc(kb) * BK, m0, &full[s]);
+        tma_load_2d(sa + C::kABytes, &tma_b, kc(kb) * BK, n0, &full[s]);
       }
     } else {
       pdl_wait();
@@ -201,6 +208,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
             dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
           }
+        } else if (EPI == 4) {
+          // split-K partial: fp32 [gridDim.z][M][N] behind y (N % 32 == 0); summed by cbx_rmsnorm_reduce
+          float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(y) + ((size_t)blockIdx.z * M + row) * N + col);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            dst[i] = make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
+                                 __uint_as_float(r[4 * i + 3]));
         } else if (EPI == 3) {
           // residual stream in place: res = bf16(bf16(acc) + res)   (N % 32 == 0)
           uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + col);
@@ -292,7 +306,7 @@ int init_gemm() {
   static bool done = false;
   if (done) return 0;
   if (set_attr<64, 0>() || set_attr<64, 1>() || set_attr<128, 0>() || set_attr<128, 1>() || set_attr<64, 2>() ||
-      set_attr<64, 3>() || set_attr<128, 3>()) return -1;
+      set_attr<64, 3>() || set_attr<128, 3>() || set_attr<64, 4>()) return -1;
   CBX_REQUIRE(get_encode() != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   done = true;
   return 0;
@@ -301,13 +315,13 @@ int init_gemm() {
 namespace {
 template <int BN, int EPI>
 int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s,
-           const EpiArgs& ea = EpiArgs()) {
+           const EpiArgs& ea = EpiArgs(), int splits = 1) {
   using C = Cfg<BN>;
   if (cbx::init_gemm()) return -1;
   CUtensorMap ma, mb;
   if (make_map(&ma, x, M, K, BM)) return -1;
   if (make_map(&mb, W, N, K, BN)) return -1;
-  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
+  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
   cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI>, grid, dim3(kThreads), C::kSmem, s, ma, mb, (bf16*)y, M, N, K,
                              ldy, ea);
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc launch failed: %s", cudaGetErrorString(e));
@@ -325,7 +339,10 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
   CBX_REQUIRE(epilogue == 0 || N % 32 == 0, "gemm_tc: SiLU epilogue needs N %% 32 == 0");
   // Narrow tiles when the grid would leave most of the 148 SMs idle.
   const int m_tiles = (M + BM - 1) / BM;
-  const bool narrow = (int64_t)m_tiles * ((N + 127) / 128) < 148;
+  // 64-wide tiles only when 128-wide ones would leave a third of the SMs idle: the GEMMs of this
+  // path are bound by L2->SM bytes, which a 128 x 128 tile halves per output element.
+  bool narrow = (int64_t)m_tiles * ((N + 127) / 128) < 100;
+  if (const char* v = getenv("CBX_GEMM_BN")) narrow = atoi(v) == 64;      // tuning aid
   if (epilogue == 1) return narrow ? launch<64, 1>(x, W, y, M, N, K, ldy, s) : launch<128, 1>(x, W, y, M, N, K, ldy, s);
   return narrow ? launch<64, 0>(x, W, y, M, N, K, ldy, s) : launch<128, 0>(x, W, y, M, N, K, ldy, s);
 }
@@ -340,6 +357,11 @@ int gemm_residual(const void* x, const void* W, void* res, int M, int N, int K, 
   CBX_REQUIRE(N % 128 == 0 && K % BK == 0, "gemm_residual: bad shape N=%d K=%d", N, K);
   const bool narrow = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
   return narrow ? launch<64, 3>(x, W, res, M, N, K, N, s) : launch<128, 3>(x, W, res, M, N, K, N, s);
+}
+// EPI 4: part[splits][M][N] fp32 = per-K-slice partial products (no rounding); N % 64 == 0.
+int gemm_partials(const void* x, const void* W, void* part, int M, int N, int K, int splits, cudaStream_t s) {
+  CBX_REQUIRE(N % 64 == 0 && splits >= 1 && K % (BK * splits) == 0, "gemm_partials: bad shape N=%d K=%d splits=%d", N, K, splits);
+  return launch<64, 4>(x, W, part, M, N, K, N, s, EpiArgs(), splits);
 }
 int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
 }  // namespace cbx

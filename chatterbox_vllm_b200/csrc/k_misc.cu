@@ -163,17 +163,34 @@ extern "C" int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, con
 // ---------------------------------------------------------------- (add +) RMSNorm -----
 // One CTA of 128 threads per row; each thread owns 8 contiguous elements (one 16-byte
 // load).  Rounding points follow vLLM: z = bf16(x + res); out = bf16(bf16(z·rstd)·w).
-template <bool kAdd>
+// MODE 0: out = norm(x).  MODE 1: res = bf16(x + res) in place, out = norm(res).
+// MODE 2: x arrives as `splits` fp32 split-K partials [splits][T][1024] of the projection that
+//         closes the residual branch: x = bf16(sum of partials), then as MODE 1.
+template <int MODE>
 __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* __restrict__ x, uint4* __restrict__ res,
                                                       const uint4* __restrict__ w, uint4* __restrict__ out,
-                                                      float eps) {
+                                                      float eps, int splits, int T) {
   const int r = blockIdx.x, t = threadIdx.x;
   pdl_trigger();
   const uint4 wv = w[t];                               // weights: independent of the previous kernel
   pdl_wait();
-  uint4 v = x[(size_t)r * 128 + t];
-  float f[8] = {bf_lo(v.x), bf_hi(v.x), bf_lo(v.y), bf_hi(v.y), bf_lo(v.z), bf_hi(v.z), bf_lo(v.w), bf_hi(v.w)};
-  if (kAdd) {
+  float f[8];
+  if (MODE == 2) {
+    const float4* p = reinterpret_cast<const float4*>(x) + ((size_t)r * 128 + t) * 2;
+    float4 a = p[0], b = p[1];
+    for (int z = 1; z < splits; ++z) {
+      const float4 a2 = p[(size_t)z * T * 256], b2 = p[(size_t)z * T * 256 + 1];
+      a.x += a2.x; a.y += a2.y; a.z += a2.z; a.w += a2.w;
+      b.x += b2.x; b.y += b2.y; b.z += b2.z; b.w += b2.w;
+    }
+    f[0] = round_bf16(a.x); f[1] = round_bf16(a.y); f[2] = round_bf16(a.z); f[3] = round_bf16(a.w);
+    f[4] = round_bf16(b.x); f[5] = round_bf16(b.y); f[6] = round_bf16(b.z); f[7] = round_bf16(b.w);
+  } else {
+    const uint4 v = x[(size_t)r * 128 + t];
+    f[0] = bf_lo(v.x); f[1] = bf_hi(v.x); f[2] = bf_lo(v.y); f[3] = bf_hi(v.y);
+    f[4] = bf_lo(v.z); f[5] = bf_hi(v.z); f[6] = bf_lo(v.w); f[7] = bf_hi(v.w);
+  }
+  if (MODE >= 1) {
     uint4 q = res[(size_t)r * 128 + t];
     float g[8] = {bf_lo(q.x), bf_hi(q.x), bf_lo(q.y), bf_hi(q.y), bf_lo(q.z), bf_hi(q.z), bf_lo(q.w), bf_hi(q.w)};
 #pragma unroll
@@ -200,12 +217,22 @@ extern "C" int cbx_rmsnorm(const void* x, void* residual, const void* w, void* o
   if (T <= 0) return 0;
   cudaError_t e;
   if (residual)
-    e = launch_pdl(rmsnorm_kernel<true>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)x,
-                   (uint4*)residual, (const uint4*)w, (uint4*)out, eps);
+    e = launch_pdl(rmsnorm_kernel<1>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)x,
+                   (uint4*)residual, (const uint4*)w, (uint4*)out, eps, 1, T);
   else
-    e = launch_pdl(rmsnorm_kernel<false>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)x,
-                   (uint4*)nullptr, (const uint4*)w, (uint4*)out, eps);
+    e = launch_pdl(rmsnorm_kernel<0>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)x,
+                   (uint4*)nullptr, (const uint4*)w, (uint4*)out, eps, 1, T);
   CBX_REQUIRE(e == cudaSuccess, "rmsnorm launch failed: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
+extern "C" int cbx_rmsnorm_reduce(const void* partials, int splits, void* residual, const void* w, void* out, int T,
+                                  float eps, void* stream) {
+  if (T <= 0) return 0;
+  CBX_REQUIRE(splits >= 1 && residual != nullptr, "cbx_rmsnorm_reduce: bad arguments");
+  cudaError_t e = launch_pdl(rmsnorm_kernel<2>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)partials,
+                             (uint4*)residual, (const uint4*)w, (uint4*)out, eps, splits, T);
+  CBX_REQUIRE(e == cudaSuccess, "rmsnorm_reduce launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
 }

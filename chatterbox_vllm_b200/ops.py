@@ -113,6 +113,23 @@ def linear_residual(x, W, res):
     return res
 
 
+def linear_partials(x, W, splits: int):
+    """fp32 [splits, T, 1024] split-K partial products of x·Wᵀ."""
+    T, K = x.shape
+    part = torch.empty(splits, T, HIDDEN, dtype=torch.float32, device=x.device)
+    check(load().cbx_linear_partials(_p(x, BF16), _p(W, BF16), _p(part), T, K, splits, _stream()), "linear_partials")
+    return part
+
+
+def rmsnorm_reduce(part, res, w, eps: float = 1e-5):
+    """res = bf16(bf16(Σ part) + res) in place; returns norm(res)·w."""
+    splits, T, _ = part.shape
+    out = torch.empty_like(res)
+    check(load().cbx_rmsnorm_reduce(_p(part, torch.float32), splits, _p(res, BF16), _p(w, BF16), _p(out), T, eps,
+                                    _stream()), "rmsnorm_reduce")
+    return out
+
+
 def layer_gate_up(res, ln_w, wgu_packed, eps: float = 1e-5, act=None, h=None):
     T = res.shape[0]
     if act is None:
@@ -220,6 +237,6 @@ class BlockPool:
 
 
 __all__ = ["slot_mapping", "rmsnorm", "pack_gate_up", "linear", "rope_kv_append", "paged_attn_decode",
-           "layer_qkv", "linear_residual", "layer_gate_up", "head_logits",
+           "layer_qkv", "linear_residual", "linear_partials", "rmsnorm_reduce", "layer_gate_up", "head_logits",
            "SamplerBuffers", "cfg_sample", "decode_prepare", "prefill_embed", "BlockPool", "BLOCK_SIZE", "HIDDEN",
            "INTER", "LOGITS_LD", "PAGE_BYTES", "SEEN_WORDS", "SPEECH_VOCAB", "_lib"]

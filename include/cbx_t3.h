@@ -64,6 +64,16 @@ int       cbx_pool_free(cbx_pool*, const int32_t* ids, int n); /* appended in th
  * out = norm(residual)·w.  x,out,residual [T,1024]; w [1024]. */
 int cbx_rmsnorm(const void* x, void* residual, const void* w, void* out, int T, float eps, void* stream);
 
+/* Split-K form of the fused add + RMSNorm: the projection that closes a residual branch left
+ * `splits` fp32 partial products partials[splits][T][1024] (cbx_linear_partials); this folds them:
+ * residual = bf16(bf16(sum of partials) + residual) in place, out = norm(residual)·w. */
+int cbx_rmsnorm_reduce(const void* partials, int splits, void* residual, const void* w, void* out, int T,
+                       float eps, void* stream);
+/* partials[z][T][1024] (fp32) = x[:, Kz]·W[:, Kz]^T for the z-th of `splits` equal K slices
+ * (tcgen05 GEMM, one grid.z slice per split; K % (64·splits) == 0).  Used for o_proj / down_proj
+ * at decode batch sizes, where 16 column tiles alone would leave most of the 148 SMs idle. */
+int cbx_linear_partials(const void* x, const void* W, void* partials, int T, int K, int splits, void* stream);
+
 /* y[T,N] = x[T,K] · W[N,K]^T (bf16 in, fp32 accumulate, bf16 out).  Replaces the
  * cuBLAS GEMMs behind vllm llama.py:117-120,221,225 and t3.py:729-730.
  * epilogue: 0 = store; 1 = SiLU(gate)·up with W packed by cbx_pack_gate_up (y is [T,N/2]);

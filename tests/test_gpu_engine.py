@@ -223,12 +223,12 @@ def test_engine_greedy_stream_matches_oracle_2layers(ops, use_graph):
     eng.close()
 
 
-@pytest.mark.parametrize("overlap", ["64", "0"])
-def test_engine_two_microbatch_overlap_parity(ops, overlap, monkeypatch):
-    """T = 64 rows: the decode step runs cond and uncond rows as two microbatches on two streams
-    (attention of one overlapping the GEMMs of the other).  Same parity bar as the single-stream
-    step, with and without CUDA-graph replay of the forked step."""
-    monkeypatch.setenv("CBX_OVERLAP_MIN_ROWS", overlap)
+@pytest.mark.parametrize("split_rows", ["512", "0"])
+def test_engine_batch32_split_k_parity(ops, split_rows, monkeypatch):
+    """T = 64 rows (tcgen05 regime): o_proj / down_proj run as split-K partials folded by the next
+    add + RMSNorm kernel (default) or unsplit with the residual epilogue (CBX_SPLIT_MAX_ROWS=0).
+    Same parity bar either way, with and without CUDA-graph replay."""
+    monkeypatch.setenv("CBX_SPLIT_MAX_ROWS", split_rows)
     n_steps = 10
     for use_graph in (True, False):
         cfg, w, eng = _mk_engine(2, 32, use_graph=use_graph)

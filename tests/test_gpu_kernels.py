@@ -314,3 +314,25 @@ def test_head_logits_fused_final_norm(ops, T):
     lg = ops.head_logits(dev(res), dev(nw), dev(Wh))
     h = rmsnorm(res.float(), nw, 1e-5, "bf16")
     assert_close_bf16(lg[:, :8194], _ref_linear(h, Wh), ulps=2.0, atol=0.02, what=f"head T={T}")
+
+
+@pytest.mark.parametrize("T,K,splits", [(5, 1024, 4), (256, 1024, 4), (256, 4096, 4), (300, 4096, 2), (128, 4096, 1)])
+def test_split_k_partials_and_reduce_norm(ops, T, K, splits):
+    """o_proj / down_proj as split-K partials folded by the following add + RMSNorm kernel: same
+    rounding points as the unsplit chain (bf16(y), bf16(y + res), norm)."""
+    g = torch.Generator().manual_seed(T + K + splits)
+    x = torch.randn(T, K, generator=g).to(BF16)
+    W = (torch.randn(1024, K, generator=g) * 0.03).to(BF16)
+    res = (torch.randn(T, 1024, generator=g) * 2).to(BF16)
+    w = (1 + 0.1 * torch.randn(1024, generator=g)).to(BF16)
+    part = ops.linear_partials(dev(x), dev(W), splits)
+    y64 = x.double() @ W.double().T
+    assert (part.double().sum(0).cpu() - y64).abs().max() < 2e-3, "partials must sum to the full product"
+    r = dev(res.clone())
+    out = ops.rmsnorm_reduce(part, r, dev(w))
+    y = y64.float().to(BF16).float()
+    want_res = (y + res.float()).to(BF16).float()
+    err = (r.float().cpu() - want_res).abs()
+    assert (err <= 2.0 * ULP * y.abs() + 1.01 * ULP * want_res.abs() + 1e-6).all(), f"res max err {err.max():.3e}"
+    # the norm is checked on the kernel's own residual (so only the norm's rounding is in play)
+    assert_close_bf16(out, rmsnorm(r.float().cpu(), w, 1e-5, "bf16"), ulps=1.01, what="norm after reduce")
