@@ -277,7 +277,10 @@ def main():
     attn_bytes = 2 * B * (mean_ctx * (KV_TOKEN_BYTES // 30) + 2048 + 2048)
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "attn_traffic.json")))["dram_bytes_per_launch"]
+        # ncu --set full capture of this kernel (profiles/): measured DRAM bytes ÷ algorithmic bytes of the
+        # captured launch, applied to this run's launch shape (the capture uses a shorter context)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "attn_traffic.json")))
+        traffic = attn_bytes * tr["dram_bytes_per_launch"] / tr["algorithmic_bytes_same_launch"]
     except Exception:
         pass
     step_bytes = W_BYTES + 2 * B * (KV_TOKEN_BYTES * (mean_ctx + 1) + KV_TOKEN_BYTES + 2048)

@@ -14,6 +14,8 @@
 //             x 16-byte chunk), mbarrier hand-back of the stage.
 // Partial (o, m, l) per (row, split) go to scratch; the CTA that publishes a row's LAST partial
 // (atomic ticket per row) merges them in the same launch — no second kernel.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 using namespace cbx;
@@ -228,6 +230,154 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
 }
 
 
+// ---------------------------------------------------------------------------------------------
+// Small-batch variant (T <= 4 rows: the 1-2 CFG-pair latency regime).  One CTA per (row, head,
+// split); the S splits of a (row, head) form a thread-block cluster and merge their partial
+// (m, l, o) through distributed shared memory — no global round trip, no ticket, no second
+// launch.  A head's K (2 KB) and V (2 KB) of a page are contiguous, so each page costs the CTA two
+// 2 KB bulk copies; all of a CTA's pages are requested up front (<= 32 pages = 128 KB in flight).
+constexpr int kSmallWarps = 4;
+constexpr int kSmallMaxPages = 32;                    // local pages per CTA
+constexpr int kSmallSmem = kSmallMaxPages * 4096 + kSmallMaxPages * 8 + kSmallWarps * 68 * 4 + 16;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(const float* local, uint32_t rank) {
+  uint32_t ra; float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local)), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+  return v;
+}
+
+template <int S>
+__global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
+    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt, int bt_stride,
+    const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len, bf16* __restrict__ out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmallMaxPages * 4096);
+  float* red = reinterpret_cast<float*>(bars + kSmallMaxPages);   // [4 warps][68]: o[64], m, l
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = S > 1 ? (int)cluster_ctarank() : 0;            // == blockIdx.x (cluster spans grid.x)
+  const int h = blockIdx.y, row = blockIdx.z;
+
+  pdl_trigger();
+  if (threadIdx.x < kSmallMaxPages) mbar_init(&bars[threadIdx.x], 1);
+  fence_barrier_init();
+  __syncthreads();
+  pdl_wait();
+
+  const int len = kv_len[row];
+  const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+  const int n_local = n_pages > rank ? (n_pages - rank + S - 1) / S : 0;   // pages rank, rank+S, ...
+  if (warp == 0 && lane < n_local) {
+    const int blk = bt[(int64_t)row_seq[row] * bt_stride + rank + lane * S];
+    const uint8_t* src = kv_layer + (size_t)blk * CBX_PAGE_BYTES + h * 2048;
+    mbar_arrive_expect_tx(&bars[lane], 4096);
+    bulk_g2s(smem + lane * 4096, src, 2048, &bars[lane]);
+    bulk_g2s(smem + lane * 4096 + 2048, src + 32768, 2048, &bars[lane]);
+  }
+  const int t16 = lane & 15, half = lane >> 4;        // QK mapping
+  const int tg = lane >> 3, c = lane & 7;             // PV mapping
+  const float qscale = 0.125f * kLog2e;
+  float q[32];
+  {
+    const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 v = qp[i];
+      q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
+      q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
+      q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
+      q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
+    }
+  }
+  float m = -INFINITY, l = 0.f, acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int j = warp; j < n_local; j += kSmallWarps) {
+    mbar_wait(&bars[j], 0);
+    const uint8_t* kt = smem + j * 4096;
+    const uint8_t* vt = kt + 2048;
+    float sc = 0.f;
+    {
+      const uint4* kr = reinterpret_cast<const uint4*>(kt + t16 * 128);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint4 v = kr[(half * 4 + i) ^ (t16 & 7)];
+        sc = fmaf(q[i * 8 + 0], bf_lo(v.x), sc); sc = fmaf(q[i * 8 + 1], bf_hi(v.x), sc);
+        sc = fmaf(q[i * 8 + 2], bf_lo(v.y), sc); sc = fmaf(q[i * 8 + 3], bf_hi(v.y), sc);
+        sc = fmaf(q[i * 8 + 4], bf_lo(v.z), sc); sc = fmaf(q[i * 8 + 5], bf_hi(v.z), sc);
+        sc = fmaf(q[i * 8 + 6], bf_lo(v.w), sc); sc = fmaf(q[i * 8 + 7], bf_hi(v.w), sc);
+      }
+    }
+    sc += __shfl_xor_sync(0xffffffffu, sc, 16);
+    const int n_valid = len - (rank + j * S) * CBX_BLOCK_SIZE;
+    sc = (t16 < n_valid) ? sc : -INFINITY;
+    float mt = sc;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, o));
+    const float m_new = fmaxf(m, mt);
+    const float p = exp2f(sc - m_new);
+    const float corr = exp2f(m - m_new);
+    m = m_new;
+    l = fmaf(l, corr, p);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] *= corr;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int tok = tg * 4 + i;
+      const float pt = __shfl_sync(0xffffffffu, p, tok);
+      if (tok < n_valid) {
+        const uint4 v = reinterpret_cast<const uint4*>(vt + tok * 128)[c];
+        acc[0] = fmaf(pt, bf_lo(v.x), acc[0]); acc[1] = fmaf(pt, bf_hi(v.x), acc[1]);
+        acc[2] = fmaf(pt, bf_lo(v.y), acc[2]); acc[3] = fmaf(pt, bf_hi(v.y), acc[3]);
+        acc[4] = fmaf(pt, bf_lo(v.z), acc[4]); acc[5] = fmaf(pt, bf_hi(v.z), acc[5]);
+        acc[6] = fmaf(pt, bf_lo(v.w), acc[6]); acc[7] = fmaf(pt, bf_hi(v.w), acc[7]);
+      }
+    }
+  }
+  // ---- warp partial -> shared memory
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+  }
+  const float lsum = warp_sum(l) * 0.5f;
+  float* mine = red + warp * 68;
+  if (lane < 8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mine[lane * 8 + i] = acc[i];
+  }
+  if (lane == 0) { mine[64] = m; mine[65] = lsum; }
+  __syncthreads();
+  if (S > 1) cluster_sync_all();
+  // ---- merge the S x 4 warp partials (cluster rank 0, one thread per output dim)
+  if (rank == 0 && threadIdx.x < 64) {
+    const int d = threadIdx.x;
+    float mx = -INFINITY;
+    for (int r = 0; r < S; ++r)
+      for (int w = 0; w < kSmallWarps; ++w) mx = fmaxf(mx, S > 1 ? ld_dsmem_f32(red + w * 68 + 64, r) : red[w * 68 + 64]);
+    float o = 0.f, lt = 0.f;
+    if (mx > -INFINITY) {
+      for (int r = 0; r < S; ++r)
+        for (int w = 0; w < kSmallWarps; ++w) {
+          const float* pw = red + w * 68;
+          const float pm = S > 1 ? ld_dsmem_f32(pw + 64, r) : pw[64];
+          if (pm == -INFINITY) continue;
+          const float wgt = exp2f(pm - mx);
+          o = fmaf(wgt, S > 1 ? ld_dsmem_f32(pw + d, r) : pw[d], o);
+          lt = fmaf(wgt, S > 1 ? ld_dsmem_f32(pw + 65, r) : pw[65], lt);
+        }
+      o /= lt;
+    }
+    const float o2 = __shfl_down_sync(0xffffffffu, o, 1);
+    if ((d & 1) == 0) *reinterpret_cast<uint32_t*>(out + (size_t)row * CBX_HIDDEN + h * 64 + d) = pack_bf16(o, o2);
+  }
+  if (S > 1) cluster_sync_all();                       // peers' shared memory stays alive until rank 0 has read it
+}
+
 // Combine split partials: 256 threads per row, thread = 4 consecutive d of one head.
 __global__ void __launch_bounds__(256) attn_merge_kernel(const float* __restrict__ o_part,
                                                          const float2* __restrict__ ml_part,
@@ -266,6 +416,12 @@ int init_attn() {
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(paged_attn_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(paged_attn_small_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmem);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(paged_attn_small_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmem);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(paged_attn_small_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmem);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   done = true;
   return 0;
 }
@@ -295,6 +451,23 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
                               int32_t* counters, int T, int max_kv_len, int max_ctas, void* stream) {
   if (T <= 0) return 0;
   if (cbx::init_attn()) return -1;
+  {
+    // small-batch path: clusters of S splits per (row, head)
+    static const bool small_on = !(getenv("CBX_ATTN_SMALL") && getenv("CBX_ATTN_SMALL")[0] == '0');
+    const int max_pages = (max_kv_len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+    const int S = T <= 2 ? 4 : 2;
+    if (small_on && T <= 4 && max_pages <= kSmallMaxPages * S) {
+      cudaStream_t st = (cudaStream_t)stream;
+      dim3 grid(S, CBX_HEADS, T), block(kSmallWarps * 32);
+      cudaError_t e = S == 4 ? launch_pdl_cluster(paged_attn_small_kernel<4>, grid, block, kSmallSmem, st, S, (const bf16*)qkv,
+                                                  (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out)
+                             : launch_pdl_cluster(paged_attn_small_kernel<2>, grid, block, kSmallSmem, st, S, (const bf16*)qkv,
+                                                  (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out);
+      CBX_REQUIRE(e == cudaSuccess, "paged_attn_small launch failed: %s", cudaGetErrorString(e));
+      count_launch();
+      return 0;
+    }
+  }
   const AttnPlan p = make_plan(T, max_kv_len);
   float* o_part = reinterpret_cast<float*>(scratch);
   float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)T * p.nsplit * CBX_HIDDEN);
