@@ -97,6 +97,24 @@ __device__ __forceinline__ uint4 ld_stream(const void* p) {
   return r;
 }
 
+// L2 prefetch of this CTA's share of [base, base+bytes): thread 0 of every CTA issues bulk
+// prefetches (SASS UBLKPF) for a 1/gridDim slice.  Used to pull the NEXT kernel's weights into the
+// 126 MB L2 while the current kernel runs, so the weight stream does not stop at kernel boundaries.
+__device__ __forceinline__ void l2_prefetch_slice(const void* base, size_t bytes) {
+  if (base == nullptr || threadIdx.x != 0) return;
+  const size_t n_cta = (size_t)gridDim.x * gridDim.y * gridDim.z;
+  const size_t cta = blockIdx.x + (size_t)gridDim.x * (blockIdx.y + (size_t)gridDim.y * blockIdx.z);
+  size_t per = ((bytes + n_cta - 1) / n_cta + 127) & ~(size_t)127;
+  size_t off = cta * per;
+  if (off >= bytes) return;
+  if (off + per > bytes) per = (bytes - off) & ~(size_t)15;
+  const char* p = reinterpret_cast<const char*>(base) + off;
+  for (size_t o = 0; o < per; o += 32768) {
+    const uint32_t n = (uint32_t)(per - o < 32768 ? per - o : 32768);
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p + o), "r"(n) : "memory");
+  }
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -21,9 +21,11 @@ int init_attn();
 int init_sample();
 int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
 int gemv_qkv_rope(const void*, const void*, const void*, const void*, const int32_t*, const int64_t*, void*, void*, int,
-                  float, cudaStream_t);
-int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t);
-int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, cudaStream_t);
+                  float, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0);
+int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0);
+int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, cudaStream_t, const void* next_w = nullptr,
+                      size_t next_bytes = 0);
+void attn_set_prefetch(const void*, size_t);
 int gemv_norm_head(const void*, const void*, const void*, void*, int, int, int, float, cudaStream_t);
 int gemm_bf16_tc(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
 int gemm_qkv_rope(const void*, const void*, void*, const void*, const int32_t*, const int64_t*, void*, int, cudaStream_t);
@@ -61,6 +63,7 @@ struct cbx_engine {
   void* attn_scratch;
   float* part;                 // split-K partials [4][split_max_rows][1024] fp32
   int split_max_rows = 512;
+  bool l2_prefetch = false;  // measured: no gain at b=1 (L2->SM bandwidth ~ HBM bandwidth on B200); env CBX_L2_PREFETCH=1 enables
   int skip = 0;   // profiling aid (env CBX_SKIP bitmask: 1 qkv, 2 attn, 4 o, 8 gate_up, 16 down): results are garbage
   std::map<std::pair<int, int>, std::pair<cudaGraphExec_t, int64_t>> graphs;   // (B, kv bucket) -> exec, nodes
   int64_t last_launches;
@@ -113,6 +116,7 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   // split-K attention tickets start at zero and reset themselves
   cudaMemset(e->attn_counters, 0, (size_t)cfg->max_rows * 4);
   if (const char* v = getenv("CBX_SKIP")) e->skip = atoi(v);
+  if (const char* v = getenv("CBX_L2_PREFETCH")) e->l2_prefetch = v[0] != '0';
   if (const char* v = getenv("CBX_SPLIT_MAX_ROWS")) { e->split_max_rows = atoi(v); if (e->split_max_rows > 512) e->split_max_rows = 512; }
   return e;
 }
@@ -184,10 +188,14 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
   int splits = 1;
   if (T > 4 && !e->trace && T <= e->split_max_rows) splits = m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1);
   bool pending = false;                                // down-proj partials not yet folded into res
+  const bool pf = e->l2_prefetch;
   for (int li = 0; li < e->w.n_layers; ++li) {
     uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;
     if (T <= 4) {
-      if (!(sk & 1) && gemv_qkv_rope(e->res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos, e->slot, e->qkv, kv, T, eps, s)) return -1;
+      // each kernel pulls a LATER kernel's weights into L2 (QKV -> Wo, attention -> Wgu, O -> Wd, gate_up -> next Wqkv)
+      if (!(sk & 1) && gemv_qkv_rope(e->res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos, e->slot, e->qkv, kv, T, eps, s,
+                                     pf ? e->wo[li] : nullptr, (size_t)1024 * 1024 * 2)) return -1;
+      if (pf) attn_set_prefetch(e->wgu[li], (size_t)8192 * 1024 * 2);
     } else {
       if (pending ? cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln1[li], e->h, T, eps, s)
                   : cbx_rmsnorm(e->res, nullptr, e->ln1[li], e->h, T, eps, s)) return -1;
@@ -197,8 +205,11 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
     if (!(sk & 2) && cbx_paged_attn_decode(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
                                            e->attn_scratch, e->attn_counters, T, max_kv_len, s)) return -1;
     if (T <= 4) {
-      if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s)) return -1;
-      if (!(sk & 8) && gemv_norm_gate_up(e->res, e->ln2[li], e->wgu[li], e->act, T, eps, s)) return -1;
+      const bool last = li + 1 == e->w.n_layers;
+      if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s, pf ? e->wd[li] : nullptr, (size_t)1024 * 4096 * 2)) return -1;
+      if (!(sk & 8) && gemv_norm_gate_up(e->res, e->ln2[li], e->wgu[li], e->act, T, eps, s,
+                                         pf ? (last ? e->w.speech_head : e->wqkv[li + 1]) : nullptr,
+                                         last ? (size_t)CBX_SPEECH_VOCAB * 1024 * 2 : (size_t)3072 * 1024 * 2)) return -1;
       if (!(sk & 16) && gemv_residual(e->act, e->wd[li], e->res, T, 4096, s)) return -1;
     } else if (splits > 1) {
       if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s)) return -1;

@@ -254,7 +254,8 @@ __device__ __forceinline__ float ld_dsmem_f32(const float* local, uint32_t rank)
 template <int S>
 __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
     const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt, int bt_stride,
-    const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len, bf16* __restrict__ out) {
+    const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len, bf16* __restrict__ out,
+    const void* next_w, size_t next_bytes) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmallMaxPages * 4096);
   float* red = reinterpret_cast<float*>(bars + kSmallMaxPages);   // [4 warps][68]: o[64], m, l
@@ -265,6 +266,7 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
   pdl_trigger();
   if (threadIdx.x < kSmallMaxPages) mbar_init(&bars[threadIdx.x], 1);
   fence_barrier_init();
+  l2_prefetch_slice(next_w, next_bytes);              // a later projection's weights -> L2 while we wait
   __syncthreads();
   pdl_wait();
 
@@ -435,6 +437,10 @@ extern "C" int64_t cbx_attn_scratch_bytes(int T, int max_kv_len) {
 extern "C" int cbx_attn_num_splits(int T, int max_kv_len) { return T <= 0 ? 0 : make_plan(T, max_kv_len).nsplit; }
 
 namespace cbx {
+// one-shot hint consumed by the next small-batch attention launch: weights to prefetch into L2
+static const void* g_next_w = nullptr;
+static size_t g_next_bytes = 0;
+void attn_set_prefetch(const void* w, size_t bytes) { g_next_w = w; g_next_bytes = bytes; }
 int paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                          const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch, int32_t* counters,
                          int T, int max_kv_len, int max_ctas, void* stream);
@@ -460,9 +466,12 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
       cudaStream_t st = (cudaStream_t)stream;
       dim3 grid(S, CBX_HEADS, T), block(kSmallWarps * 32);
       cudaError_t e = S == 4 ? launch_pdl_cluster(paged_attn_small_kernel<4>, grid, block, kSmallSmem, st, S, (const bf16*)qkv,
-                                                  (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out)
+                                                  (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out,
+                                                  g_next_w, g_next_bytes)
                              : launch_pdl_cluster(paged_attn_small_kernel<2>, grid, block, kSmallSmem, st, S, (const bf16*)qkv,
-                                                  (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out);
+                                                  (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out,
+                                                  g_next_w, g_next_bytes);
+      g_next_w = nullptr; g_next_bytes = 0;
       CBX_REQUIRE(e == cudaSuccess, "paged_attn_small launch failed: %s", cudaGetErrorString(e));
       count_launch();
       return 0;

@@ -33,6 +33,8 @@ struct GemvArgs {
   uint8_t* kv_layer;      // ROPE: this layer's pages
   int T, N, ldy;
   float eps;
+  const void* next_w;     // weights of a later kernel in the chain, prefetched into L2 (may be NULL)
+  size_t next_bytes;
 };
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
@@ -75,6 +77,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
 #pragma unroll
     for (int j = 0; j < 4; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
   }
+  l2_prefetch_slice(a.next_w, a.next_bytes);
   pdl_wait();
 
   // ---- prologue: activation rows -> shared memory (bf16)
@@ -269,23 +272,29 @@ int gemv_bf16(const void* x, const void* W, void* y, int T, int N, int K, int ld
 
 // RMSNorm(res)·ln_w -> ·Wqkv^T -> RoPE -> q into qkv[:, :1024], k/v into the page of slot[t].
 int gemv_qkv_rope(const void* res, const void* ln_w, const void* Wqkv, const void* cos_sin, const int32_t* pos,
-                  const int64_t* slot, void* qkv, void* kv_layer, int T, float eps, cudaStream_t s) {
+                  const int64_t* slot, void* qkv, void* kv_layer, int T, float eps, cudaStream_t s,
+                  const void* next_w, size_t next_bytes) {
   GemvArgs a = {};
+  a.next_w = next_w; a.next_bytes = next_bytes;
   a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = (const bf16*)Wqkv; a.y = (bf16*)qkv;
   a.cos_sin = (const bf16*)cos_sin; a.pos = pos; a.slot = slot; a.kv_layer = (uint8_t*)kv_layer;
   a.T = T; a.N = 3072; a.ldy = 3072; a.eps = eps;
   return dispatch_t<1, PRO_NORM, EPI_ROPE, 12>(a, grid_for(1536, 12), s);
 }
 // res = bf16(bf16(x·W^T) + res), N = 1024, K in {1024, 4096}.
-int gemv_residual(const void* x, const void* W, void* res, int T, int K, cudaStream_t s) {
+int gemv_residual(const void* x, const void* W, void* res, int T, int K, cudaStream_t s, const void* next_w,
+                  size_t next_bytes) {
   GemvArgs a = {};
+  a.next_w = next_w; a.next_bytes = next_bytes;
   a.x = (const bf16*)x; a.W = (const bf16*)W; a.y = (bf16*)res; a.T = T; a.N = 1024; a.ldy = 1024;
   if (K == 1024) return dispatch_t<1, PRO_COPY, EPI_RES, 4>(a, grid_for(512, 4), s);
   return dispatch_t<4, PRO_COPY, EPI_RES, 16>(a, grid_for(512, 4), s);
 }
 // act = SiLU(g)·u of RMSNorm(res)·ln_w · Wgu^T (packed gate/up), act [T, 4096].
-int gemv_norm_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, int T, float eps, cudaStream_t s) {
+int gemv_norm_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, int T, float eps, cudaStream_t s,
+                      const void* next_w, size_t next_bytes) {
   GemvArgs a = {};
+  a.next_w = next_w; a.next_bytes = next_bytes;
   a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = (const bf16*)Wgu; a.y = (bf16*)act;
   a.T = T; a.N = 8192; a.ldy = 4096; a.eps = eps;
   return dispatch_t<1, PRO_NORM, EPI_SILU, 14>(a, grid_for(4096, 14), s);

@@ -72,6 +72,7 @@ def main():
         r["o"] = timeit(lambda i: ops.linear_residual(attn_in, wo[i], res))
         r["gate_up"] = timeit(lambda i: ops.layer_gate_up(res, ln, wgu[i], act=actb, h=h))
         r["down"] = timeit(lambda i: ops.linear_residual(act, wd[i], res))
+        r["norm"] = timeit(lambda i: ops.rmsnorm(res, ln))
         r["head"] = timeit(lambda i: ops.head_logits(res, ln, whead, logits=lgb, h=h))
         B = max(T // 2, 1)
         for name, scale in (("flat", 0.3), ("sharp", 5.0)):
