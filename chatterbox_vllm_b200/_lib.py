@@ -64,6 +64,7 @@ _PROTOS = {
     "cbx_engine_set_trace": (C.c_int, [vp, vp]),
     "cbx_engine_forward": (C.c_int, [vp, C.c_int, C.c_int, vp]),
     "cbx_engine_sample": (C.c_int, [vp, C.c_int, vp]),
+    "cbx_engine_sample_subset": (C.c_int, [vp, C.c_int, C.c_int, vp, vp]),
     "cbx_engine_decode": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "cbx_engine_last_launch_count": (C.c_int64, [vp]),
 }

@@ -32,7 +32,8 @@ int gemm_qkv_rope(const void*, const void*, void*, const void*, const int32_t*, 
 int gemm_residual(const void*, const void*, void*, int, int, int, cudaStream_t);
 int launch_decode_prepare(const void*, const int32_t*, const int32_t*, const int32_t*, const int32_t*, int, void*,
                           int32_t*, int64_t*, int32_t*, int32_t*, int32_t*, int, cudaStream_t);
-int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t);
+int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t, const int32_t* pair_map = nullptr,
+                      int n_sub = 0);
 int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t);
 }  // namespace cbx
 using namespace cbx;
@@ -261,6 +262,22 @@ extern "C" int cbx_engine_sample(cbx_engine* e, int B, void* stream) {
   else if (gemm_bf16_tc(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1;
   // the sampler also stages the next decode step's embeddings / positions / slots
   return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s);
+}
+
+// Admission into a running batch of B pair slots: head + sampler for the n_sub new pairs only.
+// head_rows[0 .. 2*n_sub) index buffer "h" (cond rows of the new pairs, then their uncond rows);
+// pair_map[i] is the slot of the i-th new pair.  Other slots' sampler state and staged inputs are untouched.
+extern "C" int cbx_engine_sample_subset(cbx_engine* e, int B, int n_sub, const int32_t* pair_map, void* stream) {
+  CBX_REQUIRE(B >= 1 && B <= e->cfg.max_pairs && n_sub >= 1 && n_sub <= B && pair_map, "cbx_engine_sample_subset: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int T = 2 * n_sub;
+  cudaError_t ce = launch_pdl(gather_rows_kernel, dim3(T), dim3(128), 0, s, (const uint4*)e->h, (const int32_t*)e->head_rows,
+                              (uint4*)e->hs);
+  CBX_REQUIRE(ce == cudaSuccess, "gather_rows launch failed: %s", cudaGetErrorString(ce));
+  count_launch();
+  if (T <= 4) { if (gemv_bf16(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1; }
+  else if (gemm_bf16_tc(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1;
+  return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s, pair_map, n_sub);
 }
 
 // One decode step for pair slots [0,B): inputs were staged by the previous sampler launch.

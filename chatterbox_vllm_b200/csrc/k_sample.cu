@@ -219,13 +219,18 @@ __device__ __forceinline__ float cfg_pen(float cc, float uu, float cfg, bool see
   return v;
 }
 
+// pair_map == NULL: CTA i samples pair i from logits rows i (cond) and B+i (uncond).
+// pair_map != NULL (admission of new pairs into a running batch): CTA i samples pair pair_map[i] from
+// logits rows i and n_sub+i; every other pair's state is left alone.
 __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* __restrict__ logits,
-                                                                 cbx_sampler_state st, int B, const NextStep nx) {
+                                                                 cbx_sampler_state st, int B, const NextStep nx,
+                                                                 const int32_t* __restrict__ pair_map, int n_sub) {
   __shared__ Red red;
   __shared__ Radix rx;
-  const int b = blockIdx.x, tid = threadIdx.x;
+  const int tid = threadIdx.x;
   pdl_trigger();
   pdl_wait();
+  const int b = pair_map ? pair_map[blockIdx.x] : (int)blockIdx.x;
   if (st.finished[b]) return;
   const int n_prev = st.n_out[b];
   const int len_c = st.seq_len[b], len_u = st.seq_len[B + b];
@@ -234,8 +239,8 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* __r
   const int top_k = st.top_k[b];
 
   // ---- load: ids [8·tid, 8·tid+8) (+ 8192, 8193 on the last thread); CFG merge + repetition penalty
-  const bf16* lc = logits + (size_t)b * CBX_LOGITS_LD;
-  const bf16* lu = logits + (size_t)(B + b) * CBX_LOGITS_LD;
+  const bf16* lc = logits + (size_t)(pair_map ? blockIdx.x : b) * CBX_LOGITS_LD;
+  const bf16* lu = logits + (size_t)(pair_map ? n_sub + blockIdx.x : B + b) * CBX_LOGITS_LD;
   const uint32_t* seen = st.seen + (size_t)b * CBX_SEEN_WORDS;
   const int id0 = tid * 8;
   float l[NP], e[NP];
@@ -384,9 +389,11 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* __r
 namespace cbx {
 int init_sample() { return 0; }
 
-int launch_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, const NextStep& nx, cudaStream_t s) {
-  if (B <= 0) return 0;
-  cudaError_t e = launch_pdl(cfg_sample_kernel, dim3(B), dim3(kThreads), 0, s, (const bf16*)logits, *st, B, nx);
+int launch_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, const NextStep& nx, cudaStream_t s,
+                      const int32_t* pair_map, int n_sub) {
+  if (B <= 0 || (pair_map && n_sub <= 0)) return 0;
+  cudaError_t e = launch_pdl(cfg_sample_kernel, dim3(pair_map ? n_sub : B), dim3(kThreads), 0, s, (const bf16*)logits, *st,
+                             B, nx, pair_map, n_sub);
   CBX_REQUIRE(e == cudaSuccess, "cfg_sample launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
@@ -394,5 +401,5 @@ int launch_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, co
 }  // namespace cbx
 
 extern "C" int cbx_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, void* stream) {
-  return cbx::launch_cfg_sample(logits, st, B, cbx::NextStep(), (cudaStream_t)stream);
+  return cbx::launch_cfg_sample(logits, st, B, cbx::NextStep(), (cudaStream_t)stream, nullptr, 0);
 }

@@ -163,86 +163,117 @@ class T3Engine:
         self.gpu_launches += load().cbx_engine_last_launch_count(self._h)
 
     # ------------------------------------------------------------------ admission + prefill
-    def _admit(self, reqs: list[Request]) -> tuple[list[int], list[list[int]]]:
-        """Reserve KV blocks for prompt + max_tokens of both members of every pair (rows b and
-        B+b of the block table) and upload the table.  Returns prefix lengths and block lists."""
-        B = len(reqs)
-        bt = np.zeros((2 * B, self.bt_stride), np.int32)
-        P, held = [], []
-        for b, r in enumerate(reqs):
+    def _reset_slots(self, B: int) -> None:
+        """Start a generate() call with B empty pair slots: every slot finished, staged inputs inert
+        (kv_len 0 => attention skips the row, slot -1 => nothing is cached)."""
+        self._B = B
+        sb = self.sb
+        sb.finished[:B] = 1
+        sb.n_out[:B] = 0
+        sb.n_finished.zero_()
+        sb.seq_len[:2 * B] = 0
+        self.buffer("pos", (2 * B,), torch.int32).zero_()
+        self.buffer("kv_len", (2 * B,), torch.int32).zero_()
+        self.buffer("slot", (2 * B,), torch.int64).fill_(-1)
+        self.buffer("row_seq", (2 * B,), torch.int32).copy_(torch.arange(2 * B, dtype=torch.int32, device=self.device))
+
+    def _admit(self, reqs: list[Request], slots: list[int] | None = None) -> tuple[list[int], list[list[int]]]:
+        """Reserve KV blocks for prompt + max_tokens of both members of every pair (rows b and B+b of
+        the block table, B = slot count of this call) and upload those rows.  With slots=None the
+        requests take slots 0..n-1 of a fresh n-slot batch.  Returns prefix lengths and block lists."""
+        if slots is None:
+            slots = list(range(len(reqs)))
+            self._reset_slots(len(reqs))
+        B = self._B
+        P, held, rows, ids = [], [], [], []
+        for r in reqs:
             p = COND_LEN + len(r.text_ids) + 1
-            total = p + r.params.max_tokens
-            if total > self.max_model_len:
+            if p + r.params.max_tokens > self.max_model_len:
                 raise ValueError(f"prompt ({p}) + max_tokens ({r.params.max_tokens}) exceeds max_model_len")
             P.append(p)
         for half in range(2):
-            for b, r in enumerate(reqs):
-                blks = self.pool.alloc(-(-(P[b] + r.params.max_tokens) // BLOCK_SIZE))
-                bt[half * B + b, :len(blks)] = blks
+            for j, r in enumerate(reqs):
+                blks = self.pool.alloc(-(-(P[j] + r.params.max_tokens) // BLOCK_SIZE))
+                row = np.zeros(self.bt_stride, np.int32)
+                row[:len(blks)] = blks
+                rows.append(row)
+                ids.append(half * B + slots[j])
                 held.append(blks)
-        self.block_table[:2 * B].copy_(torch.from_numpy(bt), non_blocking=False)
+        self.block_table.index_copy_(0, torch.tensor(ids, device=self.device),
+                                     torch.from_numpy(np.stack(rows)).to(self.device))
         return P, held
 
     def _release(self, held: list[list[int]]) -> None:
         for blks in held:                                  # vLLM frees a request's blocks in reverse order
             self.pool.free(list(reversed(blks)))
 
-    def _init_sampler_state(self, reqs: list[Request], P: list[int]) -> None:
-        B, sb, dev = len(reqs), self.sb, self.device
+    def _init_sampler_state(self, reqs: list[Request], P: list[int], slots: list[int] | None = None) -> None:
+        sb, dev, B = self.sb, self.device, self._B
+        slots = list(range(len(reqs))) if slots is None else slots
+        idx = torch.tensor(slots, device=dev)
         up = lambda vals, dt: torch.tensor(vals, dtype=dt).to(dev)  # noqa: E731
         pr = [r.params for r in reqs]
-        sb.temperature[:B] = up([p.temperature for p in pr], torch.float32)
-        sb.top_p[:B] = up([p.top_p for p in pr], torch.float32)
-        sb.min_p[:B] = up([p.min_p for p in pr], torch.float32)
-        sb.rep_pen[:B] = up([p.repetition_penalty for p in pr], torch.float32)
-        sb.top_k[:B] = up([p.top_k for p in pr], torch.int32)
-        sb.ignore_eos[:B] = up([int(p.ignore_eos) for p in pr], torch.int32)
-        sb.max_out[:B] = up([p.max_tokens for p in pr], torch.int32)
+        sb.temperature[idx] = up([p.temperature for p in pr], torch.float32)
+        sb.top_p[idx] = up([p.top_p for p in pr], torch.float32)
+        sb.min_p[idx] = up([p.min_p for p in pr], torch.float32)
+        sb.rep_pen[idx] = up([p.repetition_penalty for p in pr], torch.float32)
+        sb.top_k[idx] = up([p.top_k for p in pr], torch.int32)
+        sb.ignore_eos[idx] = up([int(p.ignore_eos) for p in pr], torch.int32)
+        sb.max_out[idx] = up([p.max_tokens for p in pr], torch.int32)
         seeds = [(p.seed if p.seed is not None else self.base_seed) & (2**63 - 1) for p in pr]
-        sb.seed[:B] = up(seeds, torch.int64)
-        sb.uid[:B] = up([r.uid for r in reqs], torch.int64)
-        sb.n_out[:B] = 0
-        sb.finished[:B] = 0
-        sb.n_finished.zero_()
+        sb.seed[idx] = up(seeds, torch.int64)
+        sb.uid[idx] = up([r.uid for r in reqs], torch.int64)
+        sb.n_out[idx] = 0
+        sb.finished[idx] = 0
         # cache holds P tokens after prefill; the prefill-time sample call adds 1, so start at P-1
-        sb.seq_len[:2 * B] = up([p - 1 for p in P] * 2, torch.int32)
-        seen = np.zeros((B, ops.SEEN_WORDS), np.uint32)
-        for b, r in enumerate(reqs):
+        lens = up([p - 1 for p in P], torch.int32)
+        sb.seq_len[idx] = lens
+        sb.seq_len[idx + B] = lens
+        seen = np.zeros((len(reqs), ops.SEEN_WORDS), np.uint32)
+        for j, r in enumerate(reqs):
             if r.penalize_prompt_ids:
                 for t in r.text_ids:
                     if t >= SPEECH_TOKEN_OFFSET and t - SPEECH_TOKEN_OFFSET < SPEECH_VOCAB:
-                        s = t - SPEECH_TOKEN_OFFSET
-                        seen[b, s >> 5] |= np.uint32(1 << (s & 31))
-        sb.seen[:B] = torch.from_numpy(seen.view(np.int32)).to(dev)
+                        sp_id = t - SPEECH_TOKEN_OFFSET
+                        seen[j, sp_id >> 5] |= np.uint32(1 << (sp_id & 31))
+        sb.seen[idx] = torch.from_numpy(seen.view(np.int32)).to(dev)
 
-    def prefill(self, reqs: list[Request], P: list[int]) -> None:
-        """One-pass prefill of every pair's whole prefix (cond rows then uncond rows per pair),
-        chunked by max_rows; then the first speech token of every pair is sampled."""
-        B, dev = len(reqs), self.device
+    def prefill(self, reqs: list[Request], P: list[int], slots: list[int] | None = None) -> None:
+        """One-pass prefill of every new pair's whole prefix (cond rows then uncond rows per pair),
+        chunked by max_rows; then the first speech token of every new pair is sampled.  When other
+        slots of the batch are mid-decode, their staged next-step inputs are preserved."""
+        n, dev, B = len(reqs), self.device, self._B
+        slots = list(range(n)) if slots is None else slots
+        whole = n == B
+        staged = None
+        if not whole:                                        # prefill reuses the step buffers: save the running pairs' rows
+            names = (("res", (2 * B, HIDDEN), BF16), ("pos", (2 * B,), torch.int32), ("slot", (2 * B,), torch.int64),
+                     ("kv_len", (2 * B,), torch.int32), ("row_seq", (2 * B,), torch.int32))
+            staged = [(self.buffer(*nm), self.buffer(*nm).clone()) for nm in names]
         cond = torch.stack([r.cond_emb.to(torch.float32) for r in reqs]).to(dev).contiguous()
-        h_last = torch.empty(2 * B, HIDDEN, dtype=BF16, device=dev)
+        h_last = torch.empty(2 * n, HIDDEN, dtype=BF16, device=dev)
         x = self.buffer("x", (self.max_rows, HIDDEN), BF16)
         h = self.buffer("h", (self.max_rows, HIDDEN), BF16)
-        b0 = 0
-        while b0 < B:
-            b1, rows = b0, 0
-            while b1 < B and rows + 2 * P[b1] <= self.max_rows:
-                rows += 2 * P[b1]
-                b1 += 1
-            if b1 == b0:
+        j0 = 0
+        while j0 < n:
+            j1, rows = j0, 0
+            while j1 < n and rows + 2 * P[j1] <= self.max_rows:
+                rows += 2 * P[j1]
+                j1 += 1
+            if j1 == j0:
                 raise ValueError("max_rows too small for one pair's prefix")
             desc, pos, rseq, last = [], [], [], {}
-            for b in range(b0, b1):
-                ids, n = reqs[b].text_ids, len(reqs[b].text_ids)
+            for j in range(j0, j1):
+                ids, nt = reqs[j].text_ids, len(reqs[j].text_ids)
                 for half in range(2):
                     for i in range(COND_LEN):
-                        desc.append((0, b, i, 0))
-                    for i in range(n):
+                        desc.append((0, j, i, 0))
+                    for i in range(nt):
                         desc.append((1, ids[i], i, 0) if half == 0 else (2, 0, 0, 0))
                     desc.append((3, START_SPEECH, 0, 0))
-                    pos.extend(range(P[b]))
-                    rseq.extend([half * B + b] * P[b])
-                    last[half * B + b] = len(pos) - 1
+                    pos.extend(range(P[j]))
+                    rseq.extend([half * B + slots[j]] * P[j])
+                    last[half * n + j] = len(pos) - 1
             T = len(pos)
             d_desc = torch.tensor(desc, dtype=torch.int32).to(dev)
             d_pos = torch.tensor(pos, dtype=torch.int32).to(dev)
@@ -252,18 +283,28 @@ class T3Engine:
             self.buffer("kv_len", (T,), torch.int32).copy_(d_pos + 1)
             self.buffer("slot", (T,), torch.int64).copy_(ops.slot_mapping(self.block_table, d_rseq, d_pos))
             ops.prefill_embed(d_desc, cond, self.text_emb, self.text_pos, self.speech_emb, self.speech_pos, out=x[:T])
-            self.forward(T, max(P[b0:b1]))
+            self.forward(T, max(P[j0:j1]))
             seqs = sorted(last)
-            h_last[torch.tensor(seqs, device=dev)] = h[torch.tensor([last[s] for s in seqs], device=dev)]
-            b0 = b1
-        h[:2 * B].copy_(h_last)
-        self.buffer("head_rows", (2 * B,), torch.int32).copy_(torch.arange(2 * B, dtype=torch.int32, device=dev))
-        self.sample(B)
+            h_last[torch.tensor(seqs, device=dev)] = h[torch.tensor([last[q] for q in seqs], device=dev)]
+            j0 = j1
+        h[:2 * n].copy_(h_last)
+        self.buffer("head_rows", (2 * n,), torch.int32).copy_(torch.arange(2 * n, dtype=torch.int32, device=dev))
+        if whole:
+            self.buffer("row_seq", (2 * B,), torch.int32).copy_(torch.arange(2 * B, dtype=torch.int32, device=dev))
+            self.sample(B)
+            return
+        # restore the running pairs' staged rows, then sample only the new pairs (which stages theirs)
+        for buf, saved in staged:
+            buf[: 2 * B] = saved                               # prefill clobbered rows [0, T): put everything back …
+        pair_map = torch.tensor(slots, dtype=torch.int32, device=dev)
+        check(load().cbx_engine_sample_subset(self._h, B, n, pair_map.data_ptr(), self._stream()), "engine_sample_subset")
 
     # ------------------------------------------------------------------ public entry
     def generate(self, reqs: list[Request], poll_every: int = 32) -> list[list[int]]:
-        """Runs requests in static waves of ≤ max_pairs; returns speech-token ids per request in
-        vLLM id space (speech id + 1000), stop token included, like vLLM's output.token_ids."""
+        """Runs the requests through min(max_pairs, n) pair slots with continuous admission: a slot
+        whose pair finished is refilled with the next request while the others keep decoding.
+        Returns speech-token ids per request in vLLM id space (speech id + 1000), stop token
+        included, like vLLM's output.token_ids."""
         self.stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.stream):
             out = self._generate(reqs, poll_every)
@@ -271,29 +312,65 @@ class T3Engine:
         return out
 
     def _generate(self, reqs: list[Request], poll_every: int) -> list[list[int]]:
-        out: list[list[int]] = []
-        for w0 in range(0, len(reqs), self.max_pairs):
-            wave = reqs[w0:w0 + self.max_pairs]
-            for r in wave:
-                if r.uid == 0:
-                    self._next_uid += 1
-                    r.uid = self._next_uid
-            B = len(wave)
-            P, held = self._admit(wave)
-            try:
-                self._init_sampler_state(wave, P)
-                self.prefill(wave, P)
-                steps, max_steps, max_p = 1, max(r.params.max_tokens for r in wave), max(P)
-                while steps < max_steps:
-                    n = min(poll_every, max_steps - steps)
-                    self.decode(B, n, max_p + steps + n)
-                    steps += n
-                    if int(self.sb.n_finished.item()) >= B:      # the only host sync: every poll_every steps
+        n = len(reqs)
+        if n == 0:
+            return []
+        for r in reqs:
+            if r.uid == 0:
+                self._next_uid += 1
+                r.uid = self._next_uid
+        B = min(self.max_pairs, n)
+        self._reset_slots(B)
+        out: list = [None] * n
+        slot_req: list = [None] * B                            # request index living in each slot
+        slot_held: dict = {}
+        slot_len = [0] * B                                     # host upper bound of each slot's context length
+        nxt = 0
+        try:
+            while True:
+                free = [b for b in range(B) if slot_req[b] is None]
+                new_slots, new_reqs = [], []
+                while nxt < n and free:
+                    r = reqs[nxt]
+                    need = 2 * -(-(COND_LEN + len(r.text_ids) + 1 + r.params.max_tokens) // BLOCK_SIZE)
+                    if need > self.pool.num_free():
+                        if not any(q is not None for q in slot_req) and not new_slots:
+                            raise ValueError("KV pool too small for a single request")
                         break
-                n_out = self.sb.n_out[:B].cpu().tolist()
-                toks = self.sb.out_tokens[:B].cpu().numpy()
-                out.extend([(toks[b, :n_out[b]] + SPEECH_TOKEN_OFFSET).tolist() for b in range(B)])
-            finally:
+                    b = free.pop(0)
+                    slot_req[b] = nxt
+                    new_slots.append(b)
+                    new_reqs.append(r)
+                    nxt += 1
+                    # reserve now so the next fit check sees the pool shrink
+                    P1, held1 = self._admit([r], [b])
+                    slot_held[b] = (P1[0], held1)
+                if new_slots:
+                    P = [slot_held[b][0] for b in new_slots]
+                    self._init_sampler_state(new_reqs, P, new_slots)
+                    self.prefill(new_reqs, P, new_slots)
+                    for b, p in zip(new_slots, P):
+                        slot_len[b] = p + 1
+                active = [b for b in range(B) if slot_req[b] is not None]
+                if not active:
+                    break
+                remaining = max(reqs[slot_req[b]].params.max_tokens - (slot_len[b] - slot_held[b][0]) for b in active)
+                if remaining > 0:
+                    steps = min(poll_every, remaining)
+                    self.decode(B, steps, max(slot_len[b] for b in active) + steps)
+                    for b in active:
+                        slot_len[b] += steps
+                fin = self.sb.finished[:B].cpu().tolist()      # the only host sync: every poll_every steps
+                done = [b for b in active if fin[b]]
+                if done:
+                    n_out = self.sb.n_out[:B].cpu().tolist()
+                    toks = self.sb.out_tokens[:B].cpu().numpy()
+                    for b in done:
+                        out[slot_req[b]] = (toks[b, :n_out[b]] + SPEECH_TOKEN_OFFSET).tolist()
+                        self._release(slot_held.pop(b)[1])
+                        slot_req[b] = None
+        finally:
+            for _, held in slot_held.values():
                 self._release(held)
         return out
 

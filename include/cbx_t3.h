@@ -206,6 +206,9 @@ int cbx_engine_forward(cbx_engine*, int T, int max_kv_len, void* stream);
 /* Head GEMM over the 2B rows listed in buffer "head_rows" (row index into "h"; cond rows
  * first) + cbx_cfg_sample (t3.py:725-739 + sampler). */
 int cbx_engine_sample(cbx_engine*, int B, void* stream);
+/* Admission of n_sub new pairs into a running batch of B slots (continuous batching): head GEMM
+ * over head_rows[0 .. 2*n_sub) + sampler for the slots pair_map[0 .. n_sub) only (device int32). */
+int cbx_engine_sample_subset(cbx_engine*, int B, int n_sub, const int32_t* pair_map, void* stream);
 /* n decode steps for pair slots [0,B): forward(2B rows) → head → sample, no host sync.  The
  * step's inputs (embedding rows, positions, slots, kv lengths) were staged on the device by the
  * previous cbx_engine_sample / decode step's sampler launch.
