@@ -64,6 +64,7 @@ struct cbx_engine {
   void* attn_scratch;
   float* part;                 // split-K partials [4][split_max_rows][1024] fp32
   int split_max_rows = 512;
+  const int32_t* prefill_items = nullptr; int n_prefill_items = 0;
   bool l2_prefetch = false;  // measured: no gain at b=1 (L2->SM bandwidth ~ HBM bandwidth on B200); env CBX_L2_PREFETCH=1 enables
   int skip = 0;   // profiling aid (env CBX_SKIP bitmask: 1 qkv, 2 attn, 4 o, 8 gate_up, 16 down): results are garbage
   std::map<std::pair<int, int>, std::pair<cudaGraphExec_t, int64_t>> graphs;   // (B, kv bucket) -> exec, nodes
@@ -203,8 +204,11 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
       pending = false;
       if (!(sk & 1) && gemm_qkv_rope(e->h, e->wqkv[li], e->qkv, e->w.cos_sin, e->pos, e->slot, kv, T, s)) return -1;
     }
-    if (!(sk & 2) && cbx_paged_attn_decode(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
-                                           e->attn_scratch, e->attn_counters, T, max_kv_len, s)) return -1;
+    if (e->n_prefill_items > 0) {
+      if (!(sk & 2) && cbx_paged_attn_prefill(e->qkv, kv, e->block_table, e->bt_stride, e->prefill_items, e->n_prefill_items,
+                                              e->attn, s)) return -1;
+    } else if (!(sk & 2) && cbx_paged_attn_decode(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
+                                                  e->attn_scratch, e->attn_counters, T, max_kv_len, s)) return -1;
     if (T <= 4) {
       const bool last = li + 1 == e->w.n_layers;
       if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s, pf ? e->wd[li] : nullptr, (size_t)1024 * 4096 * 2)) return -1;
@@ -236,6 +240,12 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
 extern "C" int cbx_engine_forward(cbx_engine* e, int T, int max_kv_len, void* stream) {
   CBX_REQUIRE(T >= 1 && T <= e->cfg.max_rows, "cbx_engine_forward: T=%d out of range", T);
   return forward_layers(e, T, max_kv_len, (cudaStream_t)stream, true);
+}
+
+extern "C" int cbx_engine_set_prefill_items(cbx_engine* e, const int32_t* items, int n_items) {
+  CBX_REQUIRE(e != nullptr && (n_items == 0 || items != nullptr), "cbx_engine_set_prefill_items: bad arguments");
+  e->prefill_items = items; e->n_prefill_items = n_items;
+  return 0;
 }
 
 extern "C" int cbx_engine_set_trace(cbx_engine* e, void* trace) {

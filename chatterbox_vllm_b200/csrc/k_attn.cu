@@ -380,6 +380,134 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
   if (S > 1) cluster_sync_all();                       // peers' shared memory stays alive until rank 0 has read it
 }
 
+// ---------------------------------------------------------------------------------------------
+// Prefill (causal) attention over the paged cache: one item = 16 consecutive query rows of one
+// sequence (a "query block" qb), which need KV pages 0..qb — each page is loaded ONCE for the 16
+// queries instead of once per row (16x less page traffic than running prefix rows through the
+// decode kernel).  Same persistent producer/consumer skeleton: warp = head; lane = (query, half of
+// d); K/V rows are shared-memory broadcasts.  fp32 online softmax per query.
+// items int32 [n][4] = {row0 (first query row in qkv/out), n_q (1..16), block-table row, qb}.
+__global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
+    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt, int bt_stride,
+    const int4* __restrict__ items, int n_items, bf16* __restrict__ out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
+  uint64_t* empty = full + kStages;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  pdl_wait();
+  uint32_t it = 0;
+  if (warp == kConsumerWarps) {                       // ---- producer
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      const int4 im = items[w];
+      const int32_t* btr = bt + (int64_t)im.z * bt_stride;
+      for (int pb = 0; pb <= im.w; pb += 32) {
+        const int nb = min(32, im.w + 1 - pb);
+        const int my_blk = lane < nb ? btr[pb + lane] : 0;
+        for (int j = 0; j < nb; ++j) {
+          const int blk = __shfl_sync(0xffffffffu, my_blk, j);
+          if (lane == 0) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            mbar_wait(&empty[s], ph ^ 1);
+            mbar_arrive_expect_tx(&full[s], CBX_PAGE_BYTES);
+            bulk_g2s(smem + s * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, CBX_PAGE_BYTES, &full[s]);
+          }
+          ++it;
+        }
+      }
+    }
+    return;
+  }
+  const int h = warp, qi = lane & 15, half = lane >> 4;
+  const float qscale = 0.125f * kLog2e;
+  for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+    const int4 im = items[w];
+    const int row = im.x + qi, qb = im.w;
+    const bool live = qi < im.y;
+    float q[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) q[i] = 0.f;
+    if (live) {
+      const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint4 v = qp[i];
+        q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
+        q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
+        q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
+        q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
+      }
+    }
+    float m = -INFINITY, l = 0.f, acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+    for (int pg = 0; pg <= qb; ++pg, ++it) {
+      const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+      mbar_wait(&full[s], ph);
+      const uint8_t* kt = smem + s * CBX_PAGE_BYTES + h * 2048;
+      const uint8_t* vt = kt + 32768;
+      const int n_vis = pg < qb ? 16 : qi + 1;        // causal: query 16·qb+qi sees tokens <= itself
+      float sc[16];
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const uint4* kr = reinterpret_cast<const uint4*>(kt + t * 128);
+        float a = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 v = kr[(half * 4 + i) ^ (t & 7)];
+          a = fmaf(q[i * 8 + 0], bf_lo(v.x), a); a = fmaf(q[i * 8 + 1], bf_hi(v.x), a);
+          a = fmaf(q[i * 8 + 2], bf_lo(v.y), a); a = fmaf(q[i * 8 + 3], bf_hi(v.y), a);
+          a = fmaf(q[i * 8 + 4], bf_lo(v.z), a); a = fmaf(q[i * 8 + 5], bf_hi(v.z), a);
+          a = fmaf(q[i * 8 + 6], bf_lo(v.w), a); a = fmaf(q[i * 8 + 7], bf_hi(v.w), a);
+        }
+        sc[t] = a;
+      }
+      float mt = -INFINITY;
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        sc[t] += __shfl_xor_sync(0xffffffffu, sc[t], 16);
+        sc[t] = t < n_vis ? sc[t] : -INFINITY;
+        mt = fmaxf(mt, sc[t]);
+      }
+      const float m_new = fmaxf(m, mt);               // token 0 of page 0 is always visible: m_new is finite
+      const float corr = exp2f(m - m_new);
+      m = m_new;
+      l *= corr;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) acc[i] *= corr;
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const float p = exp2f(sc[t] - m_new);
+        l += p;
+        const uint4* vr = reinterpret_cast<const uint4*>(vt + t * 128) + half * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 v = vr[i];
+          acc[i * 8 + 0] = fmaf(p, bf_lo(v.x), acc[i * 8 + 0]); acc[i * 8 + 1] = fmaf(p, bf_hi(v.x), acc[i * 8 + 1]);
+          acc[i * 8 + 2] = fmaf(p, bf_lo(v.y), acc[i * 8 + 2]); acc[i * 8 + 3] = fmaf(p, bf_hi(v.y), acc[i * 8 + 3]);
+          acc[i * 8 + 4] = fmaf(p, bf_lo(v.z), acc[i * 8 + 4]); acc[i * 8 + 5] = fmaf(p, bf_hi(v.z), acc[i * 8 + 5]);
+          acc[i * 8 + 6] = fmaf(p, bf_lo(v.w), acc[i * 8 + 6]); acc[i * 8 + 7] = fmaf(p, bf_hi(v.w), acc[i * 8 + 7]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+    }
+    if (live) {
+      const float inv = 1.f / l;
+      uint4* dst = reinterpret_cast<uint4*>(out + (size_t)row * CBX_HIDDEN + h * 64 + half * 32);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        dst[i] = make_uint4(pack_bf16(acc[i * 8 + 0] * inv, acc[i * 8 + 1] * inv), pack_bf16(acc[i * 8 + 2] * inv, acc[i * 8 + 3] * inv),
+                            pack_bf16(acc[i * 8 + 4] * inv, acc[i * 8 + 5] * inv), pack_bf16(acc[i * 8 + 6] * inv, acc[i * 8 + 7] * inv));
+    }
+  }
+}
+
 // Combine split partials: 256 threads per row, thread = 4 consecutive d of one head.
 __global__ void __launch_bounds__(256) attn_merge_kernel(const float* __restrict__ o_part,
                                                          const float2* __restrict__ ml_part,
@@ -417,6 +545,8 @@ int init_attn() {
                                        kSmemBytes);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(paged_attn_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(paged_attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(paged_attn_small_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmem);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
@@ -501,5 +631,20 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
     CBX_REQUIRE(e == cudaSuccess, "attn_merge launch failed: %s", cudaGetErrorString(e));
     count_launch();
   }
+  return 0;
+}
+
+// Causal attention for prefill rows whose K/V are already in the cache (vllm flash_attn.py:796-800,
+// prefill form).  items: device int32 [n_items][4] = {row0, n_q, block-table row, query block}.
+extern "C" int cbx_paged_attn_prefill(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
+                                      const int32_t* items, int n_items, void* out, void* stream) {
+  if (n_items <= 0) return 0;
+  if (cbx::init_attn()) return -1;
+  const int grid = n_items < 148 ? n_items : 148;
+  cudaError_t e = launch_pdl(paged_attn_prefill_kernel, dim3(grid), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,
+                             (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, (const int4*)items, n_items,
+                             (bf16*)out);
+  CBX_REQUIRE(e == cudaSuccess, "paged_attn_prefill launch failed: %s", cudaGetErrorString(e));
+  count_launch();
   return 0;
 }

@@ -263,6 +263,7 @@ class T3Engine:
             if j1 == j0:
                 raise ValueError("max_rows too small for one pair's prefix")
             desc, pos, rseq, last = [], [], [], {}
+            starts, plens, btrows = [], [], []
             for j in range(j0, j1):
                 ids, nt = reqs[j].text_ids, len(reqs[j].text_ids)
                 for half in range(2):
@@ -271,6 +272,7 @@ class T3Engine:
                     for i in range(nt):
                         desc.append((1, ids[i], i, 0) if half == 0 else (2, 0, 0, 0))
                     desc.append((3, START_SPEECH, 0, 0))
+                    starts.append(len(pos)), plens.append(P[j]), btrows.append(half * B + slots[j])
                     pos.extend(range(P[j]))
                     rseq.extend([half * B + slots[j]] * P[j])
                     last[half * n + j] = len(pos) - 1
@@ -283,7 +285,12 @@ class T3Engine:
             self.buffer("kv_len", (T,), torch.int32).copy_(d_pos + 1)
             self.buffer("slot", (T,), torch.int64).copy_(ops.slot_mapping(self.block_table, d_rseq, d_pos))
             ops.prefill_embed(d_desc, cond, self.text_emb, self.text_pos, self.speech_emb, self.speech_pos, out=x[:T])
-            self.forward(T, max(P[j0:j1]))
+            items = ops.prefill_items(starts, plens, btrows).to(dev)       # causal attention: 16 query rows per item
+            check(load().cbx_engine_set_prefill_items(self._h, items.data_ptr(), items.shape[0]), "set_prefill_items")
+            try:
+                self.forward(T, max(P[j0:j1]))
+            finally:
+                check(load().cbx_engine_set_prefill_items(self._h, None, 0), "set_prefill_items")
             seqs = sorted(last)
             h_last[torch.tensor(seqs, device=dev)] = h[torch.tensor([last[q] for q in seqs], device=dev)]
             j0 = j1

@@ -92,6 +92,27 @@ def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: i
     return out
 
 
+def prefill_items(row_starts: list[int], lens: list[int], bt_rows: list[int]) -> torch.Tensor:
+    """Host helper: int32 [n,4] items {row0, n_q, block-table row, query block} for sequences whose
+    prefix rows start at row_starts[i] (positions 0..lens[i]-1), longest items first (they are dealt
+    round-robin to the persistent CTAs)."""
+    it = []
+    for r0, n, br in zip(row_starts, lens, bt_rows):
+        for qb in range(-(-n // BLOCK_SIZE)):
+            it.append((r0 + qb * BLOCK_SIZE, min(BLOCK_SIZE, n - qb * BLOCK_SIZE), br, qb))
+    it.sort(key=lambda t: -t[3])
+    return torch.tensor(it, dtype=torch.int32).view(-1, 4)
+
+
+def paged_attn_prefill(qkv, kv_layer, block_table, items, out=None):
+    T = qkv.shape[0]
+    if out is None:
+        out = torch.zeros(T, HIDDEN, dtype=BF16, device=qkv.device)
+    check(load().cbx_paged_attn_prefill(_p(qkv, BF16), _p(kv_layer), _p(block_table, torch.int32), block_table.stride(0),
+                                        _p(items, torch.int32), items.shape[0], _p(out), _stream()), "paged_attn_prefill")
+    return out
+
+
 def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5, qkv=None, h=None):
     """RMSNorm → QKV → RoPE → KV append.  Returns the qkv buffer [T,3072] whose first 1024 columns hold
     the rotated q (the k/v columns are not written: they went to the cache)."""
@@ -237,6 +258,6 @@ class BlockPool:
 
 
 __all__ = ["slot_mapping", "rmsnorm", "pack_gate_up", "linear", "rope_kv_append", "paged_attn_decode",
-           "layer_qkv", "linear_residual", "linear_partials", "rmsnorm_reduce", "layer_gate_up", "head_logits",
+           "layer_qkv", "prefill_items", "paged_attn_prefill", "linear_residual", "linear_partials", "rmsnorm_reduce", "layer_gate_up", "head_logits",
            "SamplerBuffers", "cfg_sample", "decode_prepare", "prefill_embed", "BlockPool", "BLOCK_SIZE", "HIDDEN",
            "INTER", "LOGITS_LD", "PAGE_BYTES", "SEEN_WORDS", "SPEECH_VOCAB", "_lib"]

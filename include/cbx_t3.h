@@ -102,6 +102,14 @@ int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* 
                           int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
                           void* out, void* scratch, int32_t* counters, int T, int max_kv_len, void* stream);
 
+/* Prefill form of the same attention (causal, many query rows per sequence): an item is 16
+ * consecutive query rows of one sequence (query block qb = first position / 16), which attend to
+ * KV pages 0..qb; each page is loaded once per item.  The rows' K/V must already be in the cache
+ * (cbx_layer_qkv appends them).  items: device int32 [n_items][4] = {row0, n_q (1..16),
+ * block-table row, qb}; q rows are read from qkv [T,3072], out is bf16 [T,1024]. */
+int cbx_paged_attn_prefill(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
+                           const int32_t* items, int n_items, void* out, void* stream);
+
 /* ---- fused layer pieces: what cbx_engine_forward launches per layer ------------------------
  * The residual stream `res` [T,1024] is updated in place by the projections that close a
  * residual branch (vllm llama.py:316-333 fused_add_rms_norm convention, rounding points kept:
@@ -198,6 +206,10 @@ void* cbx_engine_buffer(cbx_engine*, const char* name);
  * after every layer li, the residual stream (= the HF hidden state after the layer) to
  * trace[li*T*1024] (bf16).  Set before the call, clear with NULL; do not use with graphs. */
 int cbx_engine_set_trace(cbx_engine*, void* trace);
+
+/* While n_items > 0, cbx_engine_forward uses cbx_paged_attn_prefill with these items (device
+ * int32 [n_items][4]) instead of the per-row decode attention.  Cleared with n_items = 0. */
+int cbx_engine_set_prefill_items(cbx_engine*, const int32_t* items, int n_items);
 
 /* Llama forward over T rows whose embeddings are already in buffer "res" (alias "x"), with
  * pos/slot/row_seq/kv_len filled (t3.py:742-778 + vllm llama.py:394-430).  Leaves final-norm

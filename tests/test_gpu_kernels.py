@@ -336,3 +336,25 @@ def test_split_k_partials_and_reduce_norm(ops, T, K, splits):
     assert (err <= 2.0 * ULP * y.abs() + 1.01 * ULP * want_res.abs() + 1e-6).all(), f"res max err {err.max():.3e}"
     # the norm is checked on the kernel's own residual (so only the norm's rounding is in play)
     assert_close_bf16(out, rmsnorm(r.float().cpu(), w, 1e-5, "bf16"), ulps=1.01, what="norm after reduce")
+
+
+@pytest.mark.parametrize("lens", [[1], [16], [17, 5], [200, 77, 33], [450]])
+def test_paged_attention_prefill_causal(ops, lens):
+    """Causal prefill attention (16 query rows share each page load) against the fp32 reference,
+    for every row of every sequence, and against the per-row decode kernel."""
+    cfg = T3ModelConfig()
+    kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, lens, seed=10 + len(lens))
+    starts = np.concatenate(([0], np.cumsum(lens)[:-1])).tolist()
+    T = sum(lens)
+    g = torch.Generator().manual_seed(7)
+    q = torch.randn(T, 3072, generator=g).to(BF16)
+    items = ops.prefill_items(starts, lens, list(range(len(lens)))).cuda()
+    out = ops.paged_attn_prefill(dev(q), kv, bt_d, items)
+    rows = [(s, p) for s, n in enumerate(lens) for p in range(n)]
+    dec = ops.paged_attn_decode(dev(q), kv, bt_d, dev(torch.tensor([s for s, _ in rows], dtype=torch.int32)),
+                                dev(torch.tensor([p + 1 for _, p in rows], dtype=torch.int32)), max(lens))
+    assert_close_bf16(out, dec, ulps=1.01, atol=2e-3, what="prefill vs per-row decode kernel")
+    for i in list(range(0, T, max(1, T // 40))) + [T - 1]:
+        s, p = rows[i]
+        want = _ref_attn(cfg, qkv_all[s], q[i, :1024].float(), p + 1, cs)
+        assert_close_bf16(out[i], want, ulps=1.0, atol=2e-3, what=f"prefill row {i} (seq {s}, pos {p})")
