@@ -433,3 +433,70 @@ def test_engine_stops_on_eos_and_per_request_max_tokens(ops):
     assert got[0] == cut0, "generation must stop right after the first stop token (it is included)"
     assert got[1] == cut1, "per-request max_tokens must be honoured"
     eng.close()
+
+
+def test_engine_multilingual_shapes_and_prompt_penalty_quirk(ops):
+    """Config 4 shapes: text vocab 2454 (t3_config.py:33-35), text ids up to 2453, language-tag id
+    first.  With penalize_prompt_ids the reference's quirk is reproduced: prompt ids >= 1000 land in
+    the repetition-penalty mask of speech id (id - 1000)."""
+    from chatterbox_vllm_b200.engine import Request, SamplingParams, T3Engine
+    cfg = T3ModelConfig.multilingual(n_layers=2)
+    w = T3Weights.random(cfg, seed=3, head_scale=16.0, norm_jitter=0.1)
+    eng = T3Engine(w.state_dict(), device="cuda:0", max_pairs=2, max_model_len=256)
+    g = torch.Generator().manual_seed(5)
+    n_steps = 8
+    reqs = []
+    for i in range(2):
+        text = [708] + [255] + torch.randint(698, 2454, (20,), generator=g).tolist() + [0]
+        cond = torch.randn(34, 1024, generator=g) * 0.02
+        reqs.append(Request(text, cond, SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=n_steps,
+                                                       ignore_eos=True), uid=50 + i, penalize_prompt_ids=True))
+    got = eng.generate(reqs)
+    # oracle with the same prompt-derived seen mask
+    o = T3Oracle(w, "bf16")
+    for ri, r in enumerate(reqs):
+        pair = o.new_pair()
+        seen = np.zeros(8194, bool)
+        for t in r.text_ids:
+            if 1000 <= t < 1000 + 8194:
+                seen[t - 1000] = True
+        assert seen.any()
+        lg = o.prefill_pair(pair, r.cond_emb, r.text_ids, eng.cfg_scale).numpy()
+        agree = 0
+        for s_ in range(n_steps):
+            want = sampler_ref.sample_row(lg, seen, repetition_penalty=2.0, temperature=0.0)
+            tok = got[ri][s_] - 1000
+            l = sampler_ref.apply_repetition_penalty(lg, seen, 2.0)
+            assert tok == want or l.max() - l[tok] <= 4 * 2.0 ** -7 * abs(l.max()), (ri, s_, tok, want)
+            agree += int(tok == want)
+            seen[tok] = True
+            lg = o.decode_pairs([pair], [tok], eng.cfg_scale)[0].numpy()
+        assert agree >= n_steps - 2
+    eng.close()
+
+
+def test_engine_long_context_high_block_occupancy(ops):
+    """Config 5 in miniature: max_model_len 1000, KV pool ~97 % occupied, contexts running up to
+    ~1000 tokens, T = 64 rows.  Streams of a few probed pairs must match the oracle; every block
+    returns to the pool."""
+    from chatterbox_vllm_b200.engine import Request, SamplingParams, T3Engine
+    cfg = T3ModelConfig(n_layers=2)
+    w = T3Weights.random(cfg, seed=0, head_scale=16.0, norm_jitter=0.1)
+    B, n_text, n_steps = 32, 900, 40
+    P = 34 + n_text + 1
+    per_seq = -(-(P + n_steps) // 16)
+    eng = T3Engine(w.state_dict(), device="cuda:0", max_pairs=B, max_model_len=1000, num_blocks=int(2 * B * per_seq / 0.97) + 1)
+    g = torch.Generator().manual_seed(9)
+    reqs = []
+    for i in range(B):
+        text = [255] + torch.randint(3, 600, (n_text - 2,), generator=g).tolist() + [0]
+        reqs.append(Request(text, torch.randn(34, 1024, generator=g) * 0.02,
+                            SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=n_steps, ignore_eos=True),
+                            uid=900 + i))
+    got = eng.generate(reqs, poll_every=16)
+    assert all(len(t) == n_steps for t in got)
+    assert eng.pool.num_free() == eng.num_blocks - 1
+    probe = [0, B - 1]
+    assert_stream_parity([got[i] for i in probe], w, [reqs[i] for i in probe], eng.cfg_scale, n_steps, first_exact=0,
+                         min_agree=0.85, temperature=0.0, repetition_penalty=2.0)
+    eng.close()
