@@ -35,6 +35,18 @@ int launch_decode_prepare(const void*, const int32_t*, const int32_t*, const int
 int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t, const int32_t* pair_map = nullptr,
                       int n_sub = 0);
 int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t);
+struct MegaArgs {
+  const bf16* ln1[32]; const bf16* wqkv[32]; const bf16* wo[32];
+  const bf16* ln2[32]; const bf16* wgu[32]; const bf16* wd[32];
+  const bf16* norm_w; const bf16* head_w;
+  const bf16* res_in; bf16* logits; uint8_t* ws; unsigned* sync; bf16* trace;
+  const bf16* cos_sin; const int32_t* pos; const int64_t* slot; const int32_t* row_seq; const int32_t* kv_len;
+  const int32_t* bt; uint8_t* kv_cache; size_t layer_bytes;
+  int bt_stride, T, n_layers, vocab, ldl; float eps; int flags;
+};
+size_t mega_ws_bytes();
+int init_mega();
+int launch_decode_mega(const MegaArgs&, cudaStream_t);
 }  // namespace cbx
 using namespace cbx;
 
@@ -62,7 +74,11 @@ struct cbx_engine {
   int32_t *pos, *kv_len, *row_seq, *head_rows, *attn_counters;
   int64_t* slot;
   void* attn_scratch;
-  float* part;                 // split-K partials [4][split_max_rows][1024] fp32
+  float* part;                 // split-K partials [4][split_max_rows][1024] fp32 
+  unsigned* mega_sync;         // exit counter + epoch of the persistent decode kernel
+  uint8_t* mega_ws;            // its tagged exchange buffers
+  bool mega = false;           // env CBX_MEGA=1: T <= 4 decode steps run as ONE persistent kernel (k_mega.cu).  Parity-tested,
+                               // but measured slower on B200 (b=1: ~1000 us/step vs ~620 us for the PDL kernel chain), so off
   int split_max_rows = 512;
   const int32_t* prefill_items = nullptr; int n_prefill_items = 0;
   bool l2_prefetch = false;  // measured: no gain at b=1 (L2->SM bandwidth ~ HBM bandwidth on B200); env CBX_L2_PREFETCH=1 enables
@@ -92,6 +108,8 @@ static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
   p = take(R * 4); if (e) e->attn_counters = (int32_t*)p;
   p = take((R + 1024) * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256); if (e) e->attn_scratch = p;
   p = take((size_t)4 * 512 * 1024 * 4); if (e) e->part = (float*)p;
+  p = take(256); if (e) e->mega_sync = (unsigned*)p;
+  p = take(mega_ws_bytes()); if (e) e->mega_ws = (uint8_t*)p;
   return off;
 }
 
@@ -102,7 +120,8 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   if (!cfg || !w || !kv_cache || !block_table || !workspace || !st) { set_error("cbx_engine_create: NULL argument"); return nullptr; }
   if (cfg->max_rows < 2 * cfg->max_pairs || cfg->max_pairs < 1) { set_error("cbx_engine_create: max_rows < 2*max_pairs"); return nullptr; }
   if ((reinterpret_cast<uintptr_t>(workspace) & 1023) != 0) { set_error("cbx_engine_create: workspace not 1024-aligned"); return nullptr; }
-  if (init_gemm() || init_attn() || init_sample()) return nullptr;
+  if (init_gemm() || init_attn() || init_sample() || init_mega()) return nullptr;
+  if (w->n_layers > 32) { set_error("cbx_engine_create: n_layers > 32"); return nullptr; }
   cbx_engine* e = new cbx_engine();
   e->cfg = *cfg;
   e->w = *w;
@@ -117,6 +136,9 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   carve(cfg, e, (uint8_t*)workspace);
   // split-K attention tickets start at zero and reset themselves
   cudaMemset(e->attn_counters, 0, (size_t)cfg->max_rows * 4);
+  cudaMemset(e->mega_sync, 0, 256);
+  cudaMemset(e->mega_ws, 0, mega_ws_bytes());
+  if (const char* v = getenv("CBX_MEGA")) e->mega = v[0] != '0';
   if (const char* v = getenv("CBX_SKIP")) e->skip = atoi(v);
   if (const char* v = getenv("CBX_L2_PREFETCH")) e->l2_prefetch = v[0] != '0';
   if (const char* v = getenv("CBX_SPLIT_MAX_ROWS")) { e->split_max_rows = atoi(v); if (e->split_max_rows > 512) e->split_max_rows = 512; }
@@ -293,6 +315,25 @@ extern "C" int cbx_engine_sample_subset(cbx_engine* e, int B, int n_sub, const i
 // One decode step for pair slots [0,B): inputs were staged by the previous sampler launch.
 static int decode_step(cbx_engine* e, int B, int max_kv_len, cudaStream_t s) {
   const int T = 2 * B;
+  if (T <= 4 && e->mega && e->n_prefill_items == 0 && !e->skip) {
+    MegaArgs a = {};
+    for (int li = 0; li < e->w.n_layers; ++li) {
+      a.ln1[li] = (const bf16*)e->ln1[li]; a.wqkv[li] = (const bf16*)e->wqkv[li]; a.wo[li] = (const bf16*)e->wo[li];
+      a.ln2[li] = (const bf16*)e->ln2[li]; a.wgu[li] = (const bf16*)e->wgu[li]; a.wd[li] = (const bf16*)e->wd[li];
+    }
+    a.norm_w = (const bf16*)e->w.norm; a.head_w = (const bf16*)e->w.speech_head;
+    a.res_in = e->res; a.logits = e->logits; a.ws = e->mega_ws; a.sync = e->mega_sync;
+    a.trace = e->trace; a.cos_sin = (const bf16*)e->w.cos_sin; a.pos = e->pos; a.slot = e->slot; a.row_seq = e->row_seq;
+    a.kv_len = e->kv_len; a.bt = e->block_table; a.kv_cache = e->kv_cache;
+    a.layer_bytes = (size_t)e->cfg.num_blocks * CBX_PAGE_BYTES;
+    a.bt_stride = e->bt_stride; a.T = T; a.n_layers = e->w.n_layers; a.vocab = CBX_SPEECH_VOCAB; a.ldl = CBX_LOGITS_LD;
+    a.eps = e->w.rms_eps;
+    static const int mega_flags = getenv("CBX_MEGA_FLAGS") ? atoi(getenv("CBX_MEGA_FLAGS")) : 0;   // debugging aid
+    a.flags = mega_flags;
+    const int rc = launch_decode_mega(a, s);
+    if (rc < 0) return -1;
+    if (rc == 0) return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s);
+  }
   if (forward_layers(e, T, max_kv_len, s, false)) return -1;
   if (T <= 4) {                                         // final norm fused into the head GEMV
     if (gemv_norm_head(e->res, e->w.norm, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD,

@@ -44,7 +44,11 @@ struct EpiArgs {               // EPI 2 only
   const bf16* cos_sin; const int32_t* pos; const int64_t* slot; uint8_t* kv_layer;
 };
 
-template <int BN, int EPI>
+// CN = CTAs per cluster along N.  The CN CTAs of a cluster compute neighbouring column tiles of the
+// SAME row tile, so they need the same activation (A) k-slices: each loads 1/CN of the A tile and
+// TMA-multicasts it into every CTA of the cluster (the decode GEMMs are bound by bytes entering the
+// SMs from L2, and activation re-reads are most of those bytes).
+template <int BN, int EPI, int CN>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                               const __grid_constant__ CUtensorMap tma_b,
                                                               bf16* __restrict__ y, int M, int N, int K, int ldy,
@@ -62,13 +66,17 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   const int n_kb = K / BK / gridDim.z;                 // k-blocks of this CTA's K slice (split-K over blockIdx.z)
   const int kb0 = blockIdx.z * n_kb;
 
+  uint32_t crank = 0;
+  if (CN > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+  constexpr uint16_t kMask = (uint16_t)((1u << CN) - 1);
+
   pdl_trigger();
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CN); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -78,16 +86,27 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   }
   tc_fence_before();
   __syncthreads();
+  if (CN > 1)      // peers' barriers must exist before anyone multicasts into them
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     if (lane == 0) {
-      // Each CTA walks K starting at a different k-block (rotated by its tile index): all CTAs of a
-      // row of tiles read the SAME activation k-slices, and in lockstep they would hammer the same
-      // few L2 slices; the rotation spreads them over the whole activation panel.
-      const int rot = (blockIdx.x + blockIdx.y * 7) % n_kb;
-      auto kc = [&](int kb) { int k = kb + rot; return kb0 + (k >= n_kb ? k - n_kb : k); };
+      auto kc = [&](int kb) { return kb0 + kb; };
+      // A tile: with CN > 1 this CTA fetches rows [crank·128/CN, +128/CN) and multicasts them to the cluster
+      auto load_a = [&](uint8_t* stage, int kb, uint64_t* bar) {
+        if (CN == 1) {
+          tma_load_2d(stage, &tma_a, kc(kb) * BK, m0, bar);
+        } else {
+          constexpr int kRows = BM / CN;
+          asm volatile(
+              "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+              " [%0], [%1, {%3, %4}], [%2], %5;"
+              ::"r"(smem_u32(stage + crank * kRows * 128)), "l"(&tma_a), "r"(smem_u32(bar)), "r"(kc(kb) * BK),
+                "r"(m0 + (int)crank * kRows), "h"(kMask) : "memory");
+        }
+      };
       // weights of the first ring fill do not depend on the previous kernel
       const int n_pre = n_kb < C::kStages ? n_kb : C::kStages;
       for (int kb = 0; kb < n_pre; ++kb) {
@@ -96,13 +115,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       }
       pdl_wait();
       for (int kb = 0; kb < n_pre; ++kb)
-        tma_load_2d(smem + kb * C::kStageBytes, &tma_a, kc(kb) * BK, m0, &full[kb]);
+        load_a(smem + kb * C::kStageBytes, kb, &full[kb]);
       for (int kb = n_pre; kb < n_kb; ++kb) {
         const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_arrive_expect_tx(&full[s], C::kStageBytes);
         uint8_t* sa = smem + s * C::kStageBytes;
-        tma_load_2d(sa, &tma_a, kc(kb) * BK, m0, &full[s]);
+        load_a(sa, kb, &full[s]);
         tma_load_2d(sa + C::kABytes, &tma_b, kc(kb) * BK, n0, &full[s]);
       }
     } else {
@@ -121,7 +140,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k)           // +32 bytes per K=16 step inside the swizzle atom
           umma_bf16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-        umma_commit(&empty[s]);
+        if (CN == 1) umma_commit(&empty[s]);
+        else umma_commit_mc(&empty[s], kMask);      // frees the stage in every CTA of the cluster
       }
       umma_commit(tmem_full);
     }
@@ -193,7 +213,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + cb * 32, r);
       tmem_ld_wait();
       const int col = n0 + cb * 32;
-      if (row < M) {
+      if (row < M && col < N) {
         if (EPI == 1) {
           // packed gate/up: columns [0,16) gate, [16,32) up of the same 16 features
           uint32_t o[8];
@@ -250,6 +270,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     tc_fence_before();
   }
   __syncthreads();
+  if (CN > 1)      // nobody leaves while a peer may still multicast into / arrive on this CTA's shared memory
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, BN);
@@ -296,7 +318,9 @@ int make_map(CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) 
 
 template <int BN, int EPI>
 int set_attr() {
-  cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
+  cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
+  CBX_REQUIRE(e == cudaSuccess, "gemm smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
   CBX_REQUIRE(e == cudaSuccess, "gemm smem attribute: %s", cudaGetErrorString(e));
   return 0;
 }
@@ -318,12 +342,25 @@ int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, 
            const EpiArgs& ea = EpiArgs(), int splits = 1) {
   using C = Cfg<BN>;
   if (cbx::init_gemm()) return -1;
+  // CBX_GEMM_MC=1: clusters of 2 column tiles share the activation tile by TMA multicast.  Measured
+  // on B200 (T=256): gate_up 12.9 -> 13.2 us, QKV 9.7 -> 10.3 us -- multicast halves the L2 reads of
+  // A but every SM still ingests a whole A tile, and SM ingest is what bounds these GEMMs.  Off.
+  static const int mc_env = getenv("CBX_GEMM_MC") ? atoi(getenv("CBX_GEMM_MC")) : 0;
+  int n_tiles = (N + BN - 1) / BN;
+  const int m_tiles = (M + BM - 1) / BM;
+  const bool mc = mc_env != 0 && n_tiles >= 2 && (int64_t)n_tiles * m_tiles * splits <= 2 * 148;
   CUtensorMap ma, mb;
-  if (make_map(&ma, x, M, K, BM)) return -1;
+  if (make_map(&ma, x, M, K, mc ? BM / 2 : BM)) return -1;
   if (make_map(&mb, W, N, K, BN)) return -1;
-  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
-  cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI>, grid, dim3(kThreads), C::kSmem, s, ma, mb, (bf16*)y, M, N, K,
-                             ldy, ea);
+  cudaError_t e;
+  if (mc) {
+    n_tiles = (n_tiles + 1) & ~1;                      // pad to whole clusters: out-of-range tiles load zeros, store nothing
+    e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), C::kSmem, s, 2, ma, mb,
+                           (bf16*)y, M, N, K, ldy, ea);
+  } else {
+    e = launch_pdl(gemm_tc_kernel<BN, EPI, 1>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), C::kSmem, s, ma, mb, (bf16*)y, M,
+                   N, K, ldy, ea);
+  }
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;

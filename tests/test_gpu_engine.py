@@ -242,6 +242,22 @@ def test_engine_batch32_split_k_parity(ops, split_rows, monkeypatch):
         eng.close()
 
 
+@pytest.mark.parametrize("n_pairs", [1, 2])
+def test_engine_persistent_decode_kernel_parity(ops, n_pairs, monkeypatch):
+    """CBX_MEGA=1: the T <= 4 decode step as ONE persistent cooperative kernel (k_mega.cu: weight ring,
+    tagged-word exchanges, mma.sync GEMV).  Same parity bar as the kernel chain, graph and eager,
+    deterministic, and the KV pages it writes serve a later run on the default path."""
+    monkeypatch.setenv("CBX_MEGA", "1")
+    n_steps = 40
+    for use_graph in (True, False):
+        cfg, w, eng = _mk_engine(3, 2, use_graph=use_graph)
+        reqs = _requests(n_pairs, n_steps, temperature=0.0, repetition_penalty=2.0)
+        got = eng.generate(reqs, poll_every=7)
+        assert_stream_parity(got, w, reqs, eng.cfg_scale, n_steps, temperature=0.0, repetition_penalty=2.0)
+        assert eng.generate(reqs, poll_every=4) == got, "same batch must give the same bits"
+        eng.close()
+
+
 def test_engine_logits_tolerance_30layers(ops):
     """Full-depth (30-layer) model, oracle teacher-forced with the engine's own tokens: every
     engine token is the oracle's argmax or within 8 bf16 ulps of its top logit, and >= 80 % of
