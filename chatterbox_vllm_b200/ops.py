@@ -54,11 +54,19 @@ def pack_gate_up(wgu: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def linear(x: torch.Tensor, W: torch.Tensor, epilogue: int = 0, path: int = 0, out: torch.Tensor | None = None):
-    """y = x·Wᵀ ; epilogue=1: SiLU(gate)·up with W packed by pack_gate_up (y is [T, N/2])."""
+def linear(x: torch.Tensor, W: torch.Tensor, epilogue: int = 0, path: int = 0, out: torch.Tensor | None = None,
+           ld: int | None = None):
+    """y = x·Wᵀ ; epilogue=1: SiLU(gate)·up with W packed by pack_gate_up (y is [T, N/2]).
+    ld: row stride of a freshly allocated result (elements) when N itself is not vector-aligned,
+    e.g. the 8194-wide speech head; the returned tensor is the [T, N] view of it."""
     T, K = x.shape
     N = W.shape[0]
     assert W.shape[1] == K
+    if ld is not None:
+        assert out is None and epilogue == 0 and ld >= N
+        buf = torch.empty(T, ld, dtype=BF16, device=x.device)
+        check(load().cbx_linear(_p(x, BF16), _p(W, BF16), _p(buf, BF16), T, N, K, ld, 0, path, _stream()), "linear")
+        return buf[:, :N]
     if out is None:
         out = torch.empty(T, N // 2 if epilogue else N, dtype=BF16, device=x.device)
     check(load().cbx_linear(_p(x, BF16), _p(W, BF16), _p(out, BF16), T, N, K, out.stride(0), epilogue, path,

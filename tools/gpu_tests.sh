@@ -17,3 +17,4 @@ run attn    tests/test_gpu_kernels.py -k "paged_attention"
 run fused   tests/test_gpu_kernels.py -k "fused or residual or split_k"
 run sampler tests/test_gpu_engine.py -k "sampler or prefill_embed"
 run engine  tests/test_gpu_engine.py -k "engine"
+run facade  tests/test_gpu_facade.py
