@@ -311,3 +311,79 @@ extern "C" int cbx_pack_gate_up(const void* src, void* dst, int I, int K, void* 
   CBX_CHECK_LAUNCH("pack_gate_up");
   return 0;
 }
+
+// ---- token post-processing: the hand-off format between T3 and the vocoder ----------------------
+// Per request (reference tts.py:448-465 + s3tokenizer/__init__.py:38-78, on un-offset speech ids):
+// cut at the first stop id and crop `tail_crop` tokens before it; keep what lies between the first
+// SOS (exclusive) and the first EOS; drop ids >= sos (6561); cap at guard_cap (tts.py:466-486).
+// One CTA per request; order-preserving compaction with a ballot scan; int64 out as S3Gen takes it.
+namespace {
+__global__ void __launch_bounds__(256) postprocess_tokens_kernel(const int32_t* __restrict__ out_tokens,
+                                                                 const int32_t* __restrict__ n_out, int out_stride,
+                                                                 const int32_t* __restrict__ slots, int sos, int eos,
+                                                                 int tail_crop, const int32_t* __restrict__ guard_cap,
+                                                                 int64_t* __restrict__ dst, int dst_stride,
+                                                                 const int32_t* __restrict__ dst_rows,
+                                                                 int32_t* __restrict__ dst_len) {
+  __shared__ int s_stop, s_sos, s_eos, s_warp[8], s_base;
+  const int item = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int32_t* src = out_tokens + (size_t)slots[item] * out_stride;
+  int n = n_out[slots[item]];
+  n = n < 0 ? 0 : (n > out_stride ? out_stride : n);
+  if (tid == 0) { s_stop = n; s_sos = n; s_eos = n; s_base = 0; }
+  __syncthreads();
+  for (int i = tid; i < n; i += 256)
+    if (src[i] == eos) atomicMin(&s_stop, i);
+  __syncthreads();
+  if (s_stop < n) {                                   // truncate at the first stop, crop the tail before it
+    const int crop = tail_crop > 0 ? tail_crop : 0;
+    n = s_stop - crop;
+    n = n < 0 ? 0 : n;
+  }
+  __syncthreads();
+  if (tid == 0) { s_sos = n; s_eos = n; }
+  __syncthreads();
+  for (int i = tid; i < n; i += 256) {
+    const int t = src[i];
+    if (t == sos) atomicMin(&s_sos, i);
+    if (t == eos) atomicMin(&s_eos, i);
+  }
+  __syncthreads();
+  const int start = s_sos < n ? s_sos + 1 : 0;
+  const int end = s_eos < n ? s_eos : n;
+  const int cap = guard_cap ? guard_cap[item] : 0x7fffffff;
+  int64_t* out = dst + (size_t)dst_rows[item] * dst_stride;
+  for (int i0 = start; i0 < end; i0 += 256) {         // CTA-uniform trip count
+    const int i = i0 + tid;
+    const int t = i < end ? src[i] : sos;
+    const bool keep = i < end && t < sos;
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    int off = s_base;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    off += __popc(bal & ((1u << lane) - 1));
+    if (keep && off < cap && off < dst_stride) out[off] = (int64_t)t;
+    __syncthreads();
+    if (tid == 0) { int tot = 0; for (int w = 0; w < 8; ++w) tot += s_warp[w]; s_base += tot; }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    int len = s_base;
+    len = len > cap ? cap : len;
+    dst_len[dst_rows[item]] = len > dst_stride ? dst_stride : len;
+  }
+}
+}  // namespace
+
+extern "C" int cbx_postprocess_tokens(const int32_t* out_tokens, const int32_t* n_out, int out_stride, const int32_t* slots,
+                                      int n, int sos_token, int eos_token, int tail_crop, const int32_t* guard_cap,
+                                      int64_t* dst, int dst_stride, const int32_t* dst_rows, int32_t* dst_len, void* stream) {
+  if (n <= 0) return 0;
+  CBX_REQUIRE(out_tokens && n_out && slots && dst && dst_rows && dst_len && out_stride > 0 && dst_stride > 0,
+              "cbx_postprocess_tokens: bad arguments");
+  postprocess_tokens_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(out_tokens, n_out, out_stride, slots, sos_token, eos_token,
+                                                               tail_crop, guard_cap, dst, dst_stride, dst_rows, dst_len);
+  CBX_CHECK_LAUNCH("postprocess_tokens");
+  return 0;
+}

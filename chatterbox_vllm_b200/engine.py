@@ -318,7 +318,23 @@ class T3Engine:
         torch.cuda.current_stream().wait_stream(self.stream)
         return out
 
-    def _generate(self, reqs: list[Request], poll_every: int) -> list[list[int]]:
+    def generate_device(self, reqs: list[Request], tail_crop: int = 2, guard_caps: list[int] | None = None,
+                        poll_every: int = 32) -> tuple[torch.Tensor, torch.Tensor]:
+        """generate() with the vocoder hand-off done on the device (tts.py:448-486): returns
+        (int64 [n, max_tokens] S3Gen-ready speech ids, int32 [n] counts), both CUDA tensors — no token
+        leaves the GPU; the host only polls the `finished` flags."""
+        n = len(reqs)
+        width = max([r.params.max_tokens for r in reqs], default=1)
+        dst = torch.zeros(max(n, 1), width, dtype=torch.int64, device=self.device)
+        dst_len = torch.zeros(max(n, 1), dtype=torch.int32, device=self.device)
+        caps = None if guard_caps is None else torch.tensor(guard_caps, dtype=torch.int32, device=self.device)
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            self._generate(reqs, poll_every, handoff=(dst, dst_len, caps, tail_crop))
+        torch.cuda.current_stream().wait_stream(self.stream)
+        return dst[:n], dst_len[:n]
+
+    def _generate(self, reqs: list[Request], poll_every: int, handoff=None) -> list[list[int]]:
         n = len(reqs)
         if n == 0:
             return []
@@ -369,13 +385,20 @@ class T3Engine:
                         slot_len[b] += steps
                 fin = self.sb.finished[:B].cpu().tolist()      # the only host sync: every poll_every steps
                 done = [b for b in active if fin[b]]
-                if done:
+                if done and handoff is not None:            # retire on the device: post-process straight into the result rows
+                    dst, dst_len, caps, crop = handoff
+                    rows = torch.tensor([slot_req[b] for b in done], dtype=torch.int32, device=self.device)
+                    ops.postprocess_tokens(self.sb, torch.tensor(done, dtype=torch.int32, device=self.device), dst, rows,
+                                           dst_len, crop, None if caps is None else caps[rows.long()].contiguous(),
+                                           eos=self.sb.stop_token)
+                elif done:
                     n_out = self.sb.n_out[:B].cpu().tolist()
                     toks = self.sb.out_tokens[:B].cpu().numpy()
                     for b in done:
                         out[slot_req[b]] = (toks[b, :n_out[b]] + SPEECH_TOKEN_OFFSET).tolist()
-                        self._release(slot_held.pop(b)[1])
-                        slot_req[b] = None
+                for b in done:
+                    self._release(slot_held.pop(b)[1])
+                    slot_req[b] = None
         finally:
             for _, held in slot_held.values():
                 self._release(held)

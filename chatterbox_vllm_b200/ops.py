@@ -234,6 +234,18 @@ def prefill_embed(desc, cond_emb, text_emb, text_pos, speech_emb, speech_pos, ou
     return out
 
 
+def postprocess_tokens(sb: "SamplerBuffers", slots: torch.Tensor, dst: torch.Tensor, dst_rows: torch.Tensor,
+                       dst_len: torch.Tensor, tail_crop: int = 2, guard_cap: torch.Tensor | None = None,
+                       sos: int = 6561, eos: int = 6562) -> None:
+    """Device-side T3 -> vocoder hand-off for the sampler slots `slots` (int32 [n]): stop cut, tail crop,
+    SOS/EOS framing, < 6561 filter, guard cap; int64 ids into dst[dst_rows[i]], counts into dst_len."""
+    n = slots.numel()
+    check(load().cbx_postprocess_tokens(_p(sb.out_tokens, torch.int32), _p(sb.n_out, torch.int32), sb.out_stride,
+                                        _p(slots, torch.int32), n, sos, eos, tail_crop, _p(guard_cap, torch.int32),
+                                        _p(dst, torch.int64), dst.stride(0), _p(dst_rows, torch.int32),
+                                        _p(dst_len, torch.int32), _stream()), "postprocess_tokens")
+
+
 class BlockPool:
     """Host block pool (C++ in libcbx_t3.so) with vLLM's allocation policy."""
 

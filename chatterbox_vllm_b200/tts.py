@@ -62,6 +62,22 @@ def postprocess_tokens(tok_ids: list[int], tail_crop_k: int = 2) -> torch.Tensor
     return x[x < START_SPEECH]
 
 
+def guard_cap_tokens(prompt: str) -> int:
+    """tts.py:466-486: the per-prompt overrun guard applied AFTER decoding — ceil(1.6 · clamp(ceil(2.2 ·
+    non-space chars of the prompt without [tags]), 64, 1200)) speech tokens at most."""
+    try:
+        clean = re.sub(r"\[[^\]]+\]", "", prompt)
+        n_chars = sum(1 for ch in clean if not ch.isspace())
+        tpc = float(os.environ.get("CHATTERBOX_TOKENS_PER_CHAR", "2.2"))
+        tmin = int(os.environ.get("CHATTERBOX_TOKENS_MIN", "64"))
+        tmax = int(os.environ.get("CHATTERBOX_TOKENS_MAX", "1200"))
+        guard = float(os.environ.get("CHATTERBOX_TOKENS_GUARD_MULT", "1.6"))
+        est = max(tmin, min(tmax, int(math.ceil(n_chars * tpc))))
+        return int(math.ceil(est * guard))
+    except Exception:
+        return 1 << 30
+
+
 def pre_cap_tokens(prompts: list[str], max_tokens: int, max_model_len: int) -> int:
     """tts.py:372-399: per-prompt estimate ceil(2.2 · non-space chars) clamped to [64, 1200], guard
     ×1.6; the batch cap is min over prompts + 16, then min with max_tokens and max_model_len.
@@ -244,15 +260,21 @@ class ChatterboxTTS:
             sp = SamplingParams(temperature=temp_use, top_p=top_p_use, repetition_penalty=repetition_penalty,
                                 max_tokens=min(cap, budget), **sp_kw)
             reqs.append(Request(ids, cond_emb, sp, penalize_prompt_ids=self.variant == "multilingual"))
+        crop = int(os.environ.get("CHATTERBOX_TAIL_CROP_TOKENS", "2"))
         t0 = time.time()
         with torch.inference_mode():
-            outs = self.t3.generate(reqs)
+            if raw or not hasattr(self.t3, "generate_device"):
+                outs = self.t3.generate(reqs)
+            else:
+                # stop cut / tail crop / framing / filter / overrun guard run on the device; only the
+                # counts come back (tts.py:448-486)
+                toks, lens = self.t3.generate_device(reqs, tail_crop=crop, guard_caps=[guard_cap_tokens(w) for w in wrapped])
+                outs = [toks[i, :n] for i, n in enumerate(lens.tolist())]
         self.last_t3_seconds = time.time() - t0
         print(f"[T3] Speech Token Generation time: {self.last_t3_seconds:.2f}s")
-        if raw:
+        if raw or hasattr(self.t3, "generate_device"):
             return outs
-        crop = int(os.environ.get("CHATTERBOX_TAIL_CROP_TOKENS", "2"))
-        return [postprocess_tokens(o, crop) for o in outs]
+        return [postprocess_tokens(o, crop)[:guard_cap_tokens(w)] for o, w in zip(outs, wrapped)]
 
     def shutdown(self):
         if self.t3 is not None:

@@ -158,6 +158,16 @@ int cbx_decode_prepare(const void* speech_emb, const int32_t* last_tok, const in
                        const int32_t* seq_len, const int32_t* block_table, int bt_stride,
                        void* x, int32_t* pos, int64_t* slot, int32_t* kv_len, int B, void* stream);
 
+/* Token post-processing = the T3 -> vocoder hand-off (reference tts.py:448-486 + models/s3tokenizer/
+ * __init__.py:38-78, which run as Python list surgery + a torch mask per prompt): for item i, read
+ * the n_out[slots[i]] speech ids of sampler slot slots[i] (un-offset space), cut at the first
+ * eos_token and crop tail_crop ids before it, keep what lies after the first sos_token and before the
+ * first eos_token, drop ids >= sos_token, cap at guard_cap[i] (NULL = no cap), and write int64 ids to
+ * dst[dst_rows[i]*dst_stride ...] with the count in dst_len[dst_rows[i]]. */
+int cbx_postprocess_tokens(const int32_t* out_tokens, const int32_t* n_out, int out_stride, const int32_t* slots,
+                           int n, int sos_token, int eos_token, int tail_crop, const int32_t* guard_cap,
+                           int64_t* dst, int dst_stride, const int32_t* dst_rows, int32_t* dst_len, void* stream);
+
 /* t3.py:548-569 (full-block prefill embeds).  desc int32 [T,4] = {kind, a, b, c}:
  * kind 0: cond_emb row  (a = request, b = row 0..33) from cond_emb fp32 [n_req,34,1024];
  * kind 1: text row       text_emb[a] + text_pos[b]; kind 2: zero row (uncond text);

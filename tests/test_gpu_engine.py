@@ -258,6 +258,26 @@ def test_engine_persistent_decode_kernel_parity(ops, n_pairs, monkeypatch):
         eng.close()
 
 
+def test_engine_device_handoff_equals_host_postprocessing(ops):
+    """generate_device(): tokens never leave the GPU; the result must equal generate() followed by the
+    reference's host-side list surgery (tts.py:448-486), with slot recycling in between."""
+    from oracle import prompt_ref
+    cfg, w, eng = _mk_engine(2, 3)
+    # a stop id the random model emits now and then, so that streams end at different lengths
+    reqs = _requests(7, 40, temperature=0.9, top_p=0.95, repetition_penalty=1.2)
+    for i, r in enumerate(reqs):
+        r.params.seed, r.params.ignore_eos = 11 + i, False
+    host = eng.generate(reqs, poll_every=6)
+    caps = [9, 1000, 1000, 20, 1000, 1000, 3]
+    toks, lens = eng.generate_device(reqs, tail_crop=2, guard_caps=caps, poll_every=6)
+    assert toks.is_cuda and toks.dtype == torch.int64 and lens.dtype == torch.int32
+    for i in range(len(reqs)):
+        want = prompt_ref.postprocess_tokens(host[i], 2)[:caps[i]]
+        assert int(lens[i]) == len(want) and toks[i, :len(want)].cpu().tolist() == want.tolist(), f"request {i}"
+    assert eng.pool.num_free() == eng.num_blocks - 1
+    eng.close()
+
+
 def test_engine_logits_tolerance_30layers(ops):
     """Full-depth (30-layer) model, oracle teacher-forced with the engine's own tokens: every
     engine token is the oracle's argmax or within 8 bf16 ulps of its top logit, and >= 80 % of

@@ -358,3 +358,50 @@ def test_paged_attention_prefill_causal(ops, lens):
         s, p = rows[i]
         want = _ref_attn(cfg, qkv_all[s], q[i, :1024].float(), p + 1, cs)
         assert_close_bf16(out[i], want, ulps=1.0, atol=2e-3, what=f"prefill row {i} (seq {s}, pos {p})")
+
+
+# ------------------------------------------------------------------ token post-processing
+def test_postprocess_tokens_matches_oracle_bit_exact():
+    """cbx_postprocess_tokens against the CPU restatement of tts.py:448-465 + drop_invalid_tokens
+    on adversarial streams: stop early / late / absent, SOS and EOS inside, invalid ids, empty
+    results, guard caps, slot -> row scatter."""
+    import numpy as np
+    from chatterbox_vllm_b200 import ops
+    from oracle import prompt_ref
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(7)
+    B, stride = 24, 700
+    sb = ops.SamplerBuffers(B, stride, dev)
+    toks = rng.integers(0, 6561, size=(B, stride)).astype(np.int32)
+    n_out = rng.integers(0, stride + 1, size=B).astype(np.int32)
+    n_out[0], n_out[1], n_out[2] = 0, 1, stride
+    for b in range(B):
+        n = int(n_out[b])
+        if n == 0:
+            continue
+        if b % 3 != 0:                                   # a stop token somewhere (not always the last)
+            toks[b, rng.integers(0, n)] = 6562
+        if b % 4 == 1:
+            toks[b, rng.integers(0, n)] = 6561           # an SOS inside
+        if b % 5 == 2:
+            toks[b, rng.integers(0, n, size=5)] = rng.integers(6563, 8194, size=5)   # ids beyond the speech vocab
+    toks[3, 0] = 6562                                    # stop first: empty result
+    toks[4, :2] = (5, 6562)                              # stop inside the cropped tail
+    sb.out_tokens.copy_(torch.from_numpy(toks))
+    sb.n_out.copy_(torch.from_numpy(n_out))
+    for crop, use_caps in ((2, False), (0, True), (5, True)):
+        slots = torch.tensor(rng.permutation(B).astype(np.int32), device=dev)
+        rows = torch.tensor(rng.permutation(B).astype(np.int32), device=dev)
+        caps = rng.integers(1, 400, size=B).astype(np.int32) if use_caps else None
+        dst = torch.full((B, stride), -7, dtype=torch.int64, device=dev)
+        dlen = torch.full((B,), -1, dtype=torch.int32, device=dev)
+        ops.postprocess_tokens(sb, slots, dst, rows, dlen, crop, None if caps is None else torch.from_numpy(caps).to(dev))
+        dst, dlen = dst.cpu().numpy(), dlen.cpu().numpy()
+        for i in range(B):
+            b, r = int(slots[i]), int(rows[i])
+            want = prompt_ref.postprocess_tokens((toks[b, :n_out[b]].astype(np.int64) + 1000).tolist(), crop)
+            if caps is not None:
+                want = want[:caps[i]]
+            assert dlen[r] == len(want), f"slot {b}: {dlen[r]} vs {len(want)} tokens (crop {crop})"
+            assert np.array_equal(dst[r, :len(want)], want), f"slot {b} (crop {crop})"
+            assert (dst[r, len(want):] == -7).all(), "nothing may be written past the result"

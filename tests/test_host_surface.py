@@ -123,3 +123,14 @@ def test_entokenizer_matches_survey_fixture(golden_dir):
     s = "[START]" + text_utils.punc_norm("You are listening to a demo of the Chatterbox TTS model running on VLLM.") + "[STOP]"
     assert tok.encode(s) == g["demo_ids"]
     assert tok.decode(tok.encode("[START]Hello there.[STOP]")) == "[START]Hello there."
+
+
+def test_guard_cap_tokens_follows_reference_formula(monkeypatch):
+    """tts.py:466-486: est = clamp(ceil(2.2 * non-space chars outside [tags]), 64, 1200); cap = ceil(1.6 * est)."""
+    from chatterbox_vllm_b200.tts import guard_cap_tokens
+    assert guard_cap_tokens("[START]Hello world.[STOP]") == 103            # 11 chars -> est 64 -> ceil(102.4)
+    long = "[START]" + "a" * 400 + "[STOP]"
+    assert guard_cap_tokens(long) == 1410                                  # 400 * 2.2 = 880.0000000000001 -> 881 -> ceil(1409.6), as the reference's float math
+    assert guard_cap_tokens("[START]" + "a" * 4000 + "[STOP]") == 1920     # est clamps at 1200
+    monkeypatch.setenv("CHATTERBOX_TOKENS_GUARD_MULT", "2.0")
+    assert guard_cap_tokens("[fr][START]x y[STOP]") == 128
