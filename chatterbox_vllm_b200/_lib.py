@@ -59,6 +59,9 @@ _PROTOS = {
     "cbx_cfg_sample": (C.c_int, [vp, C.POINTER(SamplerState), C.c_int, vp]),
     "cbx_decode_prepare": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_prefill_embed": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]),
+    "cbx_cond_workspace_bytes": (C.c_int64, [C.c_int]),
+    "cbx_cond_encode": (C.c_int, [vp, vp, vp, C.c_int, C.c_float, vp, vp, vp]),
+    "cbx_cond_emotion_row": (C.c_int, [vp, C.c_float, vp, vp]),
     "cbx_postprocess_tokens": (C.c_int, [vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, vp, vp, vp]),
     "cbx_engine_workspace_bytes": (C.c_int64, [C.POINTER(EngineCfg)]),
     "cbx_engine_create": (vp, [C.POINTER(EngineCfg), C.POINTER(Weights), vp, vp, vp, C.POINTER(SamplerState)]),

@@ -108,6 +108,7 @@ class ChatterboxTTS:
         self.target_device, self.max_model_len = target_device, max_model_len
         self.t3, self.tokenizer, self.variant = t3, tokenizer, variant
         self.emotion_adv_fc = emotion_adv_fc          # cond_enc.emotion_adv_fc.weight [1024, 1] fp32
+        self.cond_encoder = None                      # T3CondEncoder when the checkpoint carries cond_enc.*
         self.default_cond_emb, self.default_s3gen_ref = default_cond_emb, default_s3gen_ref or {}
         self.vocoder, self.conditioner = vocoder, conditioner
         self._cond_cache: dict = {}
@@ -129,8 +130,14 @@ class ChatterboxTTS:
         eng = T3Engine(state_dict, device=target_device if target_device != "cuda" else "cuda:0",
                        max_pairs=max_pairs, max_model_len=max_model_len, **kwargs)
         fc = state_dict.get("cond_enc.emotion_adv_fc.weight")
-        return cls(target_device, max_model_len, eng, tokenizer,
-                   emotion_adv_fc=fc.float().cpu() if fc is not None else None, variant=variant, **extra)
+        tts = cls(target_device, max_model_len, eng, tokenizer,
+                  emotion_adv_fc=fc.float().cpu() if fc is not None else None, variant=variant, **extra)
+        if "cond_enc.perceiver.attn.to_q.weight" in state_dict:   # conditioning encoder on the device (cond_enc.py, perceiver.py)
+            from .cond_enc import T3CondEncoder
+            tts.cond_encoder = T3CondEncoder({k: v for k, v in state_dict.items() if k.startswith("cond_enc.")},
+                                             state_dict["speech_emb.weight"], state_dict["speech_pos_emb.emb.weight"],
+                                             device=str(eng.device))
+        return tts
 
     @classmethod
     def from_local(cls, ckpt_dir: Union[str, Path], target_device: str = "cuda", max_model_len: int = 1000,
@@ -175,6 +182,8 @@ class ChatterboxTTS:
             out = (self.default_s3gen_ref, self.default_cond_emb)
         elif self.conditioner is not None:
             out = self.conditioner(wav_fpath)
+            if len(out) == 3:                              # (s3gen_ref, speaker_emb[256], prompt speech tokens): encode here
+                out = self.conditionals_from_features(out[1], out[2], s3gen_ref=out[0])
         else:
             raise NotImplementedError(
                 "conditioning from audio needs the reference's VoiceEncoder/S3Tokenizer front-ends, which are "
@@ -185,10 +194,23 @@ class ChatterboxTTS:
         self._cond_cache[wav_fpath] = out
         return out
 
+    def conditionals_from_features(self, speaker_emb: torch.Tensor, prompt_tokens: torch.Tensor,
+                                   s3gen_ref: Optional[dict] = None) -> tuple[Optional[dict], torch.Tensor]:
+        """The T3 half of get_audio_conditionals (tts.py:238-247) on the device: voice-encoder embedding
+        [256] + S3 prompt tokens [<= 150] -> cond_emb [34,1024] fp32, left in GPU memory (the reference
+        moves it to the CPU so that it can be pickled to the vLLM process)."""
+        if getattr(self, "cond_encoder", None) is None:
+            raise RuntimeError("checkpoint has no cond_enc.* weights; cannot encode conditionals")
+        return s3gen_ref, self.cond_encoder(speaker_emb, prompt_tokens, 0.5)
+
     def update_exaggeration(self, cond_emb: torch.Tensor, exaggeration: float) -> torch.Tensor:
         """tts.py:249-257: row 33 ← emotion_adv_fc(exaggeration) (Linear(1→1024), no bias)."""
         if exaggeration == 0.5:
             return cond_emb
+        if getattr(self, "cond_encoder", None) is not None and cond_emb.is_cuda:
+            new = cond_emb.clone()
+            new[-1] = self.cond_encoder.emotion_row(exaggeration).to(new.dtype)
+            return new
         if self.emotion_adv_fc is None:
             raise RuntimeError("checkpoint has no cond_enc.emotion_adv_fc.weight; cannot change exaggeration")
         new = cond_emb.clone()

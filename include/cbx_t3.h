@@ -158,6 +158,32 @@ int cbx_decode_prepare(const void* speech_emb, const int32_t* last_tok, const in
                        const int32_t* seq_len, const int32_t* block_table, int bt_stride,
                        void* x, int32_t* pos, int64_t* slot, int32_t* kv_len, int B, void* stream);
 
+/* ---- conditioning-prefix producer ------------------------------------------------
+ * T3CondEnc + Perceiver of the reference (models/t3/modules/cond_enc.py:57-123, perceiver.py:116-215;
+ * driven from tts.py:238-257), fp32 like the reference.  All pointers are device pointers to fp32
+ * tensors with the checkpoint's shapes ("cond_enc.*" of t3_cfg.safetensors). */
+typedef struct {
+  const float* spkr_w;      /* spkr_enc.weight                [1024,256]  */
+  const float* spkr_b;      /* spkr_enc.bias                  [1024]      */
+  const float* emo_w;       /* emotion_adv_fc.weight          [1024,1]    */
+  const float* query;       /* perceiver.pre_attention_query  [1,32,1024] */
+  const float* ln_w;        /* perceiver.attn.norm.weight     [1024]      */
+  const float* ln_b;        /* perceiver.attn.norm.bias       [1024]      */
+  const float* wq; const float* bq;   /* perceiver.attn.to_q       [1024,1024], [1024] */
+  const float* wk; const float* bk;   /* perceiver.attn.to_k                           */
+  const float* wv; const float* bv;   /* perceiver.attn.to_v                           */
+  const float* wo; const float* bo;   /* perceiver.attn.proj_out                       */
+  const float* speech_emb;  /* speech_emb.weight              [8194,1024] */
+  const float* speech_pos;  /* speech_pos_emb.emb.weight      [>= n_prompt,1024] */
+} cbx_cond_weights;
+int64_t cbx_cond_workspace_bytes(int max_prompt);
+/* out fp32 [34,1024] = spkr_enc(speaker_emb[256]) | perceiver(speech_emb[tok]+speech_pos[0..n)) (32 rows)
+ * | emotion_adv_fc(emotion).  prompt_tokens int32 [n_prompt], 1 <= n_prompt <= 1024 (the reference uses 150). */
+int cbx_cond_encode(const cbx_cond_weights* w, const float* speaker_emb, const int32_t* prompt_tokens, int n_prompt,
+                    float emotion, void* workspace, float* out, void* stream);
+/* row fp32 [1024] = emotion_adv_fc(emotion): what update_exaggeration (tts.py:249-257) recomputes. */
+int cbx_cond_emotion_row(const cbx_cond_weights* w, float emotion, float* row, void* stream);
+
 /* Token post-processing = the T3 -> vocoder hand-off (reference tts.py:448-486 + models/s3tokenizer/
  * __init__.py:38-78, which run as Python list surgery + a torch mask per prompt): for item i, read
  * the n_out[slots[i]] speech ids of sampler slot slots[i] (un-offset space), cut at the first

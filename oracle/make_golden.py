@@ -10,6 +10,8 @@ Fixtures and what pins them:
   sampler_vllm.npz     vLLM 0.22 torch sampler ops on seeded logits
   block_pool_vllm.json vLLM 0.22 BlockPool on a scripted admit/finish sequence
   prompt_lengths.json  reference tokenizer.json + benchmark.py chunker on docs/benchmark-text-1.txt
+  cond_enc.npz         the REFERENCE'S OWN T3CondEnc / Perceiver modules (models/t3/modules/cond_enc.py,
+                       perceiver.py) run on seeded weights and inputs (oracle.cond_ref.random_*)
 """
 import importlib.util
 import json
@@ -139,9 +141,47 @@ def prompt_lengths():
               open(f"{OUT}/prompt_lengths.json", "w"))
 
 
+def cond_enc():
+    """Runs the reference's own modules (they only need torch + einops) and stores their output."""
+    import types
+    from oracle import cond_ref
+    base = f"{REF}/src/chatterbox_vllm/models/t3/modules/"
+    pkg = types.ModuleType("refmods")
+    pkg.__path__ = [base]
+    sys.modules["refmods"] = pkg
+    mods = {}
+    for name in ("t3_config", "perceiver", "cond_enc"):
+        spec = importlib.util.spec_from_file_location("refmods." + name, base + name + ".py")
+        m = importlib.util.module_from_spec(spec)
+        sys.modules["refmods." + name] = m
+        spec.loader.exec_module(m)
+        mods[name] = m
+    enc = mods["cond_enc"].T3CondEnc(mods["t3_config"].T3Config()).eval()
+    out = {}
+    for case, (wseed, iseed, n_prompt, emotion) in enumerate([(11, 12, 150, 0.5), (21, 22, 37, 0.8)]):
+        sd = cond_ref.random_state_dict(wseed)
+        enc.load_state_dict(sd)
+        speech_emb, speech_pos, speaker, tokens = cond_ref.random_inputs(iseed, n_prompt)
+        prompt_emb = speech_emb[tokens] + speech_pos[:n_prompt]                       # tts.py:238
+        with torch.inference_mode():
+            cond = mods["cond_enc"].T3Cond(speaker_emb=speaker.view(1, -1), cond_prompt_speech_tokens=tokens.view(1, -1),
+                                           cond_prompt_speech_emb=prompt_emb, emotion_adv=emotion * torch.ones(1, 1))
+            y = enc(cond)
+            row = enc.emotion_adv_fc(0.3 * torch.ones(1, 1))[0]                       # tts.py:254
+        assert y.shape == (34, 1024)
+        out[f"meta{case}"] = np.array([wseed, iseed, n_prompt], np.int64)
+        out[f"emotion{case}"] = np.array([emotion], np.float64)
+        out[f"cond{case}"] = y.numpy()
+        out[f"row03_{case}"] = row.numpy()
+    np.savez_compressed(os.path.join(OUT, "cond_enc.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    for fn in (hf_backbone, rope, sampler, block_pool, prompt_lengths):
+    only = sys.argv[1:]
+    for fn in (hf_backbone, rope, sampler, block_pool, prompt_lengths, cond_enc):
+        if only and fn.__name__ not in only:
+            continue
         try:
             fn()
             print("ok  ", fn.__name__)

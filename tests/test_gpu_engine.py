@@ -278,6 +278,50 @@ def test_engine_device_handoff_equals_host_postprocessing(ops):
     eng.close()
 
 
+def test_tts_surface_device_conditionals_and_token_handoff(ops):
+    """ChatterboxTTS over the real engine: conditionals encoded on the device from (speaker embedding,
+    prompt tokens) by a `conditioner` standing in for the audio front-ends, exaggeration updated on
+    the device, tokens handed to the vocoder as CUDA int64 without a host round trip."""
+    from chatterbox_vllm_b200.tts import ChatterboxTTS
+    from oracle import cond_ref, prompt_ref
+
+    class Tok:
+        def encode(self, s):
+            return [255] + [3 + (ord(c) % 600) for c in s[7:-6]][:30] + [0]
+
+    cfg = T3ModelConfig(n_layers=2)
+    w = T3Weights.random(cfg, seed=0, head_scale=16.0, norm_jitter=0.1)
+    sd = dict(w.state_dict())
+    csd = cond_ref.random_state_dict(5)
+    sd.update({"cond_enc." + k: v for k, v in csd.items()})
+    speech_emb, speech_pos = sd["speech_emb.weight"].float(), sd["speech_pos_emb.emb.weight"].float()
+    g = torch.Generator().manual_seed(3)
+    spk, ptoks = torch.randn(256, generator=g), torch.randint(0, 6561, (150,), generator=g)
+    seen = {}
+
+    def vocoder(tokens, ref, n_timesteps=10):
+        seen.setdefault("tok", []).append(tokens)
+        return torch.zeros(1, 8)
+
+    tts = ChatterboxTTS.from_state_dict(sd, Tok(), "cuda", 256, 4, conditioner=lambda path: ({"ref": path}, spk, ptoks),
+                                        vocoder=vocoder)
+    ref, cond = tts.get_audio_conditionals("voice.wav")
+    assert ref == {"ref": "voice.wav"} and cond.is_cuda and cond.shape == (34, 1024)
+    want = cond_ref.cond_encode(csd, spk, ptoks, speech_emb, speech_pos, 0.5)
+    assert float((cond.cpu() - want).abs().max()) <= 2e-5 * float(want.abs().max())
+    c8 = tts.update_exaggeration(cond, 0.8)
+    assert c8.is_cuda and torch.equal(c8[:33], cond[:33])
+    assert torch.equal(c8[33].cpu(), cond_ref.emotion_row(csd, 0.8))
+    wavs = tts.generate(["Hello there.", "A second, longer prompt."], audio_prompt_path="voice.wav", exaggeration=0.8,
+                        max_tokens=24, temperature=0.0)
+    assert len(wavs) == 2 and len(seen["tok"]) == 2
+    raw = tts.generate_tokens(["Hello there.", "A second, longer prompt."], c8, max_tokens=24, temperature=0.0, raw=True)
+    for t, r in zip(seen["tok"], raw):
+        assert t.is_cuda and t.dtype == torch.int64
+        assert t.cpu().tolist() == prompt_ref.postprocess_tokens(r, 2).tolist()
+    tts.shutdown()
+
+
 def test_engine_logits_tolerance_30layers(ops):
     """Full-depth (30-layer) model, oracle teacher-forced with the engine's own tokens: every
     engine token is the oracle's argmax or within 8 bf16 ulps of its top logit, and >= 80 % of

@@ -405,3 +405,38 @@ def test_postprocess_tokens_matches_oracle_bit_exact():
             assert dlen[r] == len(want), f"slot {b}: {dlen[r]} vs {len(want)} tokens (crop {crop})"
             assert np.array_equal(dst[r, :len(want)], want), f"slot {b} (crop {crop})"
             assert (dst[r, len(want):] == -7).all(), "nothing may be written past the result"
+
+
+# ------------------------------------------------------------------ conditioning encoder
+COND_REL_TOL = 2e-5      # fp32 kernels vs the fp32 reference modules: summation order only
+
+
+def test_cond_encoder_matches_reference_modules_fp32():
+    """cbx_cond_encode (T3CondEnc + Perceiver, fp32 FMA) against tests/golden/cond_enc.npz — the output
+    of the reference's own modules — and against the oracle on a ragged prompt length."""
+    import os
+    import numpy as np
+    from chatterbox_vllm_b200.cond_enc import T3CondEncoder
+    from oracle import cond_ref
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "cond_enc.npz"))
+    for c in (0, 1):
+        wseed, iseed, n = g[f"meta{c}"].tolist()
+        sd = cond_ref.random_state_dict(wseed)
+        speech_emb, speech_pos, spk, tok = cond_ref.random_inputs(iseed, n)
+        enc = T3CondEncoder({"cond_enc." + k: v for k, v in sd.items()}, speech_emb, speech_pos)
+        got = enc(spk, tok, float(g[f"emotion{c}"][0]))
+        want = torch.from_numpy(g[f"cond{c}"])
+        assert got.is_cuda and got.dtype == torch.float32 and got.shape == (34, 1024)
+        scale = float(want.abs().max())
+        err = float((got.cpu() - want).abs().max())
+        assert err <= COND_REL_TOL * scale, f"case {c}: max-abs {err:.3e} at scale {scale:.2f}"
+        assert torch.equal(got[33].cpu(), want[33]), "the emotion row is one multiply: bit-exact"
+        row = enc.emotion_row(0.3)
+        assert torch.equal(row.cpu(), torch.from_numpy(g[f"row03_{c}"]))
+        # another prompt length through the same encoder object (workspace reuse), vs the oracle
+        for n2 in (1, 33, 149):
+            got2 = enc(spk, tok[:n2], 0.5).cpu()
+            want2 = cond_ref.cond_encode(sd, spk, tok[:n2], speech_emb, speech_pos, 0.5)
+            assert float((got2 - want2).abs().max()) <= COND_REL_TOL * float(want2.abs().max()), f"n_prompt={n2}"
+    with pytest.raises(ValueError):
+        enc(spk, tok[:0])

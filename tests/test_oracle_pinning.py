@@ -134,3 +134,23 @@ def test_precap_and_postprocess():
     assert prompt_ref.postprocess_tokens([1001, 1002, 1003]).tolist() == [1, 2, 3]
     assert prompt_ref.clamp_sampling(0.8, 0.8, "en", False) == (0.5, 0.5)
     assert prompt_ref.clamp_sampling(0.8, 0.8, "en", True) == (0.0, 1.0)
+
+
+def test_cond_encoder_oracle_matches_reference_modules():
+    """tests/golden/cond_enc.npz was produced by the reference's OWN T3CondEnc / Perceiver modules
+    (oracle/make_golden.py::cond_enc); the restatement must reproduce it from the seeds alone."""
+    import os
+    import numpy as np
+    import torch
+    from oracle import cond_ref
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "cond_enc.npz"))
+    for c in (0, 1):
+        wseed, iseed, n = g[f"meta{c}"].tolist()
+        sd = cond_ref.random_state_dict(wseed)
+        speech_emb, speech_pos, spk, tok = cond_ref.random_inputs(iseed, n)
+        y = cond_ref.cond_encode(sd, spk, tok, speech_emb, speech_pos, float(g[f"emotion{c}"][0]))
+        want = torch.from_numpy(g[f"cond{c}"])
+        assert y.shape == (34, 1024)
+        assert float((y - want).abs().max()) <= 2e-6 * float(want.abs().max()), "oracle drifted from the reference modules"
+        row = cond_ref.emotion_row(sd, 0.3)
+        assert torch.allclose(row, torch.from_numpy(g[f"row03_{c}"]), rtol=0, atol=1e-7)

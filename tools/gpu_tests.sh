@@ -15,7 +15,7 @@ run silu    tests/test_gpu_kernels.py -k "silu"
 run rope    tests/test_gpu_kernels.py -k "rope and not fused"
 run attn    tests/test_gpu_kernels.py -k "paged_attention"
 run fused   tests/test_gpu_kernels.py -k "fused or residual or split_k"
-run post    tests/test_gpu_kernels.py -k "postprocess"
+run post    tests/test_gpu_kernels.py -k "postprocess or cond_encoder"
 run sampler tests/test_gpu_engine.py -k "sampler or prefill_embed"
 run engine  tests/test_gpu_engine.py -k "engine"
 run facade  tests/test_gpu_facade.py
