@@ -14,12 +14,13 @@
 //             x 16-byte chunk), mbarrier hand-back of the stage.
 // Partial (o, m, l) per (row, split) go to scratch; the CTA that publishes a row's LAST partial
 // (atomic ticket per row) merges them in the same launch — no second kernel.
+#include <cuda.h>
 #include <stdlib.h>
 
 #include "common.cuh"
 
 using namespace cbx;
-namespace cbx { int init_attn(); }
+namespace cbx { int init_attn(); int make_kv_rows_map(CUtensorMap* m, const void* kv_layer); }
 
 namespace {
 constexpr int kStages = 3;
@@ -383,26 +384,45 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
 // ---------------------------------------------------------------------------------------------
 // Prefill (causal) attention over the paged cache: one item = 16 consecutive query rows of one
 // sequence (a "query block" qb), which need KV pages 0..qb — each page is loaded ONCE for the 16
-// queries instead of once per row (16x less page traffic than running prefix rows through the
-// decode kernel).  Same persistent producer/consumer skeleton: warp = head; lane = (query, half of
-// d); K/V rows are shared-memory broadcasts.  fp32 online softmax per query.
+// queries instead of once per row.  Same persistent producer/consumer skeleton, warp = head, but the
+// math runs on the tensor cores (mma.sync m16n8k16, FlashAttention-2 register pipeline): per
+// (head, page) S[16x16] = Q·K^T is 8 MMAs, O[16x64] += P·V another 8, against ~1000 FMA-issue slots
+// for the same work on CUDA cores (the first version of this kernel was compute-bound at 406 us per
+// layer for 16 000 rows).  K fragments come from the page's pre-swizzled K rows with ldmatrix; the V
+// half of a page is fetched with a 2-D TMA copy whose hardware 128-byte swizzle gives V the same
+// chunk swizzle in shared memory, so ldmatrix.trans is conflict-free too.  Softmax statistics fp32;
+// P is rounded to bf16 for the PV product, as flash-attention (the kernel this replaces) does.
 // items int32 [n][4] = {row0 (first query row in qkv/out), n_q (1..16), block-table row, qb}.
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
 __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
-    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt, int bt_stride,
-    const int4* __restrict__ items, int n_items, bf16* __restrict__ out) {
+    const __grid_constant__ CUtensorMap vmap, const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer,
+    const int32_t* __restrict__ bt, int bt_stride, const int4* __restrict__ items, int n_items, bf16* __restrict__ out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
   uint64_t* empty = full + kStages;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_trigger();
   if (threadIdx.x == 0) {
+    tma_prefetch_desc(&vmap);
     for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
     fence_barrier_init();
   }
   __syncthreads();
   pdl_wait();
   uint32_t it = 0;
-  if (warp == kConsumerWarps) {                       // ---- producer
+  if (warp == kConsumerWarps) {                       // ---- producer: K half as stored, V half swizzled by the TMA engine
     for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
       const int4 im = items[w];
       const int32_t* btr = bt + (int64_t)im.z * bt_stride;
@@ -415,7 +435,8 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
             const uint32_t s = it % kStages, ph = (it / kStages) & 1;
             mbar_wait(&empty[s], ph ^ 1);
             mbar_arrive_expect_tx(&full[s], CBX_PAGE_BYTES);
-            bulk_g2s(smem + s * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, CBX_PAGE_BYTES, &full[s]);
+            bulk_g2s(smem + s * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, 32768, &full[s]);
+            tma_load_2d(smem + s * CBX_PAGE_BYTES + 32768, &vmap, 0, blk * 512 + 256, &full[s]);
           }
           ++it;
         }
@@ -423,87 +444,98 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
     }
     return;
   }
-  const int h = warp, qi = lane & 15, half = lane >> 4;
-  const float qscale = 0.125f * kLog2e;
+  const int h = warp, g = lane >> 2, c = lane & 3;    // MMA fragment coordinates: rows g / g+8, column pair c
+  const int mat = lane >> 3, r8 = lane & 7;           // ldmatrix: this lane addresses row r8 of 8x8 matrix `mat`
+  const float qscale = 0.125f * kLog2e;               // 1/sqrt(64); scores kept in the log2 domain
   for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
     const int4 im = items[w];
-    const int row = im.x + qi, qb = im.w;
-    const bool live = qi < im.y;
-    float q[32];
+    const int qb = im.w;
+    // Q as the A operand: 4 k-steps of 16 d; rows beyond n_q are zero
+    uint32_t qa[4][4];
+    {
+      const uint32_t* q0 = reinterpret_cast<const uint32_t*>(qkv + (size_t)(im.x + g) * 3072 + h * 64) + c;
+      const uint32_t* q1 = reinterpret_cast<const uint32_t*>(qkv + (size_t)(im.x + g + 8) * 3072 + h * 64) + c;
+      const bool l0 = g < im.y, l1 = g + 8 < im.y;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) q[i] = 0.f;
-    if (live) {
-      const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const uint4 v = qp[i];
-        q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
-        q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
-        q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
-        q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
+      for (int ks = 0; ks < 4; ++ks) {
+        qa[ks][0] = l0 ? q0[ks * 8] : 0u;
+        qa[ks][1] = l1 ? q1[ks * 8] : 0u;
+        qa[ks][2] = l0 ? q0[ks * 8 + 4] : 0u;
+        qa[ks][3] = l1 ? q1[ks * 8 + 4] : 0u;
       }
     }
-    float m = -INFINITY, l = 0.f, acc[32];
+    float m0 = -INFINITY, m1 = -INFINITY, l0s = 0.f, l1s = 0.f;
+    float o[8][4];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+    for (int i = 0; i < 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
     for (int pg = 0; pg <= qb; ++pg, ++it) {
       const uint32_t s = it % kStages, ph = (it / kStages) & 1;
       mbar_wait(&full[s], ph);
-      const uint8_t* kt = smem + s * CBX_PAGE_BYTES + h * 2048;
-      const uint8_t* vt = kt + 32768;
-      const int n_vis = pg < qb ? 16 : qi + 1;        // causal: query 16·qb+qi sees tokens <= itself
-      float sc[16];
+      const uint32_t kt = smem_u32(smem + s * CBX_PAGE_BYTES + h * 2048);
+      const uint32_t vt = kt + 32768;
+      // ---- S = Q·K^T: keys 0-7 (sc[0]) and 8-15 (sc[1])
+      float sc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
-      for (int t = 0; t < 16; ++t) {
-        const uint4* kr = reinterpret_cast<const uint4*>(kt + t * 128);
-        float a = 0.f;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint4 v = kr[(half * 4 + i) ^ (t & 7)];
-          a = fmaf(q[i * 8 + 0], bf_lo(v.x), a); a = fmaf(q[i * 8 + 1], bf_hi(v.x), a);
-          a = fmaf(q[i * 8 + 2], bf_lo(v.y), a); a = fmaf(q[i * 8 + 3], bf_hi(v.y), a);
-          a = fmaf(q[i * 8 + 4], bf_lo(v.z), a); a = fmaf(q[i * 8 + 5], bf_hi(v.z), a);
-          a = fmaf(q[i * 8 + 6], bf_lo(v.w), a); a = fmaf(q[i * 8 + 7], bf_hi(v.w), a);
-        }
-        sc[t] = a;
+      for (int ks = 0; ks < 4; ++ks) {
+        uint32_t kb[4];
+        const int key = (mat >> 1) * 8 + r8, chunk = ks * 2 + (mat & 1);
+        ldsm_x4(kt + key * 128 + ((chunk ^ (key & 7)) << 4), kb);
+        mma_bf16_16816(sc[0], qa[ks], kb[0], kb[1]);
+        mma_bf16_16816(sc[1], qa[ks], kb[2], kb[3]);
       }
-      float mt = -INFINITY;
+      // ---- online softmax of rows g and g+8 (this lane holds columns nt*8 + 2c, +1)
+      const bool diag = pg == qb;
+      float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-      for (int t = 0; t < 16; ++t) {
-        sc[t] += __shfl_xor_sync(0xffffffffu, sc[t], 16);
-        sc[t] = t < n_vis ? sc[t] : -INFINITY;
-        mt = fmaxf(mt, sc[t]);
-      }
-      const float m_new = fmaxf(m, mt);               // token 0 of page 0 is always visible: m_new is finite
-      const float corr = exp2f(m - m_new);
-      m = m_new;
-      l *= corr;
+      for (int nt = 0; nt < 2; ++nt) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) acc[i] *= corr;
-#pragma unroll
-      for (int t = 0; t < 16; ++t) {
-        const float p = exp2f(sc[t] - m_new);
-        l += p;
-        const uint4* vr = reinterpret_cast<const uint4*>(vt + t * 128) + half * 4;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint4 v = vr[i];
-          acc[i * 8 + 0] = fmaf(p, bf_lo(v.x), acc[i * 8 + 0]); acc[i * 8 + 1] = fmaf(p, bf_hi(v.x), acc[i * 8 + 1]);
-          acc[i * 8 + 2] = fmaf(p, bf_lo(v.y), acc[i * 8 + 2]); acc[i * 8 + 3] = fmaf(p, bf_hi(v.y), acc[i * 8 + 3]);
-          acc[i * 8 + 4] = fmaf(p, bf_lo(v.z), acc[i * 8 + 4]); acc[i * 8 + 5] = fmaf(p, bf_hi(v.z), acc[i * 8 + 5]);
-          acc[i * 8 + 6] = fmaf(p, bf_lo(v.w), acc[i * 8 + 6]); acc[i * 8 + 7] = fmaf(p, bf_hi(v.w), acc[i * 8 + 7]);
+        for (int e = 0; e < 2; ++e) {
+          const int col = nt * 8 + 2 * c + e;
+          sc[nt][e] = (!diag || col <= g) ? sc[nt][e] * qscale : -INFINITY;
+          sc[nt][2 + e] = (!diag || col <= g + 8) ? sc[nt][2 + e] * qscale : -INFINITY;
+          mx0 = fmaxf(mx0, sc[nt][e]);
+          mx1 = fmaxf(mx1, sc[nt][2 + e]);
         }
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);   // key 0 of page 0 is visible to every query: finite
+      const float cr0 = exp2f(m0 - mn0), cr1 = exp2f(m1 - mn1);
+      m0 = mn0; m1 = mn1;
+      uint32_t pa[4];
+      {
+        const float p00 = exp2f(sc[0][0] - mn0), p01 = exp2f(sc[0][1] - mn0), p02 = exp2f(sc[0][2] - mn1), p03 = exp2f(sc[0][3] - mn1);
+        const float p10 = exp2f(sc[1][0] - mn0), p11 = exp2f(sc[1][1] - mn0), p12 = exp2f(sc[1][2] - mn1), p13 = exp2f(sc[1][3] - mn1);
+        l0s = fmaf(l0s, cr0, (p00 + p01) + (p10 + p11));
+        l1s = fmaf(l1s, cr1, (p02 + p03) + (p12 + p13));
+        pa[0] = pack_bf16(p00, p01); pa[1] = pack_bf16(p02, p03); pa[2] = pack_bf16(p10, p11); pa[3] = pack_bf16(p12, p13);
+      }
+      // ---- O = O·corr + P·V
+#pragma unroll
+      for (int nd = 0; nd < 8; nd += 2) {
+        uint32_t vb[4];
+        const int key = (mat & 1) * 8 + r8, chunk = nd + (mat >> 1);
+        ldsm_x4_trans(vt + key * 128 + ((chunk ^ (key & 7)) << 4), vb);
+        o[nd][0] *= cr0; o[nd][1] *= cr0; o[nd][2] *= cr1; o[nd][3] *= cr1;
+        o[nd + 1][0] *= cr0; o[nd + 1][1] *= cr0; o[nd + 1][2] *= cr1; o[nd + 1][3] *= cr1;
+        mma_bf16_16816(o[nd], pa, vb[0], vb[1]);
+        mma_bf16_16816(o[nd + 1], pa, vb[2], vb[3]);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[s]);
     }
-    if (live) {
-      const float inv = 1.f / l;
-      uint4* dst = reinterpret_cast<uint4*>(out + (size_t)row * CBX_HIDDEN + h * 64 + half * 32);
+    l0s += __shfl_xor_sync(0xffffffffu, l0s, 1); l0s += __shfl_xor_sync(0xffffffffu, l0s, 2);
+    l1s += __shfl_xor_sync(0xffffffffu, l1s, 1); l1s += __shfl_xor_sync(0xffffffffu, l1s, 2);
+    const float i0 = 1.f / l0s, i1 = 1.f / l1s;
+    if (g < im.y) {
+      uint32_t* dst = reinterpret_cast<uint32_t*>(out + (size_t)(im.x + g) * CBX_HIDDEN + h * 64) + c;
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        dst[i] = make_uint4(pack_bf16(acc[i * 8 + 0] * inv, acc[i * 8 + 1] * inv), pack_bf16(acc[i * 8 + 2] * inv, acc[i * 8 + 3] * inv),
-                            pack_bf16(acc[i * 8 + 4] * inv, acc[i * 8 + 5] * inv), pack_bf16(acc[i * 8 + 6] * inv, acc[i * 8 + 7] * inv));
+      for (int nd = 0; nd < 8; ++nd) dst[nd * 4] = pack_bf16(o[nd][0] * i0, o[nd][1] * i0);
+    }
+    if (g + 8 < im.y) {
+      uint32_t* dst = reinterpret_cast<uint32_t*>(out + (size_t)(im.x + g + 8) * CBX_HIDDEN + h * 64) + c;
+#pragma unroll
+      for (int nd = 0; nd < 8; ++nd) dst[nd * 4] = pack_bf16(o[nd][2] * i1, o[nd][3] * i1);
     }
   }
 }
@@ -641,9 +673,11 @@ extern "C" int cbx_paged_attn_prefill(const void* qkv, const void* kv_layer, con
   if (n_items <= 0) return 0;
   if (cbx::init_attn()) return -1;
   const int grid = n_items < 148 ? n_items : 148;
+  CUtensorMap vmap;
+  if (cbx::make_kv_rows_map(&vmap, kv_layer)) return -1;
   cudaError_t e = launch_pdl(paged_attn_prefill_kernel, dim3(grid), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,
-                             (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, (const int4*)items, n_items,
-                             (bf16*)out);
+                             vmap, (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, (const int4*)items,
+                             n_items, (bf16*)out);
   CBX_REQUIRE(e == cudaSuccess, "paged_attn_prefill launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;

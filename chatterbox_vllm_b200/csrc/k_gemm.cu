@@ -38,6 +38,10 @@ struct Cfg {
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  // Throughput configuration for grids of many tiles (prefill): a ring shallow enough that TWO CTAs
+  // share an SM, so one CTA's epilogue (TMEM -> registers -> global) runs under the other's MMAs.
+  static constexpr int kStagesShallow = BN == 128 ? 3 : 4;
+  static constexpr int kSmemShallow = kStagesShallow * kStageBytes + 1024 + 256;
 };
 
 struct EpiArgs {               // EPI 2 only
@@ -49,16 +53,16 @@ struct EpiArgs {               // EPI 2 only
 // TMA-multicasts it into every CTA of the cluster (the decode GEMMs are bound by bytes entering the
 // SMs from L2, and activation re-reads are most of those bytes).
 template <int BN, int EPI, int CN>
-__global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
+__global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                               const __grid_constant__ CUtensorMap tma_b,
                                                               bf16* __restrict__ y, int M, int N, int K, int ldy,
-                                                              const EpiArgs ea) {
+                                                              const EpiArgs ea, const int n_stages) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
-  uint64_t* empty = full + C::kStages;
-  uint64_t* tmem_full = empty + C::kStages;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + n_stages * C::kStageBytes);
+  uint64_t* empty = full + n_stages;
+  uint64_t* tmem_full = empty + n_stages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -76,7 +80,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     tma_prefetch_desc(&tma_b);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CN); }
+    for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CN); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -108,7 +112,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         }
       };
       // weights of the first ring fill do not depend on the previous kernel
-      const int n_pre = n_kb < C::kStages ? n_kb : C::kStages;
+      const int n_pre = n_kb < n_stages ? n_kb : n_stages;
       for (int kb = 0; kb < n_pre; ++kb) {
         mbar_arrive_expect_tx(&full[kb], C::kStageBytes);
         tma_load_2d(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kc(kb) * BK, n0, &full[kb]);
@@ -117,7 +121,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       for (int kb = 0; kb < n_pre; ++kb)
         load_a(smem + kb * C::kStageBytes, kb, &full[kb]);
       for (int kb = n_pre; kb < n_kb; ++kb) {
-        const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
+        const int s = kb % n_stages, ph = (kb / n_stages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_arrive_expect_tx(&full[s], C::kStageBytes);
         uint8_t* sa = smem + s * C::kStageBytes;
@@ -132,7 +136,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
       for (int kb = 0; kb < n_kb; ++kb) {
-        const int s = kb % C::kStages, ph = (kb / C::kStages) & 1;
+        const int s = kb % n_stages, ph = (kb / n_stages) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + s * C::kStageBytes);
@@ -326,6 +330,12 @@ int set_attr() {
 }
 }  // namespace
 namespace cbx {
+// Tensor map over one layer's KV pages seen as bf16 rows of 64 elements (512 rows per 64 KiB page: K
+// rows then V rows), box = 256 rows, SWIZZLE_128B: the prefill attention kernel fetches a page's V
+// half through it so that V lands in shared memory chunk-swizzled like K (conflict-free ldmatrix.trans).
+int make_kv_rows_map(CUtensorMap* m, const void* kv_layer) {
+  return make_map(m, kv_layer, 1 << 30, 64, 256);
+}
 int init_gemm() {
   static bool done = false;
   if (done) return 0;
@@ -353,13 +363,17 @@ int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, 
   if (make_map(&ma, x, M, K, mc ? BM / 2 : BM)) return -1;
   if (make_map(&mb, W, N, K, BN)) return -1;
   cudaError_t e;
+  static const int shallow_env = getenv("CBX_GEMM_SHALLOW") ? atoi(getenv("CBX_GEMM_SHALLOW")) : 1;
+  const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * 148;
+  const int n_stages = shallow ? C::kStagesShallow : C::kStages;
+  const int smem_bytes = shallow ? C::kSmemShallow : C::kSmem;
   if (mc) {
     n_tiles = (n_tiles + 1) & ~1;                      // pad to whole clusters: out-of-range tiles load zeros, store nothing
-    e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), C::kSmem, s, 2, ma, mb,
-                           (bf16*)y, M, N, K, ldy, ea);
+    e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), smem_bytes, s, 2, ma, mb,
+                           (bf16*)y, M, N, K, ldy, ea, n_stages);
   } else {
-    e = launch_pdl(gemm_tc_kernel<BN, EPI, 1>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), C::kSmem, s, ma, mb, (bf16*)y, M,
-                   N, K, ldy, ea);
+    e = launch_pdl(gemm_tc_kernel<BN, EPI, 1>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), smem_bytes, s, ma, mb, (bf16*)y, M,
+                   N, K, ldy, ea, n_stages);
   }
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc launch failed: %s", cudaGetErrorString(e));
   count_launch();

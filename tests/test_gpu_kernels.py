@@ -340,8 +340,11 @@ def test_split_k_partials_and_reduce_norm(ops, T, K, splits):
 
 @pytest.mark.parametrize("lens", [[1], [16], [17, 5], [200, 77, 33], [450]])
 def test_paged_attention_prefill_causal(ops, lens):
-    """Causal prefill attention (16 query rows share each page load) against the fp32 reference,
-    for every row of every sequence, and against the per-row decode kernel."""
+    """Causal prefill attention (16 query rows share each page load, tensor-core QK^T / PV) against the
+    fp32 reference, for every row of every sequence, and against the per-row decode kernel.
+    Tolerance: like FlashAttention-2 (the kernel vLLM runs here) the probabilities are rounded to bf16
+    for the PV product, so |err| <= 2^-9 · sum_j p_j |v_j| / l <= 2^-9 · max|v| in ABSOLUTE terms (it does
+    not shrink when the v_j cancel): atol = 2^-9 · 4 for the N(0,1) values used here, plus 2 bf16 ulps."""
     cfg = T3ModelConfig()
     kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, lens, seed=10 + len(lens))
     starts = np.concatenate(([0], np.cumsum(lens)[:-1])).tolist()
@@ -353,11 +356,11 @@ def test_paged_attention_prefill_causal(ops, lens):
     rows = [(s, p) for s, n in enumerate(lens) for p in range(n)]
     dec = ops.paged_attn_decode(dev(q), kv, bt_d, dev(torch.tensor([s for s, _ in rows], dtype=torch.int32)),
                                 dev(torch.tensor([p + 1 for _, p in rows], dtype=torch.int32)), max(lens))
-    assert_close_bf16(out, dec, ulps=1.01, atol=2e-3, what="prefill vs per-row decode kernel")
+    assert_close_bf16(out, dec, ulps=2.0, atol=8e-3, what="prefill vs per-row decode kernel")
     for i in list(range(0, T, max(1, T // 40))) + [T - 1]:
         s, p = rows[i]
         want = _ref_attn(cfg, qkv_all[s], q[i, :1024].float(), p + 1, cs)
-        assert_close_bf16(out[i], want, ulps=1.0, atol=2e-3, what=f"prefill row {i} (seq {s}, pos {p})")
+        assert_close_bf16(out[i], want, ulps=2.0, atol=8e-3, what=f"prefill row {i} (seq {s}, pos {p})")
 
 
 # ------------------------------------------------------------------ token post-processing
