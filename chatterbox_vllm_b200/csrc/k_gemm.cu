@@ -156,13 +156,15 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
     tc_fence_after();
     const int row = m0 + ew * 32 + lane;
     if (EPI == 2) {
-      // ---- RoPE + q store + KV append: this 64-wide tile is head (n0/64) % 16 of q (0), k (1) or v (2)
+      // ---- RoPE + q store + KV append: each 64-wide half of the tile is head (col/64) % 16 of q (0), k (1) or v (2)
+#pragma unroll 1
+      for (int hh = 0; hh < BN / 64; ++hh) {
       uint32_t r0[32], r1[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16), r0);
-      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + 32, r1);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + hh * 64, r0);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + hh * 64 + 32, r1);
       tmem_ld_wait();
       if (row < M) {
-        const int head48 = n0 >> 6, which = head48 >> 4, h = head48 & 15;
+        const int head48 = (n0 >> 6) + hh, which = head48 >> 4, h = head48 & 15;
         uint32_t o1[16], o2[16];
         if (which < 2) {
           const int p = ea.pos[row];
@@ -209,6 +211,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
             }
           }
         }
+      }
       }
     } else {
 #pragma unroll 1
@@ -340,7 +343,7 @@ int init_gemm() {
   static bool done = false;
   if (done) return 0;
   if (set_attr<64, 0>() || set_attr<64, 1>() || set_attr<128, 0>() || set_attr<128, 1>() || set_attr<64, 2>() ||
-      set_attr<64, 3>() || set_attr<128, 3>() || set_attr<64, 4>()) return -1;
+      set_attr<64, 3>() || set_attr<128, 3>() || set_attr<64, 4>() || set_attr<128, 2>()) return -1;
   CBX_REQUIRE(get_encode() != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   done = true;
   return 0;
@@ -401,6 +404,8 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
 int gemm_qkv_rope(const void* h, const void* Wqkv, void* qkv, const void* cos_sin, const int32_t* pos,
                   const int64_t* slot, void* kv_layer, int M, cudaStream_t s) {
   EpiArgs ea = {(const bf16*)cos_sin, pos, slot, (uint8_t*)kv_layer};
+  // prefill-sized M: 128-wide tiles (two heads per tile) halve the activation re-reads
+  if ((M + BM - 1) / BM * 24 >= 2 * 148) return launch<128, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   return launch<64, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
 }
 // EPI 3: res[M, N] = bf16(bf16(x·W^T) + res), N % 32 == 0.

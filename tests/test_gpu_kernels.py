@@ -84,7 +84,7 @@ def test_linear_gemv(ops, T, N, K):
     assert_close_bf16(y, _ref_linear(x, W), ulps=1.0, atol=2e-3, what=f"gemv T={T} N={N} K={K}")
 
 
-@pytest.mark.parametrize("T", [1, 5, 64, 128, 200, 256, 300])
+@pytest.mark.parametrize("T", [1, 5, 64, 128, 200, 256, 300, 2500])     # 2500 rows: the two-CTAs-per-SM configuration
 @pytest.mark.parametrize("N,K", [(3072, 1024), (1024, 1024), (1024, 4096), (8194, 1024)])
 def test_linear_gemm_tcgen05(ops, T, N, K):
     g = torch.Generator().manual_seed(N + 7 * T)
@@ -234,7 +234,7 @@ def _unswizzled_k(page_bf16, h, tok):
     return torch.stack([krow[c ^ (tok & 7)] for c in range(8)]).reshape(64)
 
 
-@pytest.mark.parametrize("T", [1, 2, 4, 6, 200])
+@pytest.mark.parametrize("T", [1, 2, 4, 6, 200, 1600])               # 1600 rows: 128-wide tiles, two heads per RoPE epilogue
 def test_layer_qkv_fused_norm_rope_append(ops, T):
     """[RMSNorm → QKV → RoPE → KV append] in one op (GEMV kernel for T <= 4, rmsnorm + tcgen05 GEMM
     with the RoPE/append epilogue above) against the oracle's op-by-op bf16 chain."""
@@ -277,7 +277,7 @@ def test_layer_qkv_fused_norm_rope_append(ops, T):
             assert not pages[b].any(), f"page {b} must stay untouched"
 
 
-@pytest.mark.parametrize("T", [1, 3, 4, 5, 256])
+@pytest.mark.parametrize("T", [1, 3, 4, 5, 256, 4800])
 @pytest.mark.parametrize("K", [1024, 4096])
 def test_linear_residual_in_place(ops, T, K):
     g = torch.Generator().manual_seed(T * 7 + K)
@@ -292,7 +292,7 @@ def test_linear_residual_in_place(ops, T, K):
     assert (err <= tol).all(), f"max err {err.max():.3e}"
 
 
-@pytest.mark.parametrize("T", [1, 2, 4, 7, 256])
+@pytest.mark.parametrize("T", [1, 2, 4, 7, 256, 700])
 def test_layer_gate_up_fused_norm_silu(ops, T):
     g = torch.Generator().manual_seed(T + 31)
     res = (torch.randn(T, 1024, generator=g) * 1.2).to(BF16)
