@@ -20,7 +20,7 @@ for f in sorted(os.listdir(go)):
         idx = [i for i, h in enumerate(hdr) if h in KEEP]
         name = f[5:-8]
         with open(os.path.join(pr, f"{tag}_ncu_full_{name}.txt"), "w") as o:
-            o.write(f"# ncu --set full --clock-control none, kernel regex '{name}', launches of the bench decode step\n")
+            o.write(f"# ncu --set full --clock-control none, capture '{name}' (see tools/gpu_profile.sh), launches of bench.py\n")
             for r in rows[2:]:
                 for i in idx:
                     o.write(f"{hdr[i]:70s} {r[i][:90]} {units[i]}\n")
