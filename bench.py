@@ -204,14 +204,14 @@ def main():
         qkv = eng.buffer("qkv", (2 * B, 3072), torch.bfloat16)
         layer_bytes = eng.num_blocks * ops.PAGE_BYTES
         reps = 3
-        for _ in range(2):
-            ops.paged_attn_decode(qkv, eng.kv_cache[:layer_bytes], eng.block_table, rows, kvl, mean_ctx)
+        for _ in range(2):                                      # the page-range plan is built once per step, as in the engine
+            ops.paged_attn_decode(qkv, eng.kv_cache[:layer_bytes], eng.block_table, rows, kvl, mean_ctx, plan="make")
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a0.record(eng.stream)
         for _ in range(reps):
             for li in range(eng.n_layers):                      # a different layer's pages each launch: cold in L2
                 ops.paged_attn_decode(qkv, eng.kv_cache[li * layer_bytes:(li + 1) * layer_bytes], eng.block_table,
-                                      rows, kvl, mean_ctx)
+                                      rows, kvl, mean_ctx, plan="reuse")
         a1.record(eng.stream)
         torch.cuda.synchronize()
         attn_ms = a0.elapsed_time(a1) / (reps * eng.n_layers)
@@ -301,7 +301,7 @@ def main():
                        "l2": "inputs larger than L2 (KV ~%.1f GB/step)" % (2 * B * mean_ctx * KV_TOKEN_BYTES / 1e9),
                        "sampler": "T=0.5 top_p=0.5 rep=2.0 (tts.py defaults after clamp)", "cuda_graph": True},
             "clocks": clk, "gpu_launches": int(launches), "e2e": e2e,
-            "roofline": {"kernel": "paged_attn_decode_kernel", "bound": "hbm",
+            "roofline": {"kernel": "paged_attn_decode_bal_kernel", "bound": "hbm",
                          "achieved": attn_bytes / (attn_ms / 1e3) / 1e9, "peak": hbm, "unit": "GB/s",
                          "frac": attn_bytes / (attn_ms / 1e3) / 1e9 / hbm, "traffic": traffic, "peak_source": which,
                          "us_per_launch": attn_ms * 1e3, "algorithmic_bytes_per_launch": attn_bytes},

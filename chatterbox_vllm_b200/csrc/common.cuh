@@ -41,6 +41,16 @@ typedef __nv_bfloat16 bf16;
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 bool pdl_enabled();                        // env CBX_PDL != "0"
+// nvcc treats loads through `const T* __restrict__` as invariant and may hoist them ABOVE
+// griddepcontrol.wait despite its memory clobber (seen in SASS: LDG.E.CONSTANT before ACQBULK), i.e.
+// read what the previous kernel has not written yet.  A pointer whose first load does not depend on
+// another post-wait load must be laundered after the wait: p = pdl_acquire(p).
+// tools/audit_pdl_hoist.py lists every load that ended up before the wait.
+template <typename T>
+__device__ __forceinline__ const T* pdl_acquire(const T* p) {
+  asm volatile("" : "+l"(p)::"memory");
+  return p;
+}
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,

@@ -26,6 +26,9 @@ int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t, const
 int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, cudaStream_t, const void* next_w = nullptr,
                       size_t next_bytes = 0);
 void attn_set_prefetch(const void*, size_t);
+int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
+int paged_attn_decode_ex(const void*, const void*, const int32_t*, int, const int32_t*, const int32_t*, void*, void*, int32_t*,
+                         int, int, bool, void*);
 int gemv_norm_head(const void*, const void*, const void*, void*, int, int, int, float, cudaStream_t);
 int gemm_bf16_tc(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
 int gemm_qkv_rope(const void*, const void*, void*, const void*, const int32_t*, const int64_t*, void*, int, cudaStream_t);
@@ -212,6 +215,9 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
   int splits = 1;
   if (T > 4 && !e->trace && T <= e->split_max_rows) splits = m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1);
   bool pending = false;                                // down-proj partials not yet folded into res
+  // decode attention cuts the step's pages into equal per-CTA ranges: one plan serves all layers
+  static const bool plan_each = getenv("CBX_ATTN_PLAN_EACH") != nullptr;   // debugging aid: rebuild the plan per layer
+  const bool have_plan = !plan_each && e->n_prefill_items == 0 && !(sk & 2) && attn_plan(e->kv_len, T, e->attn_scratch, s) == 0;
   const bool pf = e->l2_prefetch;
   for (int li = 0; li < e->w.n_layers; ++li) {
     uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;
@@ -229,8 +235,8 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
     if (e->n_prefill_items > 0) {
       if (!(sk & 2) && cbx_paged_attn_prefill(e->qkv, kv, e->block_table, e->bt_stride, e->prefill_items, e->n_prefill_items,
                                               e->attn, s)) return -1;
-    } else if (!(sk & 2) && cbx_paged_attn_decode(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
-                                                  e->attn_scratch, e->attn_counters, T, max_kv_len, s)) return -1;
+    } else if (!(sk & 2) && paged_attn_decode_ex(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
+                                                 e->attn_scratch, e->attn_counters, T, max_kv_len, have_plan, s)) return -1;
     if (T <= 4) {
       const bool last = li + 1 == e->w.n_layers;
       if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s, pf ? e->wd[li] : nullptr, (size_t)1024 * 4096 * 2)) return -1;

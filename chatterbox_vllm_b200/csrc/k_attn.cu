@@ -29,6 +29,11 @@ constexpr int kThreads = (kConsumerWarps + 1) * 32;
 constexpr int kSmemBytes = kStages * CBX_PAGE_BYTES + 64;
 constexpr float kLog2e = 1.4426950408889634f;
 
+// balanced variant: 2 partial slots per CTA (o fp32 [1024], (m, l) per head), then the range plan
+constexpr int kPlanMaxRows = 4095;              // 1024 threads x 4 rows, and entry [T] for the total
+constexpr int kPlanInts = 2 + 2 * 148;
+constexpr int64_t kBalScratchBytes = 2 * 148 * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + kPlanInts * 4 + 256;
+
 struct AttnPlan { int pps; int nsplit; };
 inline AttnPlan make_plan(int T, int max_kv_len) {
   int max_pages = (max_kv_len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
@@ -227,6 +232,267 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
         *reinterpret_cast<uint32_t*>(out + (size_t)row * CBX_HIDDEN + d2) = pack_bf16(ox * inv, oy * inv);
       }
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Balanced variant (4 < T <= kPlanMaxRows): the launch's pages, flattened in (row, page) order, are
+// cut into gridDim.x equal ranges, so every CTA streams the same number of bytes whatever the
+// spread of context lengths (the fixed pages-per-split plan above loses 7-14 % on ragged batches).
+// A row that lies inside one range is normalised and written directly; a row cut by a range
+// boundary leaves (o, m, l) partials — at most two per CTA: slot 0 for a row begun by an earlier
+// CTA, slot 1 for a row continued by the next — and the CTA holding the row's last ticket merges
+// them.  In (row, page) order the CTA that holds a row's head reaches it last, so merges fall at the
+// end of a CTA's range rather than in the middle of its page stream.
+// plan (int32): [0] total pages, [1] pages per CTA, [2 + 2c], [3 + 2c] = (row, page) where CTA c starts.
+__global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* __restrict__ kv_len, int T, int G,
+                                                         int32_t* __restrict__ plan) {
+  __shared__ int s_first[kPlanMaxRows + 1];            // s_first[r] = flattened index of row r's first page
+  __shared__ int s_warp[32];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  pdl_trigger();
+  pdl_wait();                                          // kv_len is staged by the previous step's sampler
+  kv_len = pdl_acquire(kv_len);
+  int np[4], sum = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = t * 4 + i;
+    np[i] = r < T ? (kv_len[r] + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE : 0;
+    sum += np[i];
+  }
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += v;
+    }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  int run = incl - sum + (warp > 0 ? s_warp[warp - 1] : 0);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = t * 4 + i;
+    if (r <= T) s_first[r] = run;
+    run += np[i];
+  }
+  __syncthreads();
+  const int total = s_first[T];
+  const int q = max(1, (total + G - 1) / G);
+  if (t == 0) { plan[0] = total; plan[1] = q; }
+  if (t < G) {
+    const int g0 = t * q;
+    int row = T, page = 0;
+    if (g0 < total) {
+      int lo = 0, hi = T;                              // last r with s_first[r] <= g0 (it owns pages: s_first[r + 1] > g0)
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_first[mid] <= g0) lo = mid; else hi = mid;
+      }
+      row = lo; page = g0 - s_first[lo];
+    }
+    plan[2 + 2 * t] = row; plan[3 + 2 * t] = page;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_bal_kernel(
+    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt,
+    int bt_stride, const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len,
+    bf16* __restrict__ out, float* __restrict__ o_part, float2* __restrict__ ml_part,
+    int32_t* __restrict__ counters, const int32_t* __restrict__ plan, int T) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
+  uint64_t* empty = full + kStages;
+  volatile int& s_last = *reinterpret_cast<volatile int*>(empty + kStages);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kConsumerWarps); }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  pdl_wait();
+  plan = pdl_acquire(plan);
+  kv_len = pdl_acquire(kv_len);
+
+  const int total = plan[0], per = plan[1];
+  const int g0 = min((int)blockIdx.x * per, total);
+  int rem = min(per, total - g0);                      // pages this CTA still has to stream
+  int row = plan[2 + 2 * blockIdx.x], pg = plan[3 + 2 * blockIdx.x];
+  uint32_t it = 0;
+
+  if (warp == kConsumerWarps) {
+    // ------------------------------------------------------------ producer warp
+    while (rem > 0) {
+      const int n_pages = (kv_len[row] + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+      if (n_pages == 0) { ++row; continue; }
+      const int p1 = min(n_pages, pg + rem);
+      const int32_t* btr = bt + (int64_t)row_seq[row] * bt_stride;
+      for (int pb = pg; pb < p1; pb += 32) {
+        const int nb = min(32, p1 - pb);
+        const int my_blk = lane < nb ? btr[pb + lane] : 0;
+        for (int j = 0; j < nb; ++j) {
+          const int blk = __shfl_sync(0xffffffffu, my_blk, j);
+          if (lane == 0) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            mbar_wait(&empty[s], ph ^ 1);
+            mbar_arrive_expect_tx(&full[s], CBX_PAGE_BYTES);
+            bulk_g2s(smem + s * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, CBX_PAGE_BYTES, &full[s]);
+          }
+          ++it;
+        }
+      }
+      rem -= p1 - pg;
+      ++row; pg = 0;
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------- consumer warps
+  const int h = warp;
+  const int t16 = lane & 15, half = lane >> 4;
+  const int tg = lane >> 3, c = lane & 7;
+  const float qscale = 0.125f * kLog2e;
+
+  // rows without KV (finished pairs) belong to no range: zero them grid-wide
+  for (int r = blockIdx.x * kConsumerWarps + warp; r < T; r += gridDim.x * kConsumerWarps)
+    if (kv_len[r] <= 0 && lane < 8)
+      for (int hh = 0; hh < CBX_HEADS; ++hh)
+        reinterpret_cast<uint4*>(out + (size_t)r * CBX_HIDDEN + hh * 64)[lane] = make_uint4(0, 0, 0, 0);
+
+  int g = g0;                                          // flattened index of (row, pg)
+  while (rem > 0) {
+    const int len = kv_len[row];
+    const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
+    if (n_pages == 0) { ++row; continue; }
+    const int p0 = pg, p1 = min(n_pages, pg + rem);
+    float q[32];
+    {
+      const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint4 v = qp[i];
+        q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
+        q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
+        q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
+        q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
+      }
+    }
+    float m = -INFINITY, l = 0.f, acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+
+    for (int pgi = p0; pgi < p1; ++pgi, ++it) {
+      const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+      mbar_wait(&full[s], ph);
+      const uint8_t* kt = smem + s * CBX_PAGE_BYTES + h * 2048;
+      const uint8_t* vt = kt + 32768;
+      float sc = 0.f;
+      {
+        const uint4* kr = reinterpret_cast<const uint4*>(kt + t16 * 128);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 v = kr[(half * 4 + i) ^ (t16 & 7)];
+          sc = fmaf(q[i * 8 + 0], bf_lo(v.x), sc); sc = fmaf(q[i * 8 + 1], bf_hi(v.x), sc);
+          sc = fmaf(q[i * 8 + 2], bf_lo(v.y), sc); sc = fmaf(q[i * 8 + 3], bf_hi(v.y), sc);
+          sc = fmaf(q[i * 8 + 4], bf_lo(v.z), sc); sc = fmaf(q[i * 8 + 5], bf_hi(v.z), sc);
+          sc = fmaf(q[i * 8 + 6], bf_lo(v.w), sc); sc = fmaf(q[i * 8 + 7], bf_hi(v.w), sc);
+        }
+      }
+      sc += __shfl_xor_sync(0xffffffffu, sc, 16);
+      const int n_valid = len - pgi * CBX_BLOCK_SIZE;
+      sc = (t16 < n_valid) ? sc : -INFINITY;
+      float mt = sc;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, o));
+      const float m_new = fmaxf(m, mt);
+      const float p = exp2f(sc - m_new);
+      const float corr = exp2f(m - m_new);
+      m = m_new;
+      l = fmaf(l, corr, p);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] *= corr;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int tok = tg * 4 + i;
+        const float pt = __shfl_sync(0xffffffffu, p, tok);
+        if (tok < n_valid) {
+          const uint4 v = reinterpret_cast<const uint4*>(vt + tok * 128)[c];
+          acc[0] = fmaf(pt, bf_lo(v.x), acc[0]); acc[1] = fmaf(pt, bf_hi(v.x), acc[1]);
+          acc[2] = fmaf(pt, bf_lo(v.y), acc[2]); acc[3] = fmaf(pt, bf_hi(v.y), acc[3]);
+          acc[4] = fmaf(pt, bf_lo(v.z), acc[4]); acc[5] = fmaf(pt, bf_hi(v.z), acc[5]);
+          acc[6] = fmaf(pt, bf_lo(v.w), acc[6]); acc[7] = fmaf(pt, bf_hi(v.w), acc[7]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+      acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+    }
+    const float lsum = warp_sum(l) * 0.5f;
+    if (p0 == 0 && p1 == n_pages) {
+      if (lane < 8) {
+        const float inv = 1.f / lsum;
+        reinterpret_cast<uint4*>(out + (size_t)row * CBX_HIDDEN + h * 64)[lane] =
+            make_uint4(pack_bf16(acc[0] * inv, acc[1] * inv), pack_bf16(acc[2] * inv, acc[3] * inv),
+                       pack_bf16(acc[4] * inv, acc[5] * inv), pack_bf16(acc[6] * inv, acc[7] * inv));
+      }
+    } else {
+      // the row's pages span CTAs c_first .. c_last; the head CTA publishes in slot 1, the others in slot 0
+      const int first_page = g - p0;
+      const int c_first = first_page / per, c_last = (first_page + n_pages - 1) / per;
+      const size_t pi = (size_t)blockIdx.x * 2 + ((int)blockIdx.x == c_first ? 1 : 0);
+      if (lane < 8) {
+        float4* dst = reinterpret_cast<float4*>(o_part + pi * CBX_HIDDEN + h * 64 + lane * 8);
+        dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+      }
+      if (lane == 0) ml_part[pi * CBX_HEADS + h] = make_float2(m, lsum);
+      __threadfence();
+      asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+      if (threadIdx.x == 0) {
+        const int ns = c_last - c_first + 1;
+        const int ticket = atomicAdd(&counters[row], 1);
+        s_last = (ticket == ns - 1);
+        if (ticket == ns - 1) counters[row] = 0;      // self-reset for the next launch
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+      if (s_last) {
+        __threadfence();
+        const int d2 = threadIdx.x * 2, hh = d2 >> 6;  // 512 threads x 2 consecutive d
+        float mx = -INFINITY;
+        for (int cc = c_first; cc <= c_last; ++cc)
+          mx = fmaxf(mx, __ldcg(&ml_part[((size_t)cc * 2 + (cc == c_first ? 1 : 0)) * CBX_HEADS + hh]).x);
+        float ox = 0.f, oy = 0.f, lt = 0.f;
+        for (int cc = c_first; cc <= c_last; ++cc) {
+          const size_t pj = (size_t)cc * 2 + (cc == c_first ? 1 : 0);
+          const float2 ml = __ldcg(&ml_part[pj * CBX_HEADS + hh]);
+          const float wgt = exp2f(ml.x - mx);
+          const float2 a = __ldcg(reinterpret_cast<const float2*>(o_part + pj * CBX_HIDDEN + d2));
+          ox = fmaf(wgt, a.x, ox); oy = fmaf(wgt, a.y, oy);
+          lt = fmaf(wgt, ml.y, lt);
+        }
+        const float inv = 1.f / lt;
+        *reinterpret_cast<uint32_t*>(out + (size_t)row * CBX_HIDDEN + d2) = pack_bf16(ox * inv, oy * inv);
+      }
+      // the next partial of this CTA goes to the other slot, so nothing here can be overwritten early
+    }
+    g += p1 - p0;
+    rem -= p1 - p0;
+    ++row; pg = 0;
   }
 }
 
@@ -578,6 +844,8 @@ int init_attn() {
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(paged_attn_decode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(paged_attn_decode_bal_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(paged_attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   CBX_REQUIRE(e == cudaSuccess, "attn smem attribute: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(paged_attn_small_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmem);
@@ -594,7 +862,8 @@ int init_attn() {
 extern "C" int64_t cbx_attn_scratch_bytes(int T, int max_kv_len) {
   if (T <= 0) return 0;
   const AttnPlan p = make_plan(T, max_kv_len);
-  return (int64_t)T * p.nsplit * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256;
+  const int64_t fixed = (int64_t)T * p.nsplit * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256;
+  return fixed > kBalScratchBytes ? fixed : kBalScratchBytes;
 }
 extern "C" int cbx_attn_num_splits(int T, int max_kv_len) { return T <= 0 ? 0 : make_plan(T, max_kv_len).nsplit; }
 
@@ -605,18 +874,47 @@ static size_t g_next_bytes = 0;
 void attn_set_prefetch(const void* w, size_t bytes) { g_next_w = w; g_next_bytes = bytes; }
 int paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                          const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch, int32_t* counters,
-                         int T, int max_kv_len, int max_ctas, void* stream);
+                         int T, int max_kv_len, bool have_plan, void* stream);
+int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
+static bool balanced_on() {
+  static const bool on = !(getenv("CBX_ATTN_BALANCED") && getenv("CBX_ATTN_BALANCED")[0] == '0');
+  return on;
+}
+static int32_t* plan_of(void* scratch) {
+  return reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(scratch) + 2 * 148 * (CBX_HIDDEN * 4 + CBX_HEADS * 8));
+}
+}
+// Page-range plan shared by every layer of a decode step (kv_len is the same for all 30 launches).
+// Returns 1 when the balanced variant does not apply to T rows.
+int cbx::attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream) {
+  if (T <= 4 || T > kPlanMaxRows || !balanced_on() || scratch == nullptr) return 1;
+  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, 148, plan_of(scratch));
+  CBX_REQUIRE(e == cudaSuccess, "attn_plan launch failed: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
 }
 extern "C" int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* block_table,
                                      int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
                                      void* scratch, int32_t* counters, int T, int max_kv_len, void* stream) {
   return cbx::paged_attn_decode_ex(qkv, kv_layer, block_table, bt_stride, row_seq, kv_len, out, scratch, counters, T,
-                                   max_kv_len, 148, stream);
+                                   max_kv_len, false, stream);
 }
-// max_ctas < 148 leaves SMs free for another stream's GEMMs (two-microbatch overlap).
+extern "C" int cbx_attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream) {
+  if (T <= 0 || cbx::init_attn()) return -1;
+  return cbx::attn_plan(kv_len, T, scratch, stream);
+}
+extern "C" int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_layer, const int32_t* block_table,
+                                             int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
+                                             void* scratch, int32_t* counters, int T, int max_kv_len, void* stream) {
+  CBX_REQUIRE(T > 4 && T <= kPlanMaxRows && cbx::balanced_on(), "cbx_paged_attn_decode_planned: no plan exists for T=%d", T);
+  return cbx::paged_attn_decode_ex(qkv, kv_layer, block_table, bt_stride, row_seq, kv_len, out, scratch, counters, T,
+                                   max_kv_len, true, stream);
+}
+// have_plan: cbx::attn_plan already ran on this stream for the same kv_len (the engine builds it once per step).
 int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                               const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch,
-                              int32_t* counters, int T, int max_kv_len, int max_ctas, void* stream) {
+                              int32_t* counters, int T, int max_kv_len, bool have_plan, void* stream) {
+  const int max_ctas = 148;
   if (T <= 0) return 0;
   if (cbx::init_attn()) return -1;
   {
@@ -638,6 +936,18 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
       count_launch();
       return 0;
     }
+  }
+  if (T > 4 && T <= kPlanMaxRows && balanced_on()) {
+    CBX_REQUIRE(scratch != nullptr && counters != nullptr, "cbx_paged_attn_decode: scratch / counters is NULL");
+    if (!have_plan && attn_plan(kv_len, T, scratch, stream)) return -1;
+    float* o_part = reinterpret_cast<float*>(scratch);
+    float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)2 * 148 * CBX_HIDDEN);
+    cudaError_t e = launch_pdl(paged_attn_decode_bal_kernel, dim3(max_ctas), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,
+                               (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out,
+                               o_part, ml_part, counters, (const int32_t*)plan_of(scratch), T);
+    CBX_REQUIRE(e == cudaSuccess, "paged_attn_decode (balanced) launch failed: %s", cudaGetErrorString(e));
+    count_launch();
+    return 0;
   }
   const AttnPlan p = make_plan(T, max_kv_len);
   float* o_part = reinterpret_cast<float*>(scratch);

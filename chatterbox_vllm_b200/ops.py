@@ -80,9 +80,12 @@ def rope_kv_append(qkv, pos, slot, cos_sin, kv_layer):
 
 
 _attn_ws: dict = {}
+_attn_planned: dict = {}     # (device, stream) -> T of the plan kept in that workspace
 
 
-def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: int, out=None):
+def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: int, out=None, plan: str = "build"):
+    """plan: "build" (the call plans its page ranges itself), "make" (build the plan and keep it),
+    "reuse" (a previous "make" call on this stream saw the same kv_len: skip the plan launch)."""
     T = qkv.shape[0]
     if out is None:
         out = torch.empty(T, HIDDEN, dtype=BF16, device=qkv.device)
@@ -93,9 +96,17 @@ def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: i
         ws = (torch.empty(max(nbytes, 16), dtype=torch.uint8, device=qkv.device),
               torch.zeros(max(T, 1024), dtype=torch.int32, device=qkv.device))
         _attn_ws[key] = ws
-    check(load().cbx_paged_attn_decode(_p(qkv, BF16), _p(kv_layer), _p(block_table, torch.int32),
-                                       block_table.stride(0), _p(row_seq, torch.int32), _p(kv_len, torch.int32),
-                                       _p(out), _p(ws[0]), _p(ws[1], torch.int32), T, max_kv_len, _stream()),
+        _attn_planned.pop(key, None)
+    fn = load().cbx_paged_attn_decode
+    if plan == "make":
+        rc = load().cbx_attn_plan(_p(kv_len, torch.int32), T, _p(ws[0]), _stream())
+        if rc < 0:
+            check(rc, "attn_plan")
+        _attn_planned[key] = T if rc == 0 else 0
+    if plan != "build" and _attn_planned.get(key) == T:
+        fn = load().cbx_paged_attn_decode_planned
+    check(fn(_p(qkv, BF16), _p(kv_layer), _p(block_table, torch.int32), block_table.stride(0), _p(row_seq, torch.int32),
+             _p(kv_len, torch.int32), _p(out), _p(ws[0]), _p(ws[1], torch.int32), T, max_kv_len, _stream()),
           "paged_attn_decode")
     return out
 

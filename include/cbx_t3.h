@@ -101,6 +101,17 @@ int cbx_attn_num_splits(int T, int max_kv_len);
 int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* block_table,
                           int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
                           void* out, void* scratch, int32_t* counters, int T, int max_kv_len, void* stream);
+/* For 4 < T <= 4095 rows the decode kernel cuts the launch's pages, flattened in (row, page) order,
+ * into 148 equal ranges (one per SM) so that ragged context lengths stay balanced.  The range plan
+ * depends only on kv_len, so a caller that runs many layers over the same rows builds it once with
+ * cbx_attn_plan (returns 1 when the balanced variant does not apply to T: then use
+ * cbx_paged_attn_decode) and launches each layer with cbx_paged_attn_decode_planned.
+ * cbx_paged_attn_decode builds the plan itself on every call. */
+int cbx_attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
+int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_layer, const int32_t* block_table,
+                                  int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
+                                  void* out, void* scratch, int32_t* counters, int T, int max_kv_len,
+                                  void* stream);
 
 /* Prefill form of the same attention (causal, many query rows per sequence): an item is 16
  * consecutive query rows of one sequence (query block qb = first position / 16), which attend to

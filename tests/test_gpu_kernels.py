@@ -2,6 +2,8 @@
 the CPU oracle.  Integer work is bit-exact; floating point has its tolerance written at the
 assert.  bf16 has an 8-bit significand: 1 ulp = 2^-8 relative."""
 import numpy as np
+import random
+
 import pytest
 import torch
 
@@ -226,6 +228,45 @@ def test_paged_attention_split_tickets_reset(ops):
     for r in range(4):
         want = _ref_attn(cfg, qkv_all[r], q[r, :1024].float().cpu(), lens[r], cs)
         assert_close_bf16(a[r], want, ulps=1.0, atol=2e-3, what=f"split attn row {r}")
+
+
+@pytest.mark.parametrize("case", ["ragged", "long_few", "zeros_at_edges", "beyond_plan"])
+def test_paged_attention_balanced_page_ranges(ops, case):
+    """4 < T <= 4096 rows: the launch's pages are cut into 148 equal ranges, rows cut by a range
+    boundary are merged by ticket.  Ragged lengths, rows spanning many CTAs, kv_len = 0 rows at the
+    start / end / around range boundaries; a second launch over the same workspace must give the
+    same bits (tickets self-reset).  'beyond_plan' (T > 4096) takes the fixed-split kernel."""
+    cfg = T3ModelConfig()
+    rng = random.Random(11)
+    if case == "ragged":
+        lens = [850, 333, 64]
+        rows = [(rng.randrange(3), 0) for _ in range(300)]
+        rows = [(s, rng.randint(1, lens[s])) for s, _ in rows]
+    elif case == "long_few":
+        lens = [1000, 977]
+        rows = [(0, 1000), (1, 977), (0, 999), (1, 1), (0, 17), (1, 500), (0, 3)]
+    elif case == "zeros_at_edges":
+        lens = [400, 90]
+        rows = [(0, 0)] * 3 + [(rng.randrange(2), 0) for _ in range(200)] + [(1, 0)] * 5
+        rows = [(s, 0 if i < 3 or i >= 203 or i % 7 == 0 else rng.randint(1, lens[s])) for i, (s, _) in enumerate(rows)]
+    else:
+        lens = [40, 33]
+        rows = [(i & 1, 1 + (i * 7) % lens[i & 1]) for i in range(4100)]
+    kv, bt_d, qkv_all, cs = _build_paged(ops, cfg, lens, seed=21)
+    g = torch.Generator().manual_seed(6)
+    q = torch.randn(len(rows), 3072, generator=g).to(BF16)
+    args = (dev(q), kv, bt_d, dev(torch.tensor([r for r, _ in rows], dtype=torch.int32)),
+            dev(torch.tensor([L for _, L in rows], dtype=torch.int32)), max(lens))
+    out = ops.paged_attn_decode(*args).clone()
+    assert torch.equal(ops.paged_attn_decode(*args), out)
+    # plan built once and reused by later launches over the same kv_len (what the engine does per step)
+    assert torch.equal(ops.paged_attn_decode(*args, plan="make"), out)
+    assert torch.equal(ops.paged_attn_decode(*args, plan="reuse"), out)
+    check = range(len(rows)) if len(rows) <= 400 else range(0, len(rows), 41)
+    for i in check:
+        r, L = rows[i]
+        want = _ref_attn(cfg, qkv_all[r], q[i, :1024].float(), L, cs) if L else torch.zeros(1024)
+        assert_close_bf16(out[i], want, ulps=1.0, atol=2e-3, what=f"{case} row {i} (seq {r}, L={L})")
 
 
 # ------------------------------------------------------------------ fused layer pieces

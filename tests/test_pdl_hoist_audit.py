@@ -1,0 +1,25 @@
+"""Static check on the built library (no GPU): no kernel may read what its predecessor produces
+before griddepcontrol.wait.  nvcc is free to move `const __restrict__` loads above the wait's memory
+clobber (it did, for the attention page-range plan: LDG.E.CONSTANT before ACQBULK, stale plans under
+programmatic dependent launch), so the SASS is audited: only the kernels that prefetch WEIGHTS ahead
+of the wait by design may have global loads in front of it."""
+import os
+import shutil
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SO = os.path.join(ROOT, "chatterbox_vllm_b200", "libcbx_t3.so")
+# weight prefetch before the wait is the point of these two (k_gemv.cu / k_gemm.cu headers)
+WEIGHT_PREFETCH = ("gemv_fused_kernel", "gemm_tc_kernel")
+
+
+@pytest.mark.skipif(shutil.which("cuobjdump") is None or not os.path.exists(SO), reason="needs cuobjdump and the built library")
+def test_no_activation_load_hoisted_above_griddepcontrol_wait():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "audit_pdl_hoist.py"), SO],
+                         capture_output=True, text=True, check=True).stdout
+    flagged = [l for l in out.splitlines() if "before the wait" in l and not l.startswith(WEIGHT_PREFETCH)]
+    assert not flagged, "loads hoisted above griddepcontrol.wait:\n" + "\n".join(flagged)
+    assert any(l.startswith("paged_attn_decode_bal_kernel") and l.endswith("clean") for l in out.splitlines()), out[:400]

@@ -8,11 +8,11 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "chatterbox_vllm_b200", "libcbx_t3.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-HOT = ["paged_attn_decode_kernel", "paged_attn_small_kernel", "paged_attn_prefill_kernel", "gemm_tc_kernel", "gemv_fused_kernel",
+HOT = ["paged_attn_decode_bal_kernel", "attn_plan_kernel", "paged_attn_decode_kernel", "paged_attn_small_kernel", "paged_attn_prefill_kernel", "gemm_tc_kernel", "gemv_fused_kernel",
        "cfg_sample_kernel", "rmsnorm_kernel", "decode_mega_kernel", "postprocess_tokens_kernel", "linear_f32_kernel"]
 KEEP = {"gemm_tc_kernel_int_128_int_1_int_1", "gemm_tc_kernel_int_128_int_2_int_1", "gemm_tc_kernel_int_64_int_4_int_1",
         "gemv_fused_kernel_int_2_int_1_int_1_int_2_int_12", "gemv_fused_kernel_int_2_int_4_int_0_int_3_int_16",
-        "paged_attn_decode_kernel_bool_0", "paged_attn_small_kernel_int_4", "paged_attn_prefill_kernel", "cfg_sample_kernel",
+        "paged_attn_decode_bal_kernel", "paged_attn_small_kernel_int_4", "paged_attn_prefill_kernel", "cfg_sample_kernel",
         "rmsnorm_kernel_int_2"}            # one listing per kernel family; the summary covers every instantiation
 KEYS = ["UTCHMMA", "UTCBAR", "UTMALDG", "UBLKCP", "UBLKPF", "LDTM", "HMMA", "LDSM", "SYNCS", "UCGABAR", "ACQBULK", "LDG", "STG",
         "LDS", "STS", "FFMA", "MUFU", "ATOMS", "RED", "BAR.SYNC"]
