@@ -144,7 +144,8 @@ def main():
     pre = L0 - PREFIX - 1                                       # untimed decode steps (>= W warm-up)
     max_tokens = 1 + pre + K
     max_len = PREFIX + max_tokens + 8
-    eng = T3Engine(random_state_dict(30, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
+    n_layers = int(os.environ.get("CBX_BENCH_LAYERS", "30"))    # tuning aid only: the bench line is for 30
+    eng = T3Engine(random_state_dict(n_layers, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
                    max_rows=16384, base_seed=1234 + rank)
     sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=max_tokens, ignore_eos=True)
     # global prompt index keeps the Philox streams independent of how requests are sharded

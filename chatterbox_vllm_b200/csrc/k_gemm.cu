@@ -17,6 +17,7 @@
 // k-blocks before griddepcontrol.wait, so the weight stream overlaps the previous kernel's tail;
 // activation tiles follow after the wait.
 #include <cuda.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <map>
@@ -31,33 +32,56 @@ namespace {
 constexpr int BM = 128, BK = 64;
 constexpr int kThreads = 256;
 
-template <int BN>
+// -DCBX_GEMM_PROF: per-CTA %globaltimer stamps of every launch (tools/gemm_timeline.py reads them through
+// cbx_gemm_prof_read).  Stamps: 0 entry, 1 setup done, 2 producer past griddepcontrol.wait, 3 first stage
+// landed, 4 last MMA issued, 5 accumulator complete, 6 epilogue done.
+#ifdef CBX_GEMM_PROF
+constexpr int kProfLaunches = 256, kProfCtas = 160;
+__device__ unsigned long long g_prof[kProfLaunches][kProfCtas][8];
+int g_prof_next = 0;
+__device__ __forceinline__ void prof_stamp(int id, int k) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  if (id >= 0 && id < kProfLaunches && cta < kProfCtas) g_prof[id][cta][k] = t;
+}
+#define PROF(k) prof_stamp(ea.prof_id, k)
+#else
+#define PROF(k)
+#endif
+
+// CN = 2: the CTA pair of a cluster issues ONE tcgen05.mma.cta_group::2 (M = 256: 128 rows per CTA) per
+// K = 16 step; each CTA stages its own 128 activation rows and only HALF of the BN weight rows.
+template <int BN, int CN = 1>
 struct Cfg {
-  static constexpr int kStages = BN == 128 ? 6 : 8;
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBBytes = BN / CN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = kStageBytes > 24576 ? 6 : 8;
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   // Throughput configuration for grids of many tiles (prefill): a ring shallow enough that TWO CTAs
   // share an SM, so one CTA's epilogue (TMEM -> registers -> global) runs under the other's MMAs.
-  static constexpr int kStagesShallow = BN == 128 ? 3 : 4;
+  static constexpr int kStagesShallow = kStageBytes > 24576 ? 3 : 4;
   static constexpr int kSmemShallow = kStagesShallow * kStageBytes + 1024 + 256;
 };
 
 struct EpiArgs {               // EPI 2 only
   const bf16* cos_sin; const int32_t* pos; const int64_t* slot; uint8_t* kv_layer;
+  int prof_id;                 // CBX_GEMM_PROF builds only
 };
 
-// CN = CTAs per cluster along N.  The CN CTAs of a cluster compute neighbouring column tiles of the
-// SAME row tile, so they need the same activation (A) k-slices: each loads 1/CN of the A tile and
-// TMA-multicasts it into every CTA of the cluster (the decode GEMMs are bound by bytes entering the
-// SMs from L2, and activation re-reads are most of those bytes).
+// CN = 2: CTA pair along M (grid.x = row tiles, cluster dims (2, 1, 1), rank 0 = leader).  The decode GEMMs are bound by the
+// bytes entering the SMs (activation re-reads are most of them); a pair computes a
+// 256 x BN tile while each CTA ingests 128 activation rows + BN/2 weight rows per k-step, i.e. the
+// weight bytes per output element halve.  Both producers signal the LEADER's full barrier (peer bit of
+// the barrier address cleared, .cta_group::2 copy), the leader's elected thread issues the MMAs and
+// multicasts its commits to both CTAs' empty / accumulator barriers, each CTA drains its own TMEM.
 template <int BN, int EPI, int CN>
 __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                               const __grid_constant__ CUtensorMap tma_b,
                                                               bf16* __restrict__ y, int M, int N, int K, int ldy,
                                                               const EpiArgs ea, const int n_stages) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + n_stages * C::kStageBytes);
@@ -66,7 +90,8 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+  // pair mode: the two row tiles of a cluster are neighbours along grid.x (cluster dims (2, 1, 1))
+  const int n0 = (CN == 1 ? blockIdx.x : blockIdx.y) * BN, m0 = (CN == 1 ? blockIdx.y : blockIdx.x) * BM;
   const int n_kb = K / BK / gridDim.z;                 // k-blocks of this CTA's K slice (split-K over blockIdx.z)
   const int kb0 = blockIdx.z * n_kb;
 
@@ -75,84 +100,95 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   constexpr uint16_t kMask = (uint16_t)((1u << CN) - 1);
 
   pdl_trigger();
+  if (threadIdx.x == 0) PROF(0);
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CN); }
+    for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, BN);
-    tmem_relinquish();
+    if (CN == 1) { tmem_alloc(tmem_slot, BN); tmem_relinquish(); }
+    else { tmem_alloc_pair(tmem_slot, BN); tmem_relinquish_pair(); }
   }
   tc_fence_before();
   __syncthreads();
-  if (CN > 1)      // peers' barriers must exist before anyone multicasts into them
+  if (CN > 1)      // the peer's barriers must exist before anyone signals them
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) PROF(1);
 
   if (warp == 0) {
     if (lane == 0) {
       auto kc = [&](int kb) { return kb0 + kb; };
-      // A tile: with CN > 1 this CTA fetches rows [crank·128/CN, +128/CN) and multicasts them to the cluster
-      auto load_a = [&](uint8_t* stage, int kb, uint64_t* bar) {
-        if (CN == 1) {
-          tma_load_2d(stage, &tma_a, kc(kb) * BK, m0, bar);
-        } else {
-          constexpr int kRows = BM / CN;
-          asm volatile(
-              "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-              " [%0], [%1, {%3, %4}], [%2], %5;"
-              ::"r"(smem_u32(stage + crank * kRows * 128)), "l"(&tma_a), "r"(smem_u32(bar)), "r"(kc(kb) * BK),
-                "r"(m0 + (int)crank * kRows), "h"(kMask) : "memory");
-        }
+      // pair: this CTA's loads complete on the leader's barrier of the same stage
+      auto load = [&](uint8_t* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+        if (CN == 1) tma_load_2d(dst, map, c0, c1, bar);
+        else tma_load_2d_pair(dst, map, c0, c1, bar);
       };
+      const int nb = n0 + (int)crank * (BN / CN);       // this CTA's weight rows of the tile
       // weights of the first ring fill do not depend on the previous kernel
       const int n_pre = n_kb < n_stages ? n_kb : n_stages;
       for (int kb = 0; kb < n_pre; ++kb) {
-        mbar_arrive_expect_tx(&full[kb], C::kStageBytes);
-        tma_load_2d(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kc(kb) * BK, n0, &full[kb]);
+        if (crank == 0) mbar_arrive_expect_tx(&full[kb], CN * C::kStageBytes);
+        load(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kc(kb) * BK, nb, &full[kb]);
       }
       pdl_wait();
+      PROF(2);
       for (int kb = 0; kb < n_pre; ++kb)
-        load_a(smem + kb * C::kStageBytes, kb, &full[kb]);
+        load(smem + kb * C::kStageBytes, &tma_a, kc(kb) * BK, m0, &full[kb]);
       for (int kb = n_pre; kb < n_kb; ++kb) {
         const int s = kb % n_stages, ph = (kb / n_stages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
-        mbar_arrive_expect_tx(&full[s], C::kStageBytes);
+        if (crank == 0) mbar_arrive_expect_tx(&full[s], CN * C::kStageBytes);
         uint8_t* sa = smem + s * C::kStageBytes;
-        load_a(sa, kb, &full[s]);
-        tma_load_2d(sa + C::kABytes, &tma_b, kc(kb) * BK, n0, &full[s]);
+        load(sa, &tma_a, kc(kb) * BK, m0, &full[s]);
+        load(sa + C::kABytes, &tma_b, kc(kb) * BK, nb, &full[s]);
       }
     } else {
       pdl_wait();
     }
   } else if (warp == 1) {
     pdl_wait();
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    if (lane == 0 && crank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CN, BN);
       for (int kb = 0; kb < n_kb; ++kb) {
         const int s = kb % n_stages, ph = (kb / n_stages) & 1;
         mbar_wait(&full[s], ph);
+        if (kb == 0) PROF(3);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + s * C::kStageBytes);
         const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + C::kABytes);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k)           // +32 bytes per K=16 step inside the swizzle atom
-          umma_bf16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        for (int k = 0; k < BK / 16; ++k) {         // +32 bytes per K=16 step inside the swizzle atom
+          if (CN == 1) umma_bf16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          else umma_bf16_pair(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        }
         if (CN == 1) umma_commit(&empty[s]);
-        else umma_commit_mc(&empty[s], kMask);      // frees the stage in every CTA of the cluster
+        else umma_commit_pair(&empty[s], kMask);    // frees the stage in both CTAs
       }
-      umma_commit(tmem_full);
+      if (CN == 1) umma_commit(tmem_full);
+      else umma_commit_pair(tmem_full, kMask);
+      PROF(4);
     }
-  } else if (warp >= 4) {
-    const int ew = warp - 4;                           // == warp % 4: TMEM lane quarter
+  } else if (warp < 4) {
     pdl_wait();
+  }
+  // Epilogue.  A warp may only read the TMEM lane quarter (warp % 4); with one warp per quarter the
+  // epilogue is a single warp per SM sub-partition issuing dependent math (measured: SiLU epilogue
+  // +3.5 us at T = 256).  For the column-chunked epilogues the four role warps, idle by now, take every
+  // other 32-column chunk of their quarter.
+  constexpr bool kAllWarps = EPI != 2;
+  if (warp >= 4 || kAllWarps) {
+    __syncwarp();
+    const int ew = warp & 3;                           // TMEM lane quarter
+    if (warp >= 4) pdl_wait();
     mbar_wait(tmem_full, 0);
+    if (threadIdx.x == 128) PROF(5);
     tc_fence_after();
     const int row = m0 + ew * 32 + lane;
     if (EPI == 2) {
@@ -215,7 +251,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
       }
     } else {
 #pragma unroll 1
-    for (int cb = 0; cb < BN / 32; ++cb) {
+    for (int cb = warp < 4 ? 1 : 0; cb < BN / 32; cb += 2) {
       uint32_t r[32];
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + cb * 32, r);
       tmem_ld_wait();
@@ -228,7 +264,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
           for (int i = 0; i < 8; ++i) {
             const float g0 = round_bf16(__uint_as_float(r[2 * i])), g1 = round_bf16(__uint_as_float(r[2 * i + 1]));
             const float u0 = round_bf16(__uint_as_float(r[16 + 2 * i])), u1 = round_bf16(__uint_as_float(r[17 + 2 * i]));
-            o[i] = pack_bf16(g0 / (1.f + __expf(-g0)) * u0, g1 / (1.f + __expf(-g1)) * u1);
+            o[i] = pack_bf16(__fdividef(g0, 1.f + __expf(-g0)) * u0, __fdividef(g1, 1.f + __expf(-g1)) * u1);
           }
           if (col + 32 <= N) {
             uint4* dst = reinterpret_cast<uint4*>(y + (size_t)row * ldy + col / 2);
@@ -277,11 +313,13 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
     tc_fence_before();
   }
   __syncthreads();
-  if (CN > 1)      // nobody leaves while a peer may still multicast into / arrive on this CTA's shared memory
+  if (threadIdx.x == 0) PROF(6);
+  if (CN > 1)      // nobody leaves while the leader's MMAs may still read this CTA's shared memory / TMEM
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, BN);
+    if (CN == 1) tmem_dealloc(tmem_base, BN);
+    else tmem_dealloc_pair(tmem_base, BN);
   }
 }
 
@@ -323,14 +361,14 @@ int make_map(CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) 
   return 0;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int CN>
 int set_attr() {
-  cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
-  CBX_REQUIRE(e == cudaSuccess, "gemm smem attribute: %s", cudaGetErrorString(e));
-  e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
+  cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, CN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, CN>::kSmem);
   CBX_REQUIRE(e == cudaSuccess, "gemm smem attribute: %s", cudaGetErrorString(e));
   return 0;
 }
+template <int EPI>
+int set_attr_pairs() { return set_attr<64, EPI, 2>() || set_attr<128, EPI, 2>() || set_attr<256, EPI, 2>(); }
 }  // namespace
 namespace cbx {
 // Tensor map over one layer's KV pages seen as bf16 rows of 64 elements (512 rows per 64 KiB page: K
@@ -342,8 +380,9 @@ int make_kv_rows_map(CUtensorMap* m, const void* kv_layer) {
 int init_gemm() {
   static bool done = false;
   if (done) return 0;
-  if (set_attr<64, 0>() || set_attr<64, 1>() || set_attr<128, 0>() || set_attr<128, 1>() || set_attr<64, 2>() ||
-      set_attr<64, 3>() || set_attr<128, 3>() || set_attr<64, 4>() || set_attr<128, 2>()) return -1;
+  if (set_attr<64, 0, 1>() || set_attr<64, 1, 1>() || set_attr<128, 0, 1>() || set_attr<128, 1, 1>() || set_attr<64, 2, 1>() ||
+      set_attr<64, 3, 1>() || set_attr<128, 3, 1>() || set_attr<64, 4, 1>() || set_attr<128, 2, 1>()) return -1;
+  if (set_attr_pairs<0>() || set_attr_pairs<1>() || set_attr_pairs<2>() || set_attr_pairs<3>() || set_attr_pairs<4>()) return -1;
   CBX_REQUIRE(get_encode() != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   done = true;
   return 0;
@@ -355,32 +394,67 @@ int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, 
            const EpiArgs& ea = EpiArgs(), int splits = 1) {
   using C = Cfg<BN>;
   if (cbx::init_gemm()) return -1;
-  // CBX_GEMM_MC=1: clusters of 2 column tiles share the activation tile by TMA multicast.  Measured
-  // on B200 (T=256): gate_up 12.9 -> 13.2 us, QKV 9.7 -> 10.3 us -- multicast halves the L2 reads of
-  // A but every SM still ingests a whole A tile, and SM ingest is what bounds these GEMMs.  Off.
-  static const int mc_env = getenv("CBX_GEMM_MC") ? atoi(getenv("CBX_GEMM_MC")) : 0;
-  int n_tiles = (N + BN - 1) / BN;
-  const int m_tiles = (M + BM - 1) / BM;
-  const bool mc = mc_env != 0 && n_tiles >= 2 && (int64_t)n_tiles * m_tiles * splits <= 2 * 148;
+  const int n_tiles = (N + BN - 1) / BN, m_tiles = (M + BM - 1) / BM;
   CUtensorMap ma, mb;
-  if (make_map(&ma, x, M, K, mc ? BM / 2 : BM)) return -1;
+  if (make_map(&ma, x, M, K, BM)) return -1;
   if (make_map(&mb, W, N, K, BN)) return -1;
-  cudaError_t e;
   static const int shallow_env = getenv("CBX_GEMM_SHALLOW") ? atoi(getenv("CBX_GEMM_SHALLOW")) : 1;
   const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * 148;
   const int n_stages = shallow ? C::kStagesShallow : C::kStages;
   const int smem_bytes = shallow ? C::kSmemShallow : C::kSmem;
-  if (mc) {
-    n_tiles = (n_tiles + 1) & ~1;                      // pad to whole clusters: out-of-range tiles load zeros, store nothing
-    e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), smem_bytes, s, 2, ma, mb,
-                           (bf16*)y, M, N, K, ldy, ea, n_stages);
-  } else {
-    e = launch_pdl(gemm_tc_kernel<BN, EPI, 1>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), smem_bytes, s, ma, mb, (bf16*)y, M,
-                   N, K, ldy, ea, n_stages);
-  }
+#ifdef CBX_GEMM_PROF
+  EpiArgs eap = ea; eap.prof_id = g_prof_next++;
+  fprintf(stderr, "gemm_prof id=%d BN=%d EPI=%d M=%d N=%d K=%d grid=%dx%dx%d\n", eap.prof_id, BN, EPI, M, N, K, n_tiles, m_tiles, splits);
+  const EpiArgs& eal = eap;
+#else
+  const EpiArgs& eal = ea;
+#endif
+  cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI, 1>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), smem_bytes, s, ma, mb,
+                             (bf16*)y, M, N, K, ldy, eal, n_stages);
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
+}
+// CTA-pair form: 256 x BN tile per cluster of two CTAs along M (grid.x padded to even: rows beyond M load
+// zeros and store nothing).  (An earlier experiment multicast the activation tile across two column
+// tiles instead: it halved the L2 reads of A but not what each SM ingests, and measured 2-5 % slower.)
+template <int BN, int EPI>
+int launch_pair(const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s,
+                const EpiArgs& ea = EpiArgs(), int splits = 1) {
+  using C = Cfg<BN, 2>;
+  if (cbx::init_gemm()) return -1;
+  const int n_tiles = (N + BN - 1) / BN, m_tiles = ((M + BM - 1) / BM + 1) & ~1;
+  CUtensorMap ma, mb;
+  if (make_map(&ma, x, M, K, BM)) return -1;
+  if (make_map(&mb, W, N, K, BN / 2)) return -1;
+  static const int shallow_env = getenv("CBX_GEMM_SHALLOW") ? atoi(getenv("CBX_GEMM_SHALLOW")) : 1;
+  const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * 148;
+  const int n_stages = shallow ? C::kStagesShallow : C::kStages;
+  const int smem_bytes = shallow ? C::kSmemShallow : C::kSmem;
+  cudaError_t e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(m_tiles, n_tiles, splits), dim3(kThreads), smem_bytes, s, 2,
+                                     ma, mb, (bf16*)y, M, N, K, ldy, ea, n_stages);
+  CBX_REQUIRE(e == cudaSuccess, "gemm_tc (pair) launch failed: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
+// Pair tile width chosen for a problem: 0 = single-CTA tiles.  env CBX_GEMM_PAIR = 0 | 64 | 128 | 256 forces it.
+// Measured on B200 (tools/bench_gemm.py, bench_gemm_decode.py): at M = 16000 the 256-wide pair runs gate_up+SiLU
+// at 1235 TFLOP/s (single-CTA 128-wide tiles: 1037; cuBLAS plain GEMM of that shape: 1221), down 1116 (997),
+// QKV+RoPE 831 (793); at M = 256 every pair shape is SLOWER than single-CTA tiles (gate_up 9.4 vs 8.6 us, QKV
+// 8.2 vs 7.4): the cluster launch + two cluster barriers cost more than the saved ingest.  So: pairs from
+// `min_rows` rows up.
+int pair_width(int M, int min_rows) {
+  static const int env = getenv("CBX_GEMM_PAIR") ? atoi(getenv("CBX_GEMM_PAIR")) : -1;
+  if (M <= BM) return 0;                               // a lone row tile has no partner
+  if (env >= 0) return env;
+  return M >= min_rows ? 256 : 0;
+}
+template <int EPI>
+int launch_pair_w(int w, const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s,
+                  const EpiArgs& ea = EpiArgs(), int splits = 1) {
+  if (w == 64) return launch_pair<64, EPI>(x, W, y, M, N, K, ldy, s, ea, splits);
+  if (w == 128) return launch_pair<128, EPI>(x, W, y, M, N, K, ldy, s, ea, splits);
+  return launch_pair<256, EPI>(x, W, y, M, N, K, ldy, s, ea, splits);
 }
 }  // namespace
 
@@ -397,6 +471,8 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
   // path are bound by L2->SM bytes, which a 128 x 128 tile halves per output element.
   bool narrow = (int64_t)m_tiles * ((N + 127) / 128) < 100;
   if (const char* v = getenv("CBX_GEMM_BN")) narrow = atoi(v) == 64;      // tuning aid
+  if (const int w = pair_width(M, 4096))
+    return epilogue == 1 ? launch_pair_w<1>(w, x, W, y, M, N, K, ldy, s) : launch_pair_w<0>(w, x, W, y, M, N, K, ldy, s);
   if (epilogue == 1) return narrow ? launch<64, 1>(x, W, y, M, N, K, ldy, s) : launch<128, 1>(x, W, y, M, N, K, ldy, s);
   return narrow ? launch<64, 0>(x, W, y, M, N, K, ldy, s) : launch<128, 0>(x, W, y, M, N, K, ldy, s);
 }
@@ -404,6 +480,7 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
 int gemm_qkv_rope(const void* h, const void* Wqkv, void* qkv, const void* cos_sin, const int32_t* pos,
                   const int64_t* slot, void* kv_layer, int M, cudaStream_t s) {
   EpiArgs ea = {(const bf16*)cos_sin, pos, slot, (uint8_t*)kv_layer};
+  if (const int w = pair_width(M, 8192)) return launch_pair_w<2>(w, h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   // prefill-sized M: 128-wide tiles (two heads per tile) halve the activation re-reads
   if ((M + BM - 1) / BM * 24 >= 2 * 148) return launch<128, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   return launch<64, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
@@ -411,12 +488,14 @@ int gemm_qkv_rope(const void* h, const void* Wqkv, void* qkv, const void* cos_si
 // EPI 3: res[M, N] = bf16(bf16(x·W^T) + res), N % 32 == 0.
 int gemm_residual(const void* x, const void* W, void* res, int M, int N, int K, cudaStream_t s) {
   CBX_REQUIRE(N % 128 == 0 && K % BK == 0, "gemm_residual: bad shape N=%d K=%d", N, K);
+  if (const int w = pair_width(M, 4096)) return launch_pair_w<3>(w, x, W, res, M, N, K, N, s);
   const bool narrow = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
   return narrow ? launch<64, 3>(x, W, res, M, N, K, N, s) : launch<128, 3>(x, W, res, M, N, K, N, s);
 }
 // EPI 4: part[splits][M][N] fp32 = per-K-slice partial products (no rounding); N % 64 == 0.
 int gemm_partials(const void* x, const void* W, void* part, int M, int N, int K, int splits, cudaStream_t s) {
   CBX_REQUIRE(N % 64 == 0 && splits >= 1 && K % (BK * splits) == 0, "gemm_partials: bad shape N=%d K=%d splits=%d", N, K, splits);
+  if (const int w = pair_width(M, 4096)) return launch_pair_w<4>(w, x, W, part, M, N, K, N, s, EpiArgs(), splits);
   return launch<64, 4>(x, W, part, M, N, K, N, s, EpiArgs(), splits);
 }
 int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
@@ -431,3 +510,14 @@ extern "C" int cbx_linear(const void* x, const void* W, void* y, int T, int N, i
   if (path == 1 || (path == 0 && gemv_ok)) return cbx::gemv_bf16(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream);
   return cbx::gemm_bf16_tc(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream);
 }
+
+#ifdef CBX_GEMM_PROF
+// debug builds only: copy the stamps of launches [0, n) to host (n * 160 * 8 u64) and restart the launch ids
+extern "C" int cbx_gemm_prof_read(unsigned long long* out, int n) {
+  cudaDeviceSynchronize();
+  cudaError_t e = cudaMemcpyFromSymbol(out, g_prof, (size_t)n * kProfCtas * 8 * sizeof(unsigned long long));
+  const int used = g_prof_next;
+  g_prof_next = 0;
+  return e == cudaSuccess ? used : -1;
+}
+#endif

@@ -86,7 +86,7 @@ def test_linear_gemv(ops, T, N, K):
     assert_close_bf16(y, _ref_linear(x, W), ulps=1.0, atol=2e-3, what=f"gemv T={T} N={N} K={K}")
 
 
-@pytest.mark.parametrize("T", [1, 5, 64, 128, 200, 256, 300, 2500])     # 2500 rows: the two-CTAs-per-SM configuration
+@pytest.mark.parametrize("T", [1, 5, 64, 128, 200, 256, 300, 2500, 4200])     # 2500 rows: the two-CTAs-per-SM configuration; 4200: CTA pairs (cta_group::2)
 @pytest.mark.parametrize("N,K", [(3072, 1024), (1024, 1024), (1024, 4096), (8194, 1024)])
 def test_linear_gemm_tcgen05(ops, T, N, K):
     g = torch.Generator().manual_seed(N + 7 * T)
@@ -275,7 +275,7 @@ def _unswizzled_k(page_bf16, h, tok):
     return torch.stack([krow[c ^ (tok & 7)] for c in range(8)]).reshape(64)
 
 
-@pytest.mark.parametrize("T", [1, 2, 4, 6, 200, 1600])               # 1600 rows: 128-wide tiles, two heads per RoPE epilogue
+@pytest.mark.parametrize("T", [1, 2, 4, 6, 200, 1600, 8300])         # 1600 rows: 128-wide tiles, two heads per RoPE epilogue; 8300: CTA pairs, four heads
 def test_layer_qkv_fused_norm_rope_append(ops, T):
     """[RMSNorm → QKV → RoPE → KV append] in one op (GEMV kernel for T <= 4, rmsnorm + tcgen05 GEMM
     with the RoPE/append epilogue above) against the oracle's op-by-op bf16 chain."""
