@@ -116,6 +116,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-b1", action="store_true")
+    ap.add_argument("--no-fp8", action="store_true", help="skip the separately reported FP8-e4m3 weight leg")
+    ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8_e4m3"],
+                    help="profiling aid: run the WHOLE bench on FP8 weights (the line then says so; the default line is bf16)")
     ap.add_argument("--ctx0", type=int, default=None,
                     help="profiling aid: context length at the first timed step (default: centred on the workload mean)")
     args = ap.parse_args()
@@ -146,7 +149,8 @@ def main():
     max_len = PREFIX + max_tokens + 8
     n_layers = int(os.environ.get("CBX_BENCH_LAYERS", "30"))    # tuning aid only: the bench line is for 30
     eng = T3Engine(random_state_dict(n_layers, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
-                   max_rows=16384, base_seed=1234 + rank)
+                   max_rows=16384, base_seed=1234 + rank, weight_dtype=args.weights)
+    w_bytes = W_BYTES if args.weights == "bf16" else eng.projection_weight_bytes()
     sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=max_tokens, ignore_eos=True)
     # global prompt index keeps the Philox streams independent of how requests are sharded
     reqs = [Request(random_prompt(PREFIX - 35, seed=rank * B + i), random_cond_emb(rank * B + i, pinned=True), sp,
@@ -250,32 +254,87 @@ def main():
         assert all(len(o) == gen_e2e for o in out)
 
     # ---- M2 leg: p50 decode-step latency at B = 1 pair (config 1 shape: P = 75, 500 tokens)
-    b1 = None
-    if rank == 0 and not args.no_b1:
-        G1 = min(GEN, eng.max_model_len - 76)
+    def b1_leg(e, wb):
+        G1 = min(GEN, e.max_model_len - 76)
         sp1 = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=G1, ignore_eos=True)
         r1 = [Request(random_prompt(40, seed=1), random_cond_emb(2, pinned=True), sp1, uid=999_983)]
-        with torch.cuda.stream(eng.stream):
-            P1, held1 = eng._admit(r1)
-            eng._init_sampler_state(r1, P1)
-            eng.prefill(r1, P1)
+        with torch.cuda.stream(e.stream):
+            P1, held1 = e._admit(r1)
+            e._init_sampler_state(r1, P1)
+            e.prefill(r1, P1)
             evs = [torch.cuda.Event(enable_timing=True) for _ in range(G1)]
             for i in range(20):                                  # warm-up steps (graph capture of bucket 1)
-                eng.decode(1, 1, P1[0] + 2 + i)
-            evs[0].record(eng.stream)
+                e.decode(1, 1, P1[0] + 2 + i)
+            evs[0].record(e.stream)
             for i in range(1, G1 - 20):
-                eng.decode(1, 1, P1[0] + 21 + i)
-                evs[i].record(eng.stream)
+                e.decode(1, 1, P1[0] + 21 + i)
+                evs[i].record(e.stream)
             torch.cuda.synchronize()
-            eng._release(held1)
+            e._release(held1)
         dts = sorted(evs[i - 1].elapsed_time(evs[i]) for i in range(1, G1 - 20))
         p50, p95 = dts[len(dts) // 2], dts[int(len(dts) * 0.95)]
         ctx1 = P1[0] + 20 + (G1 - 20) // 2
-        bytes1 = W_BYTES + 2 * (KV_TOKEN_BYTES * (ctx1 + 1) + KV_TOKEN_BYTES + 2048)
-        b1 = {"metric": "p50_decode_step_ms_b1", "p50_ms": p50, "p95_ms": p95, "steps": len(dts),
-              "workload": f"1 CFG pair (2 seqs), prefix {P1[0]}, context {P1[0] + 21}..{P1[0] + G1} (mean {ctx1})",
-              "bytes_per_step": bytes1, "achieved_gbs": bytes1 / (p50 / 1e3) / 1e9,
-              "tokens_per_s": 1e3 / p50}
+        bytes1 = wb + 2 * (KV_TOKEN_BYTES * (ctx1 + 1) + KV_TOKEN_BYTES + 2048)
+        return {"metric": "p50_decode_step_ms_b1", "p50_ms": p50, "p95_ms": p95, "steps": len(dts),
+                "workload": f"1 CFG pair (2 seqs), prefix {P1[0]}, context {P1[0] + 21}..{P1[0] + G1} (mean {ctx1})",
+                "bytes_per_step": bytes1, "achieved_gbs": bytes1 / (p50 / 1e3) / 1e9,
+                "tokens_per_s": 1e3 / p50}
+
+    b1 = b1_leg(eng, w_bytes) if rank == 0 and not args.no_b1 else None
+
+    # ---- FP8-e4m3 weight leg, reported separately (north star): same M1 batch and b = 1 shape on an engine whose
+    # projections + head are e4m3 bytes with per-output-feature scales; activations / KV / sampler unchanged
+    fp8 = None
+    if rank == 0 and not args.no_fp8 and args.weights == "bf16":
+        eng.close()
+        del eng
+        torch.cuda.empty_cache()
+        e8 = T3Engine(random_state_dict(n_layers, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
+                      max_rows=16384, base_seed=1234 + rank, weight_dtype="fp8_e4m3")
+        K8 = min(K, 128)
+        L8 = max(PREFIX + 1 + W, PREFIX + GEN // 2 - K8 // 2)
+        pre8 = L8 - PREFIX - 1
+        sp8 = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=1 + pre8 + K8, ignore_eos=True)
+        for r in reqs:
+            r.params = sp8
+        with torch.cuda.stream(e8.stream):
+            P8, held8 = e8._admit(reqs)
+            e8._init_sampler_state(reqs, P8)
+            e8.prefill(reqs, P8)
+            e8._init_sampler_state(reqs, P8)
+            torch.cuda.synchronize()
+            q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            q0.record(e8.stream)
+            e8.prefill(reqs, P8)
+            q1.record(e8.stream)
+            done = 0
+            while done < pre8:
+                n = min(32, pre8 - done)
+                e8.decode(B, n, PREFIX + 1 + done + n)
+                done += n
+            torch.cuda.synchronize()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record(e8.stream)
+            done = 0
+            while done < K8:
+                n = min(32, K8 - done)
+                e8.decode(B, n, L8 + done + n)
+                done += n
+            f1.record(e8.stream)
+            torch.cuda.synchronize()
+            e8._release(held8)
+        ms8 = f0.elapsed_time(f1)
+        w8b = e8.projection_weight_bytes()
+        sb8 = w8b + 2 * B * (KV_TOKEN_BYTES * (L8 + K8 // 2 + 1) + KV_TOKEN_BYTES + 2048)
+        fp8 = {"weights": "fp8_e4m3 per output channel (weight-only; bf16 activations/KV, fp32 accumulate)",
+               "value": B * K8 / (ms8 / 1e3), "unit": "speech_tokens/s", "steps": K8, "ms_per_step": ms8 / K8,
+               "weight_bytes_per_step": w8b, "bytes_per_step": sb8, "step_achieved_gbs": sb8 / (ms8 / K8 / 1e3) / 1e9,
+               "prefill_ms": q0.elapsed_time(q1),
+               "tolerance": "kernels vs the oracle on dequantised weights: the bf16 path's bars; FP8 model vs bf16 model: "
+                            "head-logit rel-L2 <= 0.25 (tests/test_gpu_fp8.py)"}
+        if not args.no_b1:
+            fp8["b1"] = b1_leg(e8, w8b)
+        e8.close()
 
     if rank != 0:
         if world > 1:
@@ -284,6 +343,10 @@ def main():
     hbm, which = peaks()
     if b1:
         b1["frac_of_hbm_peak"] = b1["achieved_gbs"] / hbm
+    if fp8:
+        fp8["step_frac_of_hbm_peak"] = fp8["step_achieved_gbs"] / hbm
+        if "b1" in fp8:
+            fp8["b1"]["frac_of_hbm_peak"] = fp8["b1"]["achieved_gbs"] / hbm
     attn_bytes = 2 * B * (mean_ctx * (KV_TOKEN_BYTES // 30) + 2048 + 2048)
     traffic = None
     try:
@@ -293,10 +356,10 @@ def main():
         traffic = attn_bytes * tr["dram_bytes_per_launch"] / tr["algorithmic_bytes_same_launch"]
     except Exception:
         pass
-    step_bytes = W_BYTES + 2 * B * (KV_TOKEN_BYTES * (mean_ctx + 1) + KV_TOKEN_BYTES + 2048)
+    step_bytes = w_bytes + 2 * B * (KV_TOKEN_BYTES * (mean_ctx + 1) + KV_TOKEN_BYTES + 2048)
     line = {"metric": METRIC, "value": value, "unit": "speech_tokens/s", "n_gpus": world, "steps": K, "warmup": pre,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic",
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.weights == "bf16" else "bf16 activations, fp8_e4m3 weights", "data": "synthetic",
             "config": {"workload": f"M1: {B} CFG pairs ({2 * B} seqs) per GPU, prefix {PREFIX}, {GEN} speech tokens, "
                                    f"T3 Llama-520M random-init; timed steps at context {L0}..{L0 + K - 1} (mean {mean_ctx})",
                        "l2": "inputs larger than L2 (KV ~%.1f GB/step)" % (2 * B * mean_ctx * KV_TOKEN_BYTES / 1e9),
@@ -322,6 +385,8 @@ def main():
                                "causal paged attention) + head + first-token sampler"}
     if b1:
         line["b1"] = b1
+    if fp8:
+        line["fp8w"] = fp8
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline_sample()
     print(json.dumps(line), flush=True)

@@ -27,6 +27,12 @@ class Weights(C.Structure):
                 ("speech_emb", vp), ("speech_head", vp), ("cos_sin", vp), ("rms_eps", C.c_float)]
 
 
+class Fp8Weights(C.Structure):
+    _fields_ = [("n_layers", C.c_int), ("wqkv", C.POINTER(vp)), ("wo", C.POINTER(vp)), ("wgu", C.POINTER(vp)),
+                ("wd", C.POINTER(vp)), ("sqkv", C.POINTER(vp)), ("so", C.POINTER(vp)), ("sgu", C.POINTER(vp)),
+                ("sd", C.POINTER(vp)), ("speech_head", vp), ("shead", vp)]
+
+
 class EngineCfg(C.Structure):
     _fields_ = [("max_pairs", C.c_int), ("max_rows", C.c_int), ("max_model_len", C.c_int),
                 ("num_blocks", C.c_int), ("out_stride", C.c_int)]
@@ -46,6 +52,14 @@ _PROTOS = {
     "cbx_linear_partials": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "cbx_linear": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "cbx_pack_gate_up": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_quantize_fp8_rows": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_linear_fp8w": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "cbx_layer_qkv_fp8w": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_linear_residual_fp8w": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_linear_partials_fp8w": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "cbx_layer_gate_up_fp8w": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_head_logits_fp8w": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_engine_set_fp8_weights": (C.c_int, [vp, C.POINTER(Fp8Weights)]),
     "cbx_rope_kv_append": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_attn_scratch_bytes": (C.c_int64, [C.c_int, C.c_int]),
     "cbx_attn_num_splits": (C.c_int, [C.c_int, C.c_int]),

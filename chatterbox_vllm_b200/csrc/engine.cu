@@ -19,25 +19,28 @@ int64_t launches();
 int init_gemm();
 int init_attn();
 int init_sample();
-int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
+// every projection takes an optional per-output-feature scale: non-NULL = the weights are FP8-e4m3 bytes
+int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
 int gemv_qkv_rope(const void*, const void*, const void*, const void*, const int32_t*, const int64_t*, void*, void*, int,
-                  float, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0);
-int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0);
+                  float, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0, const float* wscale = nullptr);
+int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0,
+                  const float* wscale = nullptr);
 int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, cudaStream_t, const void* next_w = nullptr,
-                      size_t next_bytes = 0);
+                      size_t next_bytes = 0, const float* wscale = nullptr);
 void attn_set_prefetch(const void*, size_t);
 int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
 int paged_attn_decode_ex(const void*, const void*, const int32_t*, int, const int32_t*, const int32_t*, void*, void*, int32_t*,
                          int, int, bool, void*);
-int gemv_norm_head(const void*, const void*, const void*, void*, int, int, int, float, cudaStream_t);
-int gemm_bf16_tc(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
-int gemm_qkv_rope(const void*, const void*, void*, const void*, const int32_t*, const int64_t*, void*, int, cudaStream_t);
-int gemm_residual(const void*, const void*, void*, int, int, int, cudaStream_t);
+int gemv_norm_head(const void*, const void*, const void*, void*, int, int, int, float, cudaStream_t, const float* wscale = nullptr);
+int gemm_bf16_tc(const void*, const void*, void*, int, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
+int gemm_qkv_rope(const void*, const void*, void*, const void*, const int32_t*, const int64_t*, void*, int, cudaStream_t,
+                  const float* wscale = nullptr);
+int gemm_residual(const void*, const void*, void*, int, int, int, cudaStream_t, const float* wscale = nullptr);
 int launch_decode_prepare(const void*, const int32_t*, const int32_t*, const int32_t*, const int32_t*, int, void*,
                           int32_t*, int64_t*, int32_t*, int32_t*, int32_t*, int, cudaStream_t);
 int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t, const int32_t* pair_map = nullptr,
                       int n_sub = 0);
-int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t);
+int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
 struct MegaArgs {
   const bf16* ln1[32]; const bf16* wqkv[32]; const bf16* wo[32];
   const bf16* ln2[32]; const bf16* wgu[32]; const bf16* wd[32];
@@ -68,6 +71,11 @@ struct cbx_engine {
   cbx_engine_cfg cfg;
   cbx_weights w;
   std::vector<const void*> wqkv, wo, wgu, wd, ln1, ln2;
+  // FP8-e4m3 weight path (cbx_engine_set_fp8_weights): the four projections above and the head then point at
+  // e4m3 bytes and these hold their per-output-feature scales; NULL entries = bf16 weights
+  std::vector<const float*> sqkv, so, sgu, sd;
+  const void* head = nullptr; const float* shead = nullptr;
+  bool fp8 = false;
   uint8_t* kv_cache;
   int32_t* block_table;
   int bt_stride;
@@ -131,6 +139,8 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   const int L = w->n_layers;
   e->wqkv.assign(w->wqkv, w->wqkv + L); e->wo.assign(w->wo, w->wo + L); e->wgu.assign(w->wgu, w->wgu + L);
   e->wd.assign(w->wd, w->wd + L); e->ln1.assign(w->ln1, w->ln1 + L); e->ln2.assign(w->ln2, w->ln2 + L);
+  e->sqkv.assign(L, nullptr); e->so.assign(L, nullptr); e->sgu.assign(L, nullptr); e->sd.assign(L, nullptr);
+  e->head = w->speech_head;
   e->kv_cache = (uint8_t*)kv_cache;
   e->block_table = block_table;
   e->bt_stride = (cfg->max_model_len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
@@ -164,21 +174,46 @@ extern "C" void* cbx_engine_buffer(cbx_engine* e, const char* name) {
 }
 
 // ---- fused layer pieces (C-ABI, regime chosen by T) -----------------------------------------
+static int layer_qkv(const void* res, const void* ln_w, const void* Wqkv, const float* sc, const void* cos_sin,
+                     const int32_t* pos, const int64_t* slot, void* qkv, void* kv_layer, void* h_scratch, int T, float eps,
+                     void* stream) {
+  if (T <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (T <= 4) return gemv_qkv_rope(res, ln_w, Wqkv, cos_sin, pos, slot, qkv, kv_layer, T, eps, s, nullptr, 0, sc);
+  CBX_REQUIRE(h_scratch != nullptr, "cbx_layer_qkv: h_scratch is NULL for T > 4");
+  if (cbx_rmsnorm(res, nullptr, ln_w, h_scratch, T, eps, stream)) return -1;
+  return gemm_qkv_rope(h_scratch, Wqkv, qkv, cos_sin, pos, slot, kv_layer, T, s, sc);
+}
+static int linear_residual(const void* x, const void* W, const float* sc, void* res, int T, int K, void* stream) {
+  if (T <= 0) return 0;
+  CBX_REQUIRE(K == 1024 || K == 4096, "cbx_linear_residual: K=%d unsupported", K);
+  if (T <= 4) return gemv_residual(x, W, res, T, K, (cudaStream_t)stream, nullptr, 0, sc);
+  return gemm_residual(x, W, res, T, 1024, K, (cudaStream_t)stream, sc);
+}
+static int layer_gate_up(const void* res, const void* ln_w, const void* Wgu, const float* sc, void* act, void* h_scratch,
+                         int T, float eps, void* stream) {
+  if (T <= 0) return 0;
+  if (T <= 4) return gemv_norm_gate_up(res, ln_w, Wgu, act, T, eps, (cudaStream_t)stream, nullptr, 0, sc);
+  CBX_REQUIRE(h_scratch != nullptr, "cbx_layer_gate_up: h_scratch is NULL for T > 4");
+  if (cbx_rmsnorm(res, nullptr, ln_w, h_scratch, T, eps, stream)) return -1;
+  return gemm_bf16_tc(h_scratch, Wgu, act, T, 8192, 1024, 4096, 1, (cudaStream_t)stream, sc);
+}
+static int head_logits(const void* res, const void* norm_w, const void* Whead, const float* sc, void* logits,
+                       void* h_scratch, int T, float eps, void* stream) {
+  if (T <= 0) return 0;
+  if (T <= 4)
+    return gemv_norm_head(res, norm_w, Whead, logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD, eps, (cudaStream_t)stream, sc);
+  CBX_REQUIRE(h_scratch != nullptr, "cbx_head_logits: h_scratch is NULL for T > 4");
+  if (cbx_rmsnorm(res, nullptr, norm_w, h_scratch, T, eps, stream)) return -1;
+  return gemm_bf16_tc(h_scratch, Whead, logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, (cudaStream_t)stream, sc);
+}
 extern "C" int cbx_layer_qkv(const void* res, const void* ln_w, const void* Wqkv, const void* cos_sin,
                              const int32_t* pos, const int64_t* slot, void* qkv, void* kv_layer, void* h_scratch,
                              int T, float eps, void* stream) {
-  if (T <= 0) return 0;
-  cudaStream_t s = (cudaStream_t)stream;
-  if (T <= 4) return gemv_qkv_rope(res, ln_w, Wqkv, cos_sin, pos, slot, qkv, kv_layer, T, eps, s);
-  CBX_REQUIRE(h_scratch != nullptr, "cbx_layer_qkv: h_scratch is NULL for T > 4");
-  if (cbx_rmsnorm(res, nullptr, ln_w, h_scratch, T, eps, stream)) return -1;
-  return gemm_qkv_rope(h_scratch, Wqkv, qkv, cos_sin, pos, slot, kv_layer, T, s);
+  return layer_qkv(res, ln_w, Wqkv, nullptr, cos_sin, pos, slot, qkv, kv_layer, h_scratch, T, eps, stream);
 }
 extern "C" int cbx_linear_residual(const void* x, const void* W, void* res, int T, int K, void* stream) {
-  if (T <= 0) return 0;
-  CBX_REQUIRE(K == 1024 || K == 4096, "cbx_linear_residual: K=%d unsupported", K);
-  if (T <= 4) return gemv_residual(x, W, res, T, K, (cudaStream_t)stream);
-  return gemm_residual(x, W, res, T, 1024, K, (cudaStream_t)stream);
+  return linear_residual(x, W, nullptr, res, T, K, stream);
 }
 extern "C" int cbx_linear_partials(const void* x, const void* W, void* partials, int T, int K, int splits, void* stream) {
   if (T <= 0) return 0;
@@ -186,20 +221,62 @@ extern "C" int cbx_linear_partials(const void* x, const void* W, void* partials,
 }
 extern "C" int cbx_layer_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, void* h_scratch, int T,
                                  float eps, void* stream) {
-  if (T <= 0) return 0;
-  if (T <= 4) return gemv_norm_gate_up(res, ln_w, Wgu, act, T, eps, (cudaStream_t)stream);
-  CBX_REQUIRE(h_scratch != nullptr, "cbx_layer_gate_up: h_scratch is NULL for T > 4");
-  if (cbx_rmsnorm(res, nullptr, ln_w, h_scratch, T, eps, stream)) return -1;
-  return gemm_bf16_tc(h_scratch, Wgu, act, T, 8192, 1024, 4096, 1, (cudaStream_t)stream);
+  return layer_gate_up(res, ln_w, Wgu, nullptr, act, h_scratch, T, eps, stream);
 }
 extern "C" int cbx_head_logits(const void* res, const void* norm_w, const void* Whead, void* logits, void* h_scratch,
                                int T, float eps, void* stream) {
+  return head_logits(res, norm_w, Whead, nullptr, logits, h_scratch, T, eps, stream);
+}
+// ---- the same pieces over FP8-e4m3 weights (W8 = e4m3 bytes, wscale = fp32 per output feature, padded to a
+// multiple of 128 entries; gate/up scales in PACKED row order)
+extern "C" int cbx_layer_qkv_fp8w(const void* res, const void* ln_w, const void* Wqkv8, const float* wscale,
+                                  const void* cos_sin, const int32_t* pos, const int64_t* slot, void* qkv, void* kv_layer,
+                                  void* h_scratch, int T, float eps, void* stream) {
+  CBX_REQUIRE(wscale != nullptr, "cbx_layer_qkv_fp8w: NULL scale");
+  return layer_qkv(res, ln_w, Wqkv8, wscale, cos_sin, pos, slot, qkv, kv_layer, h_scratch, T, eps, stream);
+}
+extern "C" int cbx_linear_residual_fp8w(const void* x, const void* W8, const float* wscale, void* res, int T, int K,
+                                        void* stream) {
+  CBX_REQUIRE(wscale != nullptr, "cbx_linear_residual_fp8w: NULL scale");
+  return linear_residual(x, W8, wscale, res, T, K, stream);
+}
+extern "C" int cbx_linear_partials_fp8w(const void* x, const void* W8, const float* wscale, void* partials, int T, int K,
+                                        int splits, void* stream) {
+  CBX_REQUIRE(wscale != nullptr, "cbx_linear_partials_fp8w: NULL scale");
   if (T <= 0) return 0;
-  if (T <= 4)
-    return gemv_norm_head(res, norm_w, Whead, logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD, eps, (cudaStream_t)stream);
-  CBX_REQUIRE(h_scratch != nullptr, "cbx_head_logits: h_scratch is NULL for T > 4");
-  if (cbx_rmsnorm(res, nullptr, norm_w, h_scratch, T, eps, stream)) return -1;
-  return gemm_bf16_tc(h_scratch, Whead, logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, (cudaStream_t)stream);
+  return gemm_partials(x, W8, partials, T, 1024, K, splits, (cudaStream_t)stream, wscale);
+}
+extern "C" int cbx_layer_gate_up_fp8w(const void* res, const void* ln_w, const void* Wgu8, const float* wscale, void* act,
+                                      void* h_scratch, int T, float eps, void* stream) {
+  CBX_REQUIRE(wscale != nullptr, "cbx_layer_gate_up_fp8w: NULL scale");
+  return layer_gate_up(res, ln_w, Wgu8, wscale, act, h_scratch, T, eps, stream);
+}
+extern "C" int cbx_head_logits_fp8w(const void* res, const void* norm_w, const void* Whead8, const float* wscale,
+                                    void* logits, void* h_scratch, int T, float eps, void* stream) {
+  CBX_REQUIRE(wscale != nullptr, "cbx_head_logits_fp8w: NULL scale");
+  return head_logits(res, norm_w, Whead8, wscale, logits, h_scratch, T, eps, stream);
+}
+// Switch a created engine to FP8-e4m3 projection weights (cbx_quantize_fp8_rows output).  Embeddings, norms,
+// KV cache, activations and the sampler are unchanged (bf16 / fp32).  Graphs captured before the switch are dropped.
+extern "C" int cbx_engine_set_fp8_weights(cbx_engine* e, const cbx_fp8_weights* f) {
+  CBX_REQUIRE(e != nullptr && f != nullptr, "cbx_engine_set_fp8_weights: NULL argument");
+  CBX_REQUIRE(f->n_layers == e->w.n_layers, "cbx_engine_set_fp8_weights: %d layers, engine has %d", f->n_layers, e->w.n_layers);
+  const int L = f->n_layers;
+  for (int i = 0; i < L; ++i)
+    CBX_REQUIRE(f->wqkv[i] && f->wo[i] && f->wgu[i] && f->wd[i] && f->sqkv[i] && f->so[i] && f->sgu[i] && f->sd[i],
+                "cbx_engine_set_fp8_weights: NULL pointer in layer %d", i);
+  CBX_REQUIRE(f->speech_head && f->shead, "cbx_engine_set_fp8_weights: NULL head");
+  e->wqkv.assign(f->wqkv, f->wqkv + L); e->wo.assign(f->wo, f->wo + L); e->wgu.assign(f->wgu, f->wgu + L);
+  e->wd.assign(f->wd, f->wd + L);
+  e->sqkv.assign(f->sqkv, f->sqkv + L); e->so.assign(f->so, f->so + L); e->sgu.assign(f->sgu, f->sgu + L);
+  e->sd.assign(f->sd, f->sd + L);
+  e->head = f->speech_head; e->shead = f->shead;
+  e->fp8 = true;
+  e->mega = false;                                     // the persistent-kernel experiment is bf16 only
+  e->l2_prefetch = false;
+  for (auto& g : e->graphs) cudaGraphExecDestroy(g.second.first);
+  e->graphs.clear();
+  return 0;
 }
 
 // Rows enter in buffer "res" (the residual stream starts as the embeddings, llama.py:316-320).
@@ -224,13 +301,13 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
     if (T <= 4) {
       // each kernel pulls a LATER kernel's weights into L2 (QKV -> Wo, attention -> Wgu, O -> Wd, gate_up -> next Wqkv)
       if (!(sk & 1) && gemv_qkv_rope(e->res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos, e->slot, e->qkv, kv, T, eps, s,
-                                     pf ? e->wo[li] : nullptr, (size_t)1024 * 1024 * 2)) return -1;
+                                     pf ? e->wo[li] : nullptr, (size_t)1024 * 1024 * 2, e->sqkv[li])) return -1;
       if (pf) attn_set_prefetch(e->wgu[li], (size_t)8192 * 1024 * 2);
     } else {
       if (pending ? cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln1[li], e->h, T, eps, s)
                   : cbx_rmsnorm(e->res, nullptr, e->ln1[li], e->h, T, eps, s)) return -1;
       pending = false;
-      if (!(sk & 1) && gemm_qkv_rope(e->h, e->wqkv[li], e->qkv, e->w.cos_sin, e->pos, e->slot, kv, T, s)) return -1;
+      if (!(sk & 1) && gemm_qkv_rope(e->h, e->wqkv[li], e->qkv, e->w.cos_sin, e->pos, e->slot, kv, T, s, e->sqkv[li])) return -1;
     }
     if (e->n_prefill_items > 0) {
       if (!(sk & 2) && cbx_paged_attn_prefill(e->qkv, kv, e->block_table, e->bt_stride, e->prefill_items, e->n_prefill_items,
@@ -239,22 +316,23 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                                                  e->attn_scratch, e->attn_counters, T, max_kv_len, have_plan, s)) return -1;
     if (T <= 4) {
       const bool last = li + 1 == e->w.n_layers;
-      if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s, pf ? e->wd[li] : nullptr, (size_t)1024 * 4096 * 2)) return -1;
+      if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s, pf ? e->wd[li] : nullptr, (size_t)1024 * 4096 * 2,
+                                     e->so[li])) return -1;
       if (!(sk & 8) && gemv_norm_gate_up(e->res, e->ln2[li], e->wgu[li], e->act, T, eps, s,
                                          pf ? (last ? e->w.speech_head : e->wqkv[li + 1]) : nullptr,
-                                         last ? (size_t)CBX_SPEECH_VOCAB * 1024 * 2 : (size_t)3072 * 1024 * 2)) return -1;
-      if (!(sk & 16) && gemv_residual(e->act, e->wd[li], e->res, T, 4096, s)) return -1;
+                                         last ? (size_t)CBX_SPEECH_VOCAB * 1024 * 2 : (size_t)3072 * 1024 * 2, e->sgu[li])) return -1;
+      if (!(sk & 16) && gemv_residual(e->act, e->wd[li], e->res, T, 4096, s, nullptr, 0, e->sd[li])) return -1;
     } else if (splits > 1) {
-      if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s)) return -1;
+      if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s, e->so[li])) return -1;
       if (cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
-      if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s)) return -1;
-      if (!(sk & 16) && gemm_partials(e->act, e->wd[li], e->part, T, 1024, 4096, splits, s)) return -1;
+      if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s, e->sgu[li])) return -1;
+      if (!(sk & 16) && gemm_partials(e->act, e->wd[li], e->part, T, 1024, 4096, splits, s, e->sd[li])) return -1;
       pending = true;
     } else {
-      if (!(sk & 4) && gemm_residual(e->attn, e->wo[li], e->res, T, 1024, 1024, s)) return -1;
+      if (!(sk & 4) && gemm_residual(e->attn, e->wo[li], e->res, T, 1024, 1024, s, e->so[li])) return -1;
       if (cbx_rmsnorm(e->res, nullptr, e->ln2[li], e->h, T, eps, s)) return -1;
-      if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s)) return -1;
-      if (!(sk & 16) && gemm_residual(e->act, e->wd[li], e->res, T, 1024, 4096, s)) return -1;
+      if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s, e->sgu[li])) return -1;
+      if (!(sk & 16) && gemm_residual(e->act, e->wd[li], e->res, T, 1024, 4096, s, e->sd[li])) return -1;
     }
     if (e->trace)
       cudaMemcpyAsync(e->trace + (size_t)li * T * CBX_HIDDEN, e->res, (size_t)T * CBX_HIDDEN * 2,
@@ -296,8 +374,8 @@ extern "C" int cbx_engine_sample(cbx_engine* e, int B, void* stream) {
   CBX_REQUIRE(ce == cudaSuccess, "gather_rows launch failed: %s", cudaGetErrorString(ce));
   count_launch();
   const int T = 2 * B;
-  if (T <= 4) { if (gemv_bf16(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1; }
-  else if (gemm_bf16_tc(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1;
+  if (T <= 4) { if (gemv_bf16(e->hs, e->head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s, e->shead)) return -1; }
+  else if (gemm_bf16_tc(e->hs, e->head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s, e->shead)) return -1;
   // the sampler also stages the next decode step's embeddings / positions / slots
   return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s);
 }
@@ -313,8 +391,8 @@ extern "C" int cbx_engine_sample_subset(cbx_engine* e, int B, int n_sub, const i
                               (uint4*)e->hs);
   CBX_REQUIRE(ce == cudaSuccess, "gather_rows launch failed: %s", cudaGetErrorString(ce));
   count_launch();
-  if (T <= 4) { if (gemv_bf16(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1; }
-  else if (gemm_bf16_tc(e->hs, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1;
+  if (T <= 4) { if (gemv_bf16(e->hs, e->head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s, e->shead)) return -1; }
+  else if (gemm_bf16_tc(e->hs, e->head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s, e->shead)) return -1;
   return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s, pair_map, n_sub);
 }
 
@@ -342,9 +420,9 @@ static int decode_step(cbx_engine* e, int B, int max_kv_len, cudaStream_t s) {
   }
   if (forward_layers(e, T, max_kv_len, s, false)) return -1;
   if (T <= 4) {                                         // final norm fused into the head GEMV
-    if (gemv_norm_head(e->res, e->w.norm, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD,
-                       e->w.rms_eps, s)) return -1;
-  } else if (gemm_bf16_tc(e->h, e->w.speech_head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s)) return -1;
+    if (gemv_norm_head(e->res, e->w.norm, e->head, e->logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD,
+                       e->w.rms_eps, s, e->shead)) return -1;
+  } else if (gemm_bf16_tc(e->h, e->head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s, e->shead)) return -1;
   return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s);
 }
 

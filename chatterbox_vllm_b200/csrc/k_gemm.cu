@@ -16,7 +16,17 @@
 // Programmatic dependent launch: the producer issues the WEIGHT tiles of the first kStages
 // k-blocks before griddepcontrol.wait, so the weight stream overlaps the previous kernel's tail;
 // activation tiles follow after the wait.
+//
+// W8 = true (weight-only FP8-e4m3, per-output-channel fp32 scale): tcgen05.mma kind::f16 takes no
+// 8-bit B operand next to a bf16 A, so the weight tile travels HBM -> L2 -> shared memory as BYTES
+// (half the ingest, which is what bounds the decode GEMMs) and is widened on chip: TMA drops the
+// BN x 64-byte e4m3 tile into a linear staging buffer, warps 4-7 (idle until the epilogue) convert it
+// to bf16 (exact) straight into the SWIZZLE_128B operand layout, fence.proxy.async, and arrive on a
+// per-stage "converted" barrier the MMA issuer waits on.  Weights do not depend on the previous
+// kernel, so the first ring fill is loaded AND converted before griddepcontrol.wait.  The scale
+// multiplies the fp32 accumulator in the epilogue, before the first bf16 rounding point.
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -52,12 +62,13 @@ __device__ __forceinline__ void prof_stamp(int id, int k) {
 
 // CN = 2: the CTA pair of a cluster issues ONE tcgen05.mma.cta_group::2 (M = 256: 128 rows per CTA) per
 // K = 16 step; each CTA stages its own 128 activation rows and only HALF of the BN weight rows.
-template <int BN, int CN = 1>
+template <int BN, int CN = 1, bool W8 = false>
 struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN / CN * BK * 2;
-  static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = kStageBytes > 24576 ? 6 : 8;
+  static constexpr int kB8Bytes = W8 ? BN * BK : 0;     // e4m3 staging tile (linear rows of 64 bytes)
+  static constexpr int kStageBytes = kABytes + kBBytes + kB8Bytes;
+  static constexpr int kStages = W8 ? (BN > 64 ? 5 : 6) : (kStageBytes > 24576 ? 6 : 8);
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   // Throughput configuration for grids of many tiles (prefill): a ring shallow enough that TWO CTAs
   // share an SM, so one CTA's epilogue (TMEM -> registers -> global) runs under the other's MMAs.
@@ -76,18 +87,53 @@ struct EpiArgs {               // EPI 2 only
 // weight bytes per output element halve.  Both producers signal the LEADER's full barrier (peer bit of
 // the barrier address cleared, .cta_group::2 copy), the leader's elected thread issues the MMAs and
 // multicasts its commits to both CTAs' empty / accumulator barriers, each CTA drains its own TMEM.
-template <int BN, int EPI, int CN>
+// 16 e4m3 bytes -> 16 bf16 (exact) as two 16-byte operand chunks
+__device__ __forceinline__ void e4m3x16_to_bf16(const uint4& v, uint4& lo8, uint4& hi8) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  uint32_t o[8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint32_t h0, h1;
+    asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\t"
+        "cvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
+        : "=r"(h0), "=r"(h1) : "r"(w[i]));
+    const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&h0));
+    const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&h1));
+    o[2 * i] = pack_bf16(f0.x, f0.y);
+    o[2 * i + 1] = pack_bf16(f1.x, f1.y);
+  }
+  lo8 = make_uint4(o[0], o[1], o[2], o[3]);
+  hi8 = make_uint4(o[4], o[5], o[6], o[7]);
+}
+// r[i] *= scale[i], i < 32 (scale 16-byte aligned; the same 32 values for every row of the tile)
+__device__ __forceinline__ void scale32(uint32_t (&r)[32], const float* __restrict__ sc) {
+  const float4* sp = reinterpret_cast<const float4*>(sc);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 v = __ldg(sp + i);
+    r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) * v.x);
+    r[4 * i + 1] = __float_as_uint(__uint_as_float(r[4 * i + 1]) * v.y);
+    r[4 * i + 2] = __float_as_uint(__uint_as_float(r[4 * i + 2]) * v.z);
+    r[4 * i + 3] = __float_as_uint(__uint_as_float(r[4 * i + 3]) * v.w);
+  }
+}
+
+template <int BN, int EPI, int CN, bool W8 = false>
 __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                               const __grid_constant__ CUtensorMap tma_b,
                                                               bf16* __restrict__ y, int M, int N, int K, int ldy,
-                                                              const EpiArgs ea, const int n_stages) {
-  using C = Cfg<BN, CN>;
+                                                              const EpiArgs ea, const int n_stages,
+                                                              const float* __restrict__ wscale) {
+  using C = Cfg<BN, CN, W8>;
+  static_assert(!W8 || CN == 1, "the FP8-weight form uses single-CTA tiles");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + n_stages * C::kStageBytes);
   uint64_t* empty = full + n_stages;
   uint64_t* tmem_full = empty + n_stages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* fullb = tmem_full + 2;                     // W8: e4m3 staging tile landed
+  uint64_t* conv = fullb + n_stages;                   // W8: bf16 operand tile written (4 converter warps)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // pair mode: the two row tiles of a cluster are neighbours along grid.x (cluster dims (2, 1, 1))
@@ -107,6 +153,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    if (W8) for (int s = 0; s < n_stages; ++s) { mbar_init(&fullb[s], 1); mbar_init(&conv[s], 4); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -133,6 +180,29 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
       const int nb = n0 + (int)crank * (BN / CN);       // this CTA's weight rows of the tile
       // weights of the first ring fill do not depend on the previous kernel
       const int n_pre = n_kb < n_stages ? n_kb : n_stages;
+      if (W8) {
+        // bytes of the e4m3 tile land on fullb (the converters' barrier), activations on full
+        constexpr int kB8Off = C::kABytes + C::kBBytes;
+        for (int kb = 0; kb < n_pre; ++kb) {
+          mbar_arrive_expect_tx(&fullb[kb], C::kB8Bytes);
+          tma_load_2d(smem + kb * C::kStageBytes + kB8Off, &tma_b, kc(kb) * BK, nb, &fullb[kb]);
+        }
+        pdl_wait();
+        PROF(2);
+        for (int kb = 0; kb < n_pre; ++kb) {
+          mbar_arrive_expect_tx(&full[kb], C::kABytes);
+          tma_load_2d(smem + kb * C::kStageBytes, &tma_a, kc(kb) * BK, m0, &full[kb]);
+        }
+        for (int kb = n_pre; kb < n_kb; ++kb) {
+          const int s = kb % n_stages, ph = (kb / n_stages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* sa = smem + s * C::kStageBytes;
+          mbar_arrive_expect_tx(&fullb[s], C::kB8Bytes);
+          tma_load_2d(sa + kB8Off, &tma_b, kc(kb) * BK, nb, &fullb[s]);
+          mbar_arrive_expect_tx(&full[s], C::kABytes);
+          tma_load_2d(sa, &tma_a, kc(kb) * BK, m0, &full[s]);
+        }
+      } else {
       for (int kb = 0; kb < n_pre; ++kb) {
         if (crank == 0) mbar_arrive_expect_tx(&full[kb], CN * C::kStageBytes);
         load(smem + kb * C::kStageBytes + C::kABytes, &tma_b, kc(kb) * BK, nb, &full[kb]);
@@ -149,6 +219,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
         load(sa, &tma_a, kc(kb) * BK, m0, &full[s]);
         load(sa + C::kABytes, &tma_b, kc(kb) * BK, nb, &full[s]);
       }
+      }
     } else {
       pdl_wait();
     }
@@ -159,6 +230,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
       for (int kb = 0; kb < n_kb; ++kb) {
         const int s = kb % n_stages, ph = (kb / n_stages) & 1;
         mbar_wait(&full[s], ph);
+        if (W8) mbar_wait(&conv[s], ph);
         if (kb == 0) PROF(3);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + s * C::kStageBytes);
@@ -177,6 +249,33 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
     }
   } else if (warp < 4) {
     pdl_wait();
+  } else if (W8) {
+    // ---- converters (warps 4-7): e4m3 staging tile -> bf16 operand tile in the SWIZZLE_128B layout.
+    // Thread t takes 16-byte chunk c = i*128 + t of the tile: weight row c >> 2, bytes (c & 3)*16..+16 of
+    // its 64-element k-block, i.e. bf16 chunks 2*(c & 3) and 2*(c & 3) + 1 of the 128-byte operand row,
+    // stored at chunk ^ (row & 7) (TMA's 128-byte swizzle; stage bases are 1024-aligned).
+    const int t = threadIdx.x - 128;
+    constexpr int kB8Off = C::kABytes + C::kBBytes;
+    for (int kb = 0; kb < n_kb; ++kb) {
+      const int s = kb % n_stages, ph = (kb / n_stages) & 1;
+      if (kb >= n_stages) mbar_wait(&empty[s], ph ^ 1);   // the MMAs that read this operand tile are done
+      mbar_wait(&fullb[s], ph);
+      uint8_t* st = smem + s * C::kStageBytes;
+      const uint4* src = reinterpret_cast<const uint4*>(st + kB8Off);
+      uint8_t* dstb = st + C::kABytes;
+#pragma unroll
+      for (int i = 0; i < BN * 4 / 128; ++i) {
+        const int c = i * 128 + t, row = c >> 2, ch = (c & 3) * 2;
+        uint4 lo8, hi8;
+        e4m3x16_to_bf16(src[c], lo8, hi8);
+        uint8_t* rowp = dstb + row * 128;
+        *reinterpret_cast<uint4*>(rowp + ((ch ^ (row & 7)) << 4)) = lo8;
+        *reinterpret_cast<uint4*>(rowp + (((ch + 1) ^ (row & 7)) << 4)) = hi8;
+      }
+      fence_proxy_async();                              // generic-proxy writes -> visible to tcgen05.mma
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&conv[s]);
+    }
   }
   // Epilogue.  A warp may only read the TMEM lane quarter (warp % 4); with one warp per quarter the
   // epilogue is a single warp per SM sub-partition issuing dependent math (measured: SiLU epilogue
@@ -199,6 +298,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + hh * 64, r0);
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + hh * 64 + 32, r1);
       tmem_ld_wait();
+      if (W8) { scale32(r0, wscale + n0 + hh * 64); scale32(r1, wscale + n0 + hh * 64 + 32); }
       if (row < M) {
         const int head48 = (n0 >> 6) + hh, which = head48 >> 4, h = head48 & 15;
         uint32_t o1[16], o2[16];
@@ -256,6 +356,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + cb * 32, r);
       tmem_ld_wait();
       const int col = n0 + cb * 32;
+      if (W8 && col < N) scale32(r, wscale + col);        // wscale is padded to a multiple of 128 entries
       if (row < M && col < N) {
         if (EPI == 1) {
           // packed gate/up: columns [0,16) gate, [16,32) up of the same 16 features
@@ -361,6 +462,36 @@ int make_map(CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) 
   return 0;
 }
 
+// 2-D row-major e4m3 [rows, cols] weight tensor as bytes, box = {64 bytes, box_rows}, no swizzle (the
+// converter warps re-lay it out as bf16).
+int make_map_u8(CUtensorMap* m, const void* ptr, int rows, int cols, int box_rows) {
+  typedef std::tuple<const void*, int, int, int> Key;
+  static std::map<Key, CUtensorMap> cache;
+  Key key(ptr, rows, cols, box_rows);
+  auto itr = cache.find(key);
+  if (itr != cache.end()) { *m = itr->second; return 0; }
+  EncodeTiledFn enc = get_encode();
+  CBX_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CBX_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (u8) failed (%d) rows=%d cols=%d", (int)r, rows, cols);
+  if (cache.size() > 4096) cache.clear();
+  cache[key] = *m;
+  return 0;
+}
+
+template <int BN, int EPI>
+int set_attr8() {
+  cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<BN, 1, true>::kSmem);
+  CBX_REQUIRE(e == cudaSuccess, "gemm (fp8w) smem attribute: %s", cudaGetErrorString(e));
+  return 0;
+}
 template <int BN, int EPI, int CN>
 int set_attr() {
   cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, CN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, CN>::kSmem);
@@ -383,12 +514,30 @@ int init_gemm() {
   if (set_attr<64, 0, 1>() || set_attr<64, 1, 1>() || set_attr<128, 0, 1>() || set_attr<128, 1, 1>() || set_attr<64, 2, 1>() ||
       set_attr<64, 3, 1>() || set_attr<128, 3, 1>() || set_attr<64, 4, 1>() || set_attr<128, 2, 1>()) return -1;
   if (set_attr_pairs<0>() || set_attr_pairs<1>() || set_attr_pairs<2>() || set_attr_pairs<3>() || set_attr_pairs<4>()) return -1;
+  if (set_attr8<64, 0>() || set_attr8<64, 1>() || set_attr8<64, 2>() || set_attr8<64, 3>() || set_attr8<64, 4>() ||
+      set_attr8<128, 0>() || set_attr8<128, 1>() || set_attr8<128, 2>() || set_attr8<128, 3>()) return -1;
   CBX_REQUIRE(get_encode() != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   done = true;
   return 0;
 }
 }  // namespace cbx
 namespace {
+// FP8-weight form: W is [N, K] e4m3 bytes, wscale [>= round_up(N, 128)] fp32.  Deep ring, one CTA per SM.
+template <int BN, int EPI>
+int launch8(const void* x, const void* W, const float* wscale, void* y, int M, int N, int K, int ldy, cudaStream_t s,
+            const EpiArgs& ea = EpiArgs(), int splits = 1) {
+  using C = Cfg<BN, 1, true>;
+  if (cbx::init_gemm()) return -1;
+  const int n_tiles = (N + BN - 1) / BN, m_tiles = (M + BM - 1) / BM;
+  CUtensorMap ma, mb;
+  if (make_map(&ma, x, M, K, BM)) return -1;
+  if (make_map_u8(&mb, W, N, K, BN)) return -1;
+  cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI, 1, true>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), C::kSmem, s, ma, mb,
+                             (bf16*)y, M, N, K, ldy, ea, (int)C::kStages, wscale);
+  CBX_REQUIRE(e == cudaSuccess, "gemm_tc (fp8w) launch failed: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
 template <int BN, int EPI>
 int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, cudaStream_t s,
            const EpiArgs& ea = EpiArgs(), int splits = 1) {
@@ -410,7 +559,7 @@ int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, 
   const EpiArgs& eal = ea;
 #endif
   cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI, 1>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), smem_bytes, s, ma, mb,
-                             (bf16*)y, M, N, K, ldy, eal, n_stages);
+                             (bf16*)y, M, N, K, ldy, eal, n_stages, (const float*)nullptr);
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
@@ -432,7 +581,7 @@ int launch_pair(const void* x, const void* W, void* y, int M, int N, int K, int 
   const int n_stages = shallow ? C::kStagesShallow : C::kStages;
   const int smem_bytes = shallow ? C::kSmemShallow : C::kSmem;
   cudaError_t e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(m_tiles, n_tiles, splits), dim3(kThreads), smem_bytes, s, 2,
-                                     ma, mb, (bf16*)y, M, N, K, ldy, ea, n_stages);
+                                     ma, mb, (bf16*)y, M, N, K, ldy, ea, n_stages, (const float*)nullptr);
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc (pair) launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
@@ -460,7 +609,7 @@ int launch_pair_w(int w, const void* x, const void* W, void* y, int M, int N, in
 
 namespace cbx {
 int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int ldy, int epilogue,
-                 cudaStream_t s) {
+                 cudaStream_t s, const float* wscale) {
   CBX_REQUIRE(M >= 1 && K % BK == 0 && K >= BK, "gemm_tc: bad shape M=%d K=%d", M, K);
   CBX_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0,
               "gemm_tc: operands must be 16-byte aligned");
@@ -471,6 +620,10 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
   // path are bound by L2->SM bytes, which a 128 x 128 tile halves per output element.
   bool narrow = (int64_t)m_tiles * ((N + 127) / 128) < 100;
   if (const char* v = getenv("CBX_GEMM_BN")) narrow = atoi(v) == 64;      // tuning aid
+  if (wscale) {
+    if (epilogue == 1) return narrow ? launch8<64, 1>(x, W, wscale, y, M, N, K, ldy, s) : launch8<128, 1>(x, W, wscale, y, M, N, K, ldy, s);
+    return narrow ? launch8<64, 0>(x, W, wscale, y, M, N, K, ldy, s) : launch8<128, 0>(x, W, wscale, y, M, N, K, ldy, s);
+  }
   if (const int w = pair_width(M, 4096))
     return epilogue == 1 ? launch_pair_w<1>(w, x, W, y, M, N, K, ldy, s) : launch_pair_w<0>(w, x, W, y, M, N, K, ldy, s);
   if (epilogue == 1) return narrow ? launch<64, 1>(x, W, y, M, N, K, ldy, s) : launch<128, 1>(x, W, y, M, N, K, ldy, s);
@@ -478,27 +631,37 @@ int gemm_bf16_tc(const void* x, const void* W, void* y, int M, int N, int K, int
 }
 // EPI 2: y = qkv buffer [M, 3072]; q rotated into its first 1024 columns, k/v into the KV pages.
 int gemm_qkv_rope(const void* h, const void* Wqkv, void* qkv, const void* cos_sin, const int32_t* pos,
-                  const int64_t* slot, void* kv_layer, int M, cudaStream_t s) {
+                  const int64_t* slot, void* kv_layer, int M, cudaStream_t s, const float* wscale) {
   EpiArgs ea = {(const bf16*)cos_sin, pos, slot, (uint8_t*)kv_layer};
+  if (wscale) {
+    if ((M + BM - 1) / BM * 24 >= 2 * 148) return launch8<128, 2>(h, Wqkv, wscale, qkv, M, 3072, 1024, 3072, s, ea);
+    return launch8<64, 2>(h, Wqkv, wscale, qkv, M, 3072, 1024, 3072, s, ea);
+  }
   if (const int w = pair_width(M, 8192)) return launch_pair_w<2>(w, h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   // prefill-sized M: 128-wide tiles (two heads per tile) halve the activation re-reads
   if ((M + BM - 1) / BM * 24 >= 2 * 148) return launch<128, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   return launch<64, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
 }
 // EPI 3: res[M, N] = bf16(bf16(x·W^T) + res), N % 32 == 0.
-int gemm_residual(const void* x, const void* W, void* res, int M, int N, int K, cudaStream_t s) {
+int gemm_residual(const void* x, const void* W, void* res, int M, int N, int K, cudaStream_t s, const float* wscale) {
   CBX_REQUIRE(N % 128 == 0 && K % BK == 0, "gemm_residual: bad shape N=%d K=%d", N, K);
+  if (wscale) {
+    const bool narrow8 = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
+    return narrow8 ? launch8<64, 3>(x, W, wscale, res, M, N, K, N, s) : launch8<128, 3>(x, W, wscale, res, M, N, K, N, s);
+  }
   if (const int w = pair_width(M, 4096)) return launch_pair_w<3>(w, x, W, res, M, N, K, N, s);
   const bool narrow = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
   return narrow ? launch<64, 3>(x, W, res, M, N, K, N, s) : launch<128, 3>(x, W, res, M, N, K, N, s);
 }
 // EPI 4: part[splits][M][N] fp32 = per-K-slice partial products (no rounding); N % 64 == 0.
-int gemm_partials(const void* x, const void* W, void* part, int M, int N, int K, int splits, cudaStream_t s) {
+int gemm_partials(const void* x, const void* W, void* part, int M, int N, int K, int splits, cudaStream_t s,
+                  const float* wscale) {
   CBX_REQUIRE(N % 64 == 0 && splits >= 1 && K % (BK * splits) == 0, "gemm_partials: bad shape N=%d K=%d splits=%d", N, K, splits);
+  if (wscale) return launch8<64, 4>(x, W, wscale, part, M, N, K, N, s, EpiArgs(), splits);
   if (const int w = pair_width(M, 4096)) return launch_pair_w<4>(w, x, W, part, M, N, K, N, s, EpiArgs(), splits);
   return launch<64, 4>(x, W, part, M, N, K, N, s, EpiArgs(), splits);
 }
-int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t);
+int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
 }  // namespace cbx
 
 extern "C" int cbx_linear(const void* x, const void* W, void* y, int T, int N, int K, int ldy, int epilogue,
@@ -508,7 +671,19 @@ extern "C" int cbx_linear(const void* x, const void* W, void* y, int T, int N, i
   const bool gemv_ok = T <= 4 && (K == 1024 || (K == 4096 && epilogue == 0));
   if (path == 1) CBX_REQUIRE(gemv_ok, "cbx_linear: GEMV path needs T <= 4 and K in {1024,4096}");
   if (path == 1 || (path == 0 && gemv_ok)) return cbx::gemv_bf16(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream);
-  return cbx::gemm_bf16_tc(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream);
+  return cbx::gemm_bf16_tc(x, W, y, T, N, K, ldy, epilogue, (cudaStream_t)stream, nullptr);
+}
+
+// FP8-e4m3 weights W8 [N, K] + fp32 scale per output feature (wscale holds >= round_up(N, 128) entries).
+extern "C" int cbx_linear_fp8w(const void* x, const void* W8, const float* wscale, void* y, int T, int N, int K, int ldy,
+                               int epilogue, int path, void* stream) {
+  CBX_REQUIRE(T >= 1 && wscale != nullptr, "cbx_linear_fp8w: T < 1 or NULL scale");
+  CBX_REQUIRE(path >= 0 && path <= 2, "cbx_linear_fp8w: bad path %d", path);
+  const bool gemv_ok = T <= 4 && (K == 1024 || (K == 4096 && epilogue == 0));
+  if (path == 1) CBX_REQUIRE(gemv_ok, "cbx_linear_fp8w: GEMV path needs T <= 4 and K in {1024,4096}");
+  if (path == 1 || (path == 0 && gemv_ok))
+    return cbx::gemv_bf16(x, W8, y, T, N, K, ldy, epilogue, (cudaStream_t)stream, wscale);
+  return cbx::gemm_bf16_tc(x, W8, y, T, N, K, ldy, epilogue, (cudaStream_t)stream, wscale);
 }
 
 #ifdef CBX_GEMM_PROF

@@ -14,6 +14,14 @@
 // so the weight stream of kernel n+1 overlaps the tail of kernel n (programmatic dependent
 // launch).  The T x 1024 activation rows are normalised redundantly by every CTA (2-8 KB from
 // L2) — cheaper than a separate launch.
+//
+// W8 = true: FP8-e4m3 weights with one fp32 scale per output feature (the optional weight-only
+// FP8 path of the north star).  The stream halves (2 KB per warp per item); bytes are widened with
+// cvt.rn.f16x2.e4m3x2 in registers, accumulation stays fp32, and the scale multiplies the finished
+// dot product before the first bf16 rounding point, so y = bf16((x . q) * s) == x . (q * s) up to
+// fp32 summation order — exactly the oracle's "dequantised weights" chain.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 using namespace cbx;
@@ -25,7 +33,8 @@ enum { EPI_STORE = 0, EPI_SILU = 1, EPI_ROPE = 2, EPI_RES = 3 };
 struct GemvArgs {
   const bf16* x;          // PRO_COPY: [T, K] input rows;  PRO_NORM: residual stream [T, 1024]
   const bf16* ln_w;       // PRO_NORM: RMSNorm weight [1024]
-  const bf16* W;          // [N, K]
+  const void* W;          // [N, K] bf16, or e4m3 bytes when W8
+  const float* wscale;    // W8: [N] per-output-feature scale
   bf16* y;                // STORE/SILU: out [T, ldy];  RES: residual stream [T, 1024];  ROPE: qkv [T, 3072]
   const bf16* cos_sin;    // ROPE: [max_pos, 64] = cos(32) | sin(32)
   const int32_t* pos;     // ROPE: [T]
@@ -42,6 +51,21 @@ __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
   f[4] = bf_lo(v.z); f[5] = bf_hi(v.z); f[6] = bf_lo(v.w); f[7] = bf_hi(v.w);
 }
 
+// 16 e4m3 bytes -> 16 floats (exact: e4m3 is a subset of f16)
+__device__ __forceinline__ void unpack16_e4m3(const uint4& v, float (&f)[16]) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint32_t lo, hi;
+    asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\t"
+        "cvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
+        : "=r"(lo), "=r"(hi) : "r"(w[i]));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&lo));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    f[4 * i] = a.x; f[4 * i + 1] = a.y; f[4 * i + 2] = b.x; f[4 * i + 3] = b.y;
+  }
+}
+
 template <int EPI>
 __device__ __forceinline__ void item_rows(int item, int& ra, int& rb) {
   if (EPI == EPI_SILU)      { ra = (item >> 4) * 32 + (item & 15); rb = ra + 16; }   // packed gate/up
@@ -50,9 +74,11 @@ __device__ __forceinline__ void item_rows(int item, int& ra, int& rb) {
 }
 
 // TT = padded row count (1,2,4); KSEG = K / 1024 (1 or 4); NW = warps per CTA.
-template <int TT, int KSEG, int PRO, int EPI, int NW>
+template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
 __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a) {
   constexpr int K = KSEG * 1024;
+  constexpr int ES = W8 ? 1 : 2;                      // bytes per weight element
+  constexpr int NJ = W8 ? 2 : 4;                      // 128-bit loads per lane per 1024-element row segment
   constexpr int IPC = NW / KSEG;                      // items per CTA per round
   static_assert(NW % KSEG == 0, "warps must cover whole K-segment groups");
   static_assert(PRO == PRO_COPY || KSEG == 1, "norm prologue is over hidden = 1024");
@@ -68,14 +94,15 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
   // ---- weight prefetch of this warp's first item: independent of the previous kernel
   int item = blockIdx.x * IPC + warp / KSEG;
   const int stride = gridDim.x * IPC;
-  uint4 cur[2][4];
+  const uint8_t* Wb = reinterpret_cast<const uint8_t*>(a.W);
+  uint4 cur[2][NJ];
   if (item < n_items) {
     int ra, rb;
     item_rows<EPI>(item, ra, rb);
-    const uint4* wa = reinterpret_cast<const uint4*>(a.W + (size_t)ra * K + kseg * 1024) + lane;
-    const uint4* wb = reinterpret_cast<const uint4*>(a.W + (size_t)rb * K + kseg * 1024) + lane;
+    const uint4* wa = reinterpret_cast<const uint4*>(Wb + ((size_t)ra * K + kseg * 1024) * ES) + lane;
+    const uint4* wb = reinterpret_cast<const uint4*>(Wb + ((size_t)rb * K + kseg * 1024) * ES) + lane;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
+    for (int j = 0; j < NJ; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
   }
   l2_prefetch_slice(a.next_w, a.next_bytes);
   pdl_wait();
@@ -122,22 +149,43 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
   for (int base = blockIdx.x * IPC; base < n_items; base += stride) {
     item = base + warp / KSEG;
     const bool valid = item < n_items;
-    uint4 nxt[2][4];
+    uint4 nxt[2][NJ];
     const int nitem = item + stride;
     if (nitem < n_items) {
       int ra, rb;
       item_rows<EPI>(nitem, ra, rb);
-      const uint4* wa = reinterpret_cast<const uint4*>(a.W + (size_t)ra * K + kseg * 1024) + lane;
-      const uint4* wb = reinterpret_cast<const uint4*>(a.W + (size_t)rb * K + kseg * 1024) + lane;
+      const uint4* wa = reinterpret_cast<const uint4*>(Wb + ((size_t)ra * K + kseg * 1024) * ES) + lane;
+      const uint4* wb = reinterpret_cast<const uint4*>(Wb + ((size_t)rb * K + kseg * 1024) * ES) + lane;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) { nxt[0][j] = ld_stream(wa + j * 32); nxt[1][j] = ld_stream(wb + j * 32); }
+      for (int j = 0; j < NJ; ++j) { nxt[0][j] = ld_stream(wa + j * 32); nxt[1][j] = ld_stream(wb + j * 32); }
     }
     float acc[2][TT];
 #pragma unroll
     for (int t = 0; t < TT; ++t) acc[0][t] = acc[1][t] = 0.f;
-    if (valid) {
+    if (valid && W8) {
+      // lane's 16 bytes of load j are elements [j*512 + lane*16, +16) of the segment
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < NJ; ++j) {
+        float fa[16], fb[16];
+        unpack16_e4m3(cur[0][j], fa);
+        unpack16_e4m3(cur[1][j], fb);
+#pragma unroll
+        for (int t = 0; t < TT; ++t) {
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float fx[8];
+            unpack8(xs[t * (K / 8) + kseg * 128 + j * 64 + lane * 2 + c], fx);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              acc[0][t] = fmaf(fa[c * 8 + e], fx[e], acc[0][t]);
+              acc[1][t] = fmaf(fb[c * 8 + e], fx[e], acc[1][t]);
+            }
+          }
+        }
+      }
+    } else if (valid) {
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
         float fa[8], fb[8];
         unpack8(cur[0][j], fa);
         unpack8(cur[1][j], fb);
@@ -179,6 +227,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       float v0 = 0.f, v1 = 0.f;
 #pragma unroll
       for (int t = 0; t < TT; ++t) if (lane == t) { v0 = acc[0][t]; v1 = acc[1][t]; }
+      if (W8) { v0 *= a.wscale[ra]; v1 *= a.wscale[rb]; }
       if (lane < T) {
         const int t = lane;
         if (EPI == EPI_STORE) {
@@ -225,18 +274,23 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       }
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
+    for (int j = 0; j < NJ; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
   }
+}
+
+template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
+int launch_w(const GemvArgs& a, int grid, cudaStream_t s) {
+  constexpr int smem = TT * KSEG * 1024 * 2 + (KSEG > 1 ? NW * 2 * TT * 4 : 0);
+  static_assert(smem <= 48 * 1024, "x tile must fit the default dynamic smem limit");
+  cudaError_t e = launch_pdl(gemv_fused_kernel<TT, KSEG, PRO, EPI, NW, W8>, dim3(grid), dim3(NW * 32), smem, s, a);
+  if (e != cudaSuccess) { set_error("gemv launch failed: %s", cudaGetErrorString(e)); return -2; }
+  count_launch();
+  return 0;
 }
 
 template <int TT, int KSEG, int PRO, int EPI, int NW>
 int launch(const GemvArgs& a, int grid, cudaStream_t s) {
-  constexpr int smem = TT * KSEG * 1024 * 2 + (KSEG > 1 ? NW * 2 * TT * 4 : 0);
-  static_assert(smem <= 48 * 1024, "x tile must fit the default dynamic smem limit");
-  cudaError_t e = launch_pdl(gemv_fused_kernel<TT, KSEG, PRO, EPI, NW>, dim3(grid), dim3(NW * 32), smem, s, a);
-  if (e != cudaSuccess) { set_error("gemv launch failed: %s", cudaGetErrorString(e)); return -2; }
-  count_launch();
-  return 0;
+  return a.wscale ? launch_w<TT, KSEG, PRO, EPI, NW, true>(a, grid, s) : launch_w<TT, KSEG, PRO, EPI, NW, false>(a, grid, s);
 }
 
 template <int KSEG, int PRO, int EPI, int NW>
@@ -255,12 +309,13 @@ inline int grid_for(int n_items, int items_per_cta) {
 
 namespace cbx {
 // Plain y = x·W^T (epilogue 0) or SiLU(gate)·up (epilogue 1).  T <= 4, K in {1024, 4096}.
-int gemv_bf16(const void* x, const void* W, void* y, int T, int N, int K, int ldy, int epilogue, cudaStream_t s) {
+int gemv_bf16(const void* x, const void* W, void* y, int T, int N, int K, int ldy, int epilogue, cudaStream_t s,
+              const float* wscale) {
   CBX_REQUIRE(T >= 1 && T <= 4, "gemv: T=%d not in [1,4]", T);
   CBX_REQUIRE(K == 1024 || K == 4096, "gemv: K=%d unsupported", K);
   CBX_REQUIRE(N % 2 == 0 && (epilogue == 0 || N % 32 == 0), "gemv: N=%d unsupported", N);
   GemvArgs a = {};
-  a.x = (const bf16*)x; a.W = (const bf16*)W; a.y = (bf16*)y; a.T = T; a.N = N; a.ldy = ldy;
+  a.x = (const bf16*)x; a.W = W; a.wscale = wscale; a.y = (bf16*)y; a.T = T; a.N = N; a.ldy = ldy;
   if (K == 1024) {
     if (epilogue == 1) return dispatch_t<1, PRO_COPY, EPI_SILU, 14>(a, grid_for(N / 2, 14), s);
     if (N <= 2048) return dispatch_t<1, PRO_COPY, EPI_STORE, 4>(a, grid_for(N / 2, 4), s);
@@ -273,37 +328,38 @@ int gemv_bf16(const void* x, const void* W, void* y, int T, int N, int K, int ld
 // RMSNorm(res)·ln_w -> ·Wqkv^T -> RoPE -> q into qkv[:, :1024], k/v into the page of slot[t].
 int gemv_qkv_rope(const void* res, const void* ln_w, const void* Wqkv, const void* cos_sin, const int32_t* pos,
                   const int64_t* slot, void* qkv, void* kv_layer, int T, float eps, cudaStream_t s,
-                  const void* next_w, size_t next_bytes) {
+                  const void* next_w, size_t next_bytes, const float* wscale) {
   GemvArgs a = {};
-  a.next_w = next_w; a.next_bytes = next_bytes;
-  a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = (const bf16*)Wqkv; a.y = (bf16*)qkv;
+  a.next_w = next_w; a.next_bytes = next_bytes; a.wscale = wscale;
+  a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = Wqkv; a.y = (bf16*)qkv;
   a.cos_sin = (const bf16*)cos_sin; a.pos = pos; a.slot = slot; a.kv_layer = (uint8_t*)kv_layer;
   a.T = T; a.N = 3072; a.ldy = 3072; a.eps = eps;
   return dispatch_t<1, PRO_NORM, EPI_ROPE, 12>(a, grid_for(1536, 12), s);
 }
 // res = bf16(bf16(x·W^T) + res), N = 1024, K in {1024, 4096}.
 int gemv_residual(const void* x, const void* W, void* res, int T, int K, cudaStream_t s, const void* next_w,
-                  size_t next_bytes) {
+                  size_t next_bytes, const float* wscale) {
   GemvArgs a = {};
-  a.next_w = next_w; a.next_bytes = next_bytes;
-  a.x = (const bf16*)x; a.W = (const bf16*)W; a.y = (bf16*)res; a.T = T; a.N = 1024; a.ldy = 1024;
+  a.next_w = next_w; a.next_bytes = next_bytes; a.wscale = wscale;
+  a.x = (const bf16*)x; a.W = W; a.y = (bf16*)res; a.T = T; a.N = 1024; a.ldy = 1024;
   if (K == 1024) return dispatch_t<1, PRO_COPY, EPI_RES, 4>(a, grid_for(512, 4), s);
   return dispatch_t<4, PRO_COPY, EPI_RES, 16>(a, grid_for(512, 4), s);
 }
 // act = SiLU(g)·u of RMSNorm(res)·ln_w · Wgu^T (packed gate/up), act [T, 4096].
 int gemv_norm_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, int T, float eps, cudaStream_t s,
-                      const void* next_w, size_t next_bytes) {
+                      const void* next_w, size_t next_bytes, const float* wscale) {
   GemvArgs a = {};
-  a.next_w = next_w; a.next_bytes = next_bytes;
-  a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = (const bf16*)Wgu; a.y = (bf16*)act;
+  a.next_w = next_w; a.next_bytes = next_bytes; a.wscale = wscale;
+  a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = Wgu; a.y = (bf16*)act;
   a.T = T; a.N = 8192; a.ldy = 4096; a.eps = eps;
   return dispatch_t<1, PRO_NORM, EPI_SILU, 14>(a, grid_for(4096, 14), s);
 }
 // logits = RMSNorm(res)·norm_w · Whead^T, N even.
 int gemv_norm_head(const void* res, const void* norm_w, const void* Whead, void* logits, int T, int N, int ldy,
-                   float eps, cudaStream_t s) {
+                   float eps, cudaStream_t s, const float* wscale) {
   GemvArgs a = {};
-  a.x = (const bf16*)res; a.ln_w = (const bf16*)norm_w; a.W = (const bf16*)Whead; a.y = (bf16*)logits;
+  a.wscale = wscale;
+  a.x = (const bf16*)res; a.ln_w = (const bf16*)norm_w; a.W = Whead; a.y = (bf16*)logits;
   a.T = T; a.N = N; a.ldy = ldy; a.eps = eps;
   return dispatch_t<1, PRO_NORM, EPI_STORE, 14>(a, grid_for(N / 2, 14), s);
 }

@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from . import ops
-from ._lib import (BLOCK_SIZE, EngineCfg, HIDDEN, PAGE_BYTES, SPEECH_VOCAB, Weights, check, load)
+from ._lib import (BLOCK_SIZE, EngineCfg, Fp8Weights, HIDDEN, PAGE_BYTES, SPEECH_VOCAB, Weights, check, load)
 
 BF16 = torch.bfloat16
 COND_LEN = 34                 # CONDITIONING_SIZE, t3.py:42
@@ -64,7 +64,10 @@ class T3Engine:
     def __init__(self, state_dict: dict, *, device="cuda:0", max_pairs: int = 128, max_model_len: int = 1000,
                  num_blocks: int | None = None, max_rows: int | None = None, cfg_scale: float | None = None,
                  rms_eps: float = 1e-5, base_seed: int = 0, use_graph: bool = True,
-                 stop_token: int = STOP_SPEECH):
+                 stop_token: int = STOP_SPEECH, weight_dtype: str | None = None):
+        """weight_dtype: "bf16" (default; env CBX_WEIGHT_DTYPE overrides) or "fp8_e4m3" — the optional
+        weight-only FP8 path: the four projections of every layer and the speech head are quantised per
+        output feature on the GPU at load time and the bf16 copies are dropped."""
         load()                                           # fail loudly if the CUDA library is missing
         if not torch.cuda.is_available():
             raise RuntimeError("T3Engine needs a CUDA device (no CPU fallback)")
@@ -96,6 +99,12 @@ class T3Engine:
                                            self.block_table.data_ptr(), ws, C.byref(self._st))
         if not self._h:
             raise RuntimeError("cbx_engine_create: " + load().cbx_last_error().decode())
+        self.weight_dtype = (weight_dtype or os.environ.get("CBX_WEIGHT_DTYPE", "bf16")).lower()
+        if self.weight_dtype in ("fp8", "fp8_e4m3", "e4m3"):
+            self.weight_dtype = "fp8_e4m3"
+            self._quantize_weights()
+        elif self.weight_dtype != "bf16":
+            raise ValueError(f"weight_dtype {self.weight_dtype!r}: expected 'bf16' or 'fp8_e4m3'")
         self.gpu_launches = 0
 
     # ------------------------------------------------------------------ weights
@@ -132,6 +141,28 @@ class T3Engine:
         self._w = Weights(L, *self._arrs, self.norm.data_ptr(), self.speech_emb.data_ptr(),
                           self.speech_head.data_ptr(), self.cos_sin.data_ptr(), rms_eps)
         torch.cuda.synchronize()
+
+    def _quantize_weights(self) -> None:
+        """bf16 projections -> e4m3 bytes + per-output-feature fp32 scales (gate/up AFTER packing, so the
+        scale array is in packed row order); the engine is switched over and the bf16 copies released."""
+        L = self.n_layers
+        with torch.cuda.stream(self.stream):
+            q = lambda ws: [ops.quantize_fp8_rows(w) for w in ws]  # noqa: E731
+            self.wqkv, self.wo, self.wgu, self.wd = q(self.wqkv), q(self.wo), q(self.wgu), q(self.wd)
+            self.speech_head = ops.quantize_fp8_rows(self.speech_head)
+        self.stream.synchronize()
+        arr = lambda ps: (C.c_void_p * L)(*ps)  # noqa: E731
+        self._arrs8 = [arr([w.q.data_ptr() for w in ws]) for ws in (self.wqkv, self.wo, self.wgu, self.wd)] + \
+                      [arr([w.scale_buf.data_ptr() for w in ws]) for ws in (self.wqkv, self.wo, self.wgu, self.wd)]
+        self._w8 = Fp8Weights(L, *self._arrs8, self.speech_head.q.data_ptr(), self.speech_head.scale_buf.data_ptr())
+        check(load().cbx_engine_set_fp8_weights(self._h, C.byref(self._w8)), "set_fp8_weights")
+
+    def projection_weight_bytes(self) -> int:
+        """Bytes one decode step streams for the projections + head (the W term of the step roofline)."""
+        ws = self.wqkv + self.wo + self.wgu + self.wd + [self.speech_head]
+        if self.weight_dtype == "fp8_e4m3":
+            return sum(w.q.numel() + 4 * w.q.shape[0] for w in ws)
+        return sum(w.numel() * 2 for w in ws)
 
     # ------------------------------------------------------------------ helpers
     def buffer(self, name: str, shape, dtype) -> torch.Tensor:

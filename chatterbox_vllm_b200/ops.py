@@ -54,7 +54,39 @@ def pack_gate_up(wgu: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def linear(x: torch.Tensor, W: torch.Tensor, epilogue: int = 0, path: int = 0, out: torch.Tensor | None = None,
+class Fp8Weight:
+    """An nn.Linear weight [N, K] as FP8-e4m3 bytes + one fp32 scale per output feature (the optional
+    weight-only FP8 path).  `scale_buf` is padded with 1.0 to a multiple of 128 entries, as the
+    tcgen05 epilogue reads scales 32 at a time.  Every projection op below accepts one in place of a
+    bf16 weight."""
+
+    def __init__(self, q: torch.Tensor, scale_buf: torch.Tensor):
+        self.q, self.scale_buf = q, scale_buf
+        self.shape = q.shape
+
+    @property
+    def scale(self) -> torch.Tensor:
+        return self.scale_buf[:self.q.shape[0]]
+
+    def dequant(self) -> torch.Tensor:
+        """fp32 [N, K] = q · scale — what the kernels multiply by (exactly, up to summation order)."""
+        return self.q.view(torch.float8_e4m3fn).float() * self.scale[:, None]
+
+
+def quantize_fp8_rows(W: torch.Tensor) -> Fp8Weight:
+    """scale[n] = max|W[n,:]|/448, q = e4m3(W/scale) — on the GPU (cbx_quantize_fp8_rows)."""
+    N, K = W.shape
+    q = torch.empty(N, K, dtype=torch.uint8, device=W.device)
+    sb = torch.ones((N + 127) // 128 * 128, dtype=torch.float32, device=W.device)
+    check(load().cbx_quantize_fp8_rows(_p(W, BF16), _p(q), _p(sb), N, K, _stream()), "quantize_fp8_rows")
+    return Fp8Weight(q, sb)
+
+
+def _w8(W):
+    return isinstance(W, Fp8Weight)
+
+
+def linear(x: torch.Tensor, W, epilogue: int = 0, path: int = 0, out: torch.Tensor | None = None,
            ld: int | None = None):
     """y = x·Wᵀ ; epilogue=1: SiLU(gate)·up with W packed by pack_gate_up (y is [T, N/2]).
     ld: row stride of a freshly allocated result (elements) when N itself is not vector-aligned,
@@ -62,15 +94,22 @@ def linear(x: torch.Tensor, W: torch.Tensor, epilogue: int = 0, path: int = 0, o
     T, K = x.shape
     N = W.shape[0]
     assert W.shape[1] == K
+
+    def run(dst, ldy, epi):
+        if _w8(W):
+            check(load().cbx_linear_fp8w(_p(x, BF16), _p(W.q, torch.uint8), _p(W.scale_buf, torch.float32), _p(dst, BF16),
+                                         T, N, K, ldy, epi, path, _stream()), "linear_fp8w")
+        else:
+            check(load().cbx_linear(_p(x, BF16), _p(W, BF16), _p(dst, BF16), T, N, K, ldy, epi, path, _stream()), "linear")
+
     if ld is not None:
         assert out is None and epilogue == 0 and ld >= N
         buf = torch.empty(T, ld, dtype=BF16, device=x.device)
-        check(load().cbx_linear(_p(x, BF16), _p(W, BF16), _p(buf, BF16), T, N, K, ld, 0, path, _stream()), "linear")
+        run(buf, ld, 0)
         return buf[:, :N]
     if out is None:
         out = torch.empty(T, N // 2 if epilogue else N, dtype=BF16, device=x.device)
-    check(load().cbx_linear(_p(x, BF16), _p(W, BF16), _p(out, BF16), T, N, K, out.stride(0), epilogue, path,
-                            _stream()), "linear")
+    run(out, out.stride(0), epilogue)
     return out
 
 
@@ -140,6 +179,12 @@ def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5, 
         qkv = torch.zeros(T, 3 * HIDDEN, dtype=BF16, device=res.device)
     if h is None and T > 4:
         h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device)
+    if _w8(wqkv):
+        check(load().cbx_layer_qkv_fp8w(_p(res, BF16), _p(ln_w, BF16), _p(wqkv.q, torch.uint8),
+                                        _p(wqkv.scale_buf, torch.float32), _p(cos_sin, BF16), _p(pos, torch.int32),
+                                        _p(slot, torch.int64), _p(qkv), _p(kv_layer), _p(h), T, eps, _stream()),
+              "layer_qkv_fp8w")
+        return qkv
     check(load().cbx_layer_qkv(_p(res, BF16), _p(ln_w, BF16), _p(wqkv, BF16), _p(cos_sin, BF16), _p(pos, torch.int32),
                                _p(slot, torch.int64), _p(qkv), _p(kv_layer), _p(h), T, eps, _stream()), "layer_qkv")
     return qkv
@@ -148,7 +193,11 @@ def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5, 
 def linear_residual(x, W, res):
     """res += x·Wᵀ in place (N = 1024)."""
     T, K = x.shape
-    assert W.shape == (HIDDEN, K) and res.shape == (T, HIDDEN)
+    assert tuple(W.shape) == (HIDDEN, K) and res.shape == (T, HIDDEN)
+    if _w8(W):
+        check(load().cbx_linear_residual_fp8w(_p(x, BF16), _p(W.q, torch.uint8), _p(W.scale_buf, torch.float32),
+                                              _p(res, BF16), T, K, _stream()), "linear_residual_fp8w")
+        return res
     check(load().cbx_linear_residual(_p(x, BF16), _p(W, BF16), _p(res, BF16), T, K, _stream()), "linear_residual")
     return res
 
@@ -157,6 +206,10 @@ def linear_partials(x, W, splits: int):
     """fp32 [splits, T, 1024] split-K partial products of x·Wᵀ."""
     T, K = x.shape
     part = torch.empty(splits, T, HIDDEN, dtype=torch.float32, device=x.device)
+    if _w8(W):
+        check(load().cbx_linear_partials_fp8w(_p(x, BF16), _p(W.q, torch.uint8), _p(W.scale_buf, torch.float32), _p(part),
+                                              T, K, splits, _stream()), "linear_partials_fp8w")
+        return part
     check(load().cbx_linear_partials(_p(x, BF16), _p(W, BF16), _p(part), T, K, splits, _stream()), "linear_partials")
     return part
 
@@ -176,6 +229,11 @@ def layer_gate_up(res, ln_w, wgu_packed, eps: float = 1e-5, act=None, h=None):
         act = torch.empty(T, INTER, dtype=BF16, device=res.device)
     if h is None and T > 4:
         h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device)
+    if _w8(wgu_packed):
+        check(load().cbx_layer_gate_up_fp8w(_p(res, BF16), _p(ln_w, BF16), _p(wgu_packed.q, torch.uint8),
+                                            _p(wgu_packed.scale_buf, torch.float32), _p(act), _p(h), T, eps, _stream()),
+              "layer_gate_up_fp8w")
+        return act
     check(load().cbx_layer_gate_up(_p(res, BF16), _p(ln_w, BF16), _p(wgu_packed, BF16), _p(act), _p(h), T, eps,
                                    _stream()), "layer_gate_up")
     return act
@@ -187,6 +245,11 @@ def head_logits(res, norm_w, whead, eps: float = 1e-5, logits=None, h=None):
         logits = torch.zeros(T, LOGITS_LD, dtype=BF16, device=res.device)
     if h is None and T > 4:
         h = torch.empty(T, HIDDEN, dtype=BF16, device=res.device)
+    if _w8(whead):
+        check(load().cbx_head_logits_fp8w(_p(res, BF16), _p(norm_w, BF16), _p(whead.q, torch.uint8),
+                                          _p(whead.scale_buf, torch.float32), _p(logits), _p(h), T, eps, _stream()),
+              "head_logits_fp8w")
+        return logits
     check(load().cbx_head_logits(_p(res, BF16), _p(norm_w, BF16), _p(whead, BF16), _p(logits), _p(h), T, eps,
                                  _stream()), "head_logits")
     return logits

@@ -74,6 +74,27 @@ int cbx_rmsnorm_reduce(const void* partials, int splits, void* residual, const v
  * at decode batch sizes, where 16 column tiles alone would leave most of the 148 SMs idle. */
 int cbx_linear_partials(const void* x, const void* W, void* partials, int T, int K, int splits, void* stream);
 
+/* Per-output-feature e4m3 quantisation of a bf16 [N,K] weight: scale[n] = max|W[n,:]|/448 (1 for a zero
+ * row), W8[n,k] = e4m3_rn_satfinite(W[n,k]/scale[n]).  Bit-identical to torch's
+ * (W.float()/scale[:,None]).to(torch.float8_e4m3fn). */
+int cbx_quantize_fp8_rows(const void* W, void* W8, float* scale, int N, int K, void* stream);
+/* cbx_linear over FP8 weights: y = bf16((x · W8^T) * wscale[n]) (epilogue 1: SiLU(gate)·up of the scaled
+ * pair).  GEMV regime widens the bytes in registers; tcgen05 regime widens them in shared memory
+ * (converter warps write the SWIZZLE_128B bf16 operand tile).  wscale must hold round_up(N,128) floats. */
+int cbx_linear_fp8w(const void* x, const void* W8, const float* wscale, void* y, int T, int N, int K, int ldy,
+                    int epilogue, int path, void* stream);
+/* FP8-weight forms of the fused layer pieces below (same arguments + wscale). */
+int cbx_layer_qkv_fp8w(const void* res, const void* ln_w, const void* Wqkv8, const float* wscale,
+                       const void* cos_sin, const int32_t* pos, const int64_t* slot, void* qkv, void* kv_layer,
+                       void* h_scratch, int T, float eps, void* stream);
+int cbx_linear_residual_fp8w(const void* x, const void* W8, const float* wscale, void* res, int T, int K, void* stream);
+int cbx_linear_partials_fp8w(const void* x, const void* W8, const float* wscale, void* partials, int T, int K,
+                             int splits, void* stream);
+int cbx_layer_gate_up_fp8w(const void* res, const void* ln_w, const void* Wgu8, const float* wscale, void* act,
+                           void* h_scratch, int T, float eps, void* stream);
+int cbx_head_logits_fp8w(const void* res, const void* norm_w, const void* Whead8, const float* wscale, void* logits,
+                         void* h_scratch, int T, float eps, void* stream);
+
 /* y[T,N] = x[T,K] · W[N,K]^T (bf16 in, fp32 accumulate, bf16 out).  Replaces the
  * cuBLAS GEMMs behind vllm llama.py:117-120,221,225 and t3.py:729-730.
  * epilogue: 0 = store; 1 = SiLU(gate)·up with W packed by cbx_pack_gate_up (y is [T,N/2]);
@@ -245,6 +266,26 @@ int64_t cbx_engine_workspace_bytes(const cbx_engine_cfg* cfg);
 cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_weights* w, void* kv_cache,
                               int32_t* block_table, void* workspace, const cbx_sampler_state* st);
 void cbx_engine_destroy(cbx_engine*);
+/* ---- optional FP8-e4m3 weight path (north star: "an optional FP8-e4m3 per-channel weight path is
+ * reported separately with its own tolerance"; SURVEY §8(d) cfg 5).  Weight-only: activations, KV
+ * cache, embeddings and the sampler stay bf16 / fp32.  The reference has no counterpart (vLLM's
+ * `quantization="fp8"` would be the nearest switch on `LLM(...)`, tts.py:130-140). */
+typedef struct cbx_fp8_weights {
+  int n_layers;
+  const void* const* wqkv;   /* [L] -> [3072,1024] e4m3 bytes                 */
+  const void* const* wo;     /* [L] -> [1024,1024]                            */
+  const void* const* wgu;    /* [L] -> [8192,1024] quantised AFTER cbx_pack_gate_up */
+  const void* const* wd;     /* [L] -> [1024,4096]                            */
+  const float* const* sqkv;  /* [L] -> [3072] fp32 scale per output feature   */
+  const float* const* so;    /* [L] -> [1024]                                 */
+  const float* const* sgu;   /* [L] -> [8192] (packed row order)              */
+  const float* const* sd;    /* [L] -> [1024]                                 */
+  const void* speech_head;   /* [8194,1024] e4m3 bytes                        */
+  const float* shead;        /* [8320] = 8194 scales padded with 1.0 to a multiple of 128 */
+} cbx_fp8_weights;
+/* Switch a created engine's projections + speech head to FP8 weights (pointers must outlive it). */
+int cbx_engine_set_fp8_weights(cbx_engine*, const cbx_fp8_weights*);
+
 /* Device pointer of an internal buffer by name ("x","h","qkv","attn","act","logits","pos",
  * "slot","kv_len","row_seq","head_rows") for tests / the Python façade; NULL if unknown. */
 void* cbx_engine_buffer(cbx_engine*, const char* name);

@@ -187,6 +187,29 @@ class T3Weights:
         return sd
 
 
+def fp8_e4m3_rows(w: torch.Tensor):
+    """Per-output-feature FP8-e4m3 quantisation of an nn.Linear weight [N, K] (the optional weight-only
+    FP8 path, SURVEY.md §8(d) cfg 5): scale[n] = max|w[n,:]| / 448 (1 for a zero row),
+    q = e4m3_rn(w / scale).  Returns (q as torch.float8_e4m3fn, scale fp32)."""
+    wf = w.float()
+    amax = wf.abs().amax(dim=1)
+    scale = torch.where(amax > 0, amax / 448.0, torch.ones_like(amax))
+    return (wf / scale[:, None]).to(torch.float8_e4m3fn), scale
+
+
+def with_fp8_projections(w: "T3Weights") -> "T3Weights":
+    """The weights the FP8 engine effectively multiplies by: q·scale in fp32 for the four projections
+    of every layer and the speech head (embeddings, norms, position tables stay bf16).  T3Oracle
+    upcasts weights with .float(), so it runs on these unchanged."""
+    import copy
+    dq = lambda t: (lambda q, s: q.float() * s[:, None])(*fp8_e4m3_rows(t))  # noqa: E731
+    w8 = copy.copy(w)
+    w8.wqkv, w8.wo = [dq(t) for t in w.wqkv], [dq(t) for t in w.wo]
+    w8.wgu, w8.wd = [dq(t) for t in w.wgu], [dq(t) for t in w.wd]
+    w8.speech_head = dq(w.speech_head)
+    return w8
+
+
 def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float, mode: str) -> torch.Tensor:
     """vLLM rms_norm: out = bf16(bf16(x·rstd) · w); fp32 statistics."""
     xf = x.float()

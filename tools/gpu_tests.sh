@@ -19,3 +19,4 @@ run post    tests/test_gpu_kernels.py -k "postprocess or cond_encoder"
 run sampler tests/test_gpu_engine.py -k "sampler or prefill_embed"
 run engine  tests/test_gpu_engine.py -k "engine"
 run facade  tests/test_gpu_facade.py
+run fp8     tests/test_gpu_fp8.py
