@@ -1,6 +1,7 @@
 // common.cuh — shared device helpers for libcbx_t3.so (sm_100a only).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -137,6 +138,17 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// explicit shared-space 128-bit accesses (a pointer carved out of the dynamic shared array by integer
+// arithmetic is generic to the compiler: LD.E/ST.E plus a MEMBAR.ALL.CTA in front of every proxy fence)
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // ---- mbarrier ----------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -269,6 +281,32 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)1 << 46;
   d |= (uint64_t)2 << 61;
   return d;
+}
+// ---- FP8-e4m3 weight bytes -> f16 without the conversion pipe --------------------------------------
+// An e4m3 byte s.eeee.mmm placed at bits 14..7 of a 16-bit lane reads as the f16 number value/256 — for
+// normals, subnormals and zero alike (both formats keep 3 / 10 mantissa bits under the same hidden-bit
+// rule; the exponent bias differs by 8).  The sign then sits at bit 14: adding (x & 0x4000) moves it to
+// bit 15.  PRMT + shift + AND + ADD per two elements, all on the integer/FMA pipes; cvt.f16x2.e4m3x2 runs
+// on the 16-lane conversion unit: the first converter built on it left the FP8 prefill 2x slower than bf16.
+// Consumers fold the factor 256 into the per-output-feature scale.
+__device__ __forceinline__ void e4m3x4_to_f16x2_div256(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  const uint32_t a = __byte_perm(w, 0, 0x4140) << 7;    // halves: byte0, byte1
+  const uint32_t b = __byte_perm(w, 0, 0x4342) << 7;    // halves: byte2, byte3
+  lo = a + (a & 0x40004000u);
+  hi = b + (b & 0x40004000u);
+}
+// Same four bytes as two bf16x2 words (still value / 256, exact).  tcgen05.mma kind::f16 does NOT take a bf16 A
+// next to an f16 B — the descriptor encodes the two formats separately and CUTLASS's traits only ask for two
+// 16-bit types, but the B200 raises cudaErrorIllegalInstruction — so the f16 lanes are widened to fp32
+// (HADD2.F32, exact, subnormals included) and the bf16 is the top half of each fp32 word (3 mantissa bits: no
+// rounding).  14 integer / half-pipe ops per four weights, none on the conversion unit.
+__device__ __forceinline__ void e4m3x4_to_bf16x2_div256(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  uint32_t h0, h1;
+  e4m3x4_to_f16x2_div256(w, h0, h1);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&h0));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&h1));
+  lo = __byte_perm(__float_as_uint(a.x), __float_as_uint(a.y), 0x7632);
+  hi = __byte_perm(__float_as_uint(b.x), __float_as_uint(b.y), 0x7632);
 }
 // Instruction descriptor for kind::f16: C=f32, A=B=bf16, both K-major, M x N.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {

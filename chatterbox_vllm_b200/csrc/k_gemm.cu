@@ -20,9 +20,11 @@
 // W8 = true (weight-only FP8-e4m3, per-output-channel fp32 scale): tcgen05.mma kind::f16 takes no
 // 8-bit B operand next to a bf16 A, so the weight tile travels HBM -> L2 -> shared memory as BYTES
 // (half the ingest, which is what bounds the decode GEMMs) and is widened on chip: TMA drops the
-// BN x 64-byte e4m3 tile into a linear staging buffer, warps 4-7 (idle until the epilogue) convert it
-// to bf16 (exact) straight into the SWIZZLE_128B operand layout, fence.proxy.async, and arrive on a
-// per-stage "converted" barrier the MMA issuer waits on.  Weights do not depend on the previous
+// BN x 64-byte e4m3 tile into a linear staging buffer, eight converter warps (4-7, idle until the
+// epilogue, plus four extra warps 8-11 the W8 form launches) widen it
+// to bf16 (exact; integer + half-pipe ops only: common.cuh e4m3x4_to_bf16x2_div256 — a bf16 A next to
+// an f16 B raises an illegal-instruction error on B200) straight into the SWIZZLE_128B operand layout,
+// fence.proxy.async, and arrive on a per-stage "converted" barrier the MMA issuer waits on.  Weights do not depend on the previous
 // kernel, so the first ring fill is loaded AND converted before griddepcontrol.wait.  The scale
 // multiplies the fp32 accumulator in the epilogue, before the first bf16 rounding point.
 #include <cuda.h>
@@ -87,30 +89,21 @@ struct EpiArgs {               // EPI 2 only
 // weight bytes per output element halve.  Both producers signal the LEADER's full barrier (peer bit of
 // the barrier address cleared, .cta_group::2 copy), the leader's elected thread issues the MMAs and
 // multicasts its commits to both CTAs' empty / accumulator barriers, each CTA drains its own TMEM.
-// 16 e4m3 bytes -> 16 bf16 (exact) as two 16-byte operand chunks
+// 16 e4m3 bytes -> 16 bf16 (= value / 256, exact) as two 16-byte operand chunks
 __device__ __forceinline__ void e4m3x16_to_bf16(const uint4& v, uint4& lo8, uint4& hi8) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  uint32_t o[8];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    uint32_t h0, h1;
-    asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\t"
-        "cvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
-        : "=r"(h0), "=r"(h1) : "r"(w[i]));
-    const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&h0));
-    const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&h1));
-    o[2 * i] = pack_bf16(f0.x, f0.y);
-    o[2 * i + 1] = pack_bf16(f1.x, f1.y);
-  }
-  lo8 = make_uint4(o[0], o[1], o[2], o[3]);
-  hi8 = make_uint4(o[4], o[5], o[6], o[7]);
+  e4m3x4_to_bf16x2_div256(v.x, lo8.x, lo8.y);
+  e4m3x4_to_bf16x2_div256(v.y, lo8.z, lo8.w);
+  e4m3x4_to_bf16x2_div256(v.z, hi8.x, hi8.y);
+  e4m3x4_to_bf16x2_div256(v.w, hi8.z, hi8.w);
 }
-// r[i] *= scale[i], i < 32 (scale 16-byte aligned; the same 32 values for every row of the tile)
+// r[i] *= 256 * scale[i], i < 32 (scale 16-byte aligned; the same 32 values for every row of the tile; 256 undoes
+// the widening's exponent offset)
 __device__ __forceinline__ void scale32(uint32_t (&r)[32], const float* __restrict__ sc) {
   const float4* sp = reinterpret_cast<const float4*>(sc);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const float4 v = __ldg(sp + i);
+    float4 v = __ldg(sp + i);
+    v.x *= 256.f; v.y *= 256.f; v.z *= 256.f; v.w *= 256.f;
     r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) * v.x);
     r[4 * i + 1] = __float_as_uint(__uint_as_float(r[4 * i + 1]) * v.y);
     r[4 * i + 2] = __float_as_uint(__uint_as_float(r[4 * i + 2]) * v.z);
@@ -118,8 +111,10 @@ __device__ __forceinline__ void scale32(uint32_t (&r)[32], const float* __restri
   }
 }
 
+// W8 launches 12 warps: the extra four (8-11) are converters only.
+constexpr int kThreads8 = 384;
 template <int BN, int EPI, int CN, bool W8 = false>
-__global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
+__global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                               const __grid_constant__ CUtensorMap tma_b,
                                                               bf16* __restrict__ y, int M, int N, int K, int ldy,
                                                               const EpiArgs ea, const int n_stages,
@@ -133,7 +128,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   uint64_t* tmem_full = empty + n_stages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   uint64_t* fullb = tmem_full + 2;                     // W8: e4m3 staging tile landed
-  uint64_t* conv = fullb + n_stages;                   // W8: bf16 operand tile written (4 converter warps)
+  uint64_t* conv = fullb + n_stages;                   // W8: bf16 operand tile written (the 2 warps of a converter group)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // pair mode: the two row tiles of a cluster are neighbours along grid.x (cluster dims (2, 1, 1))
@@ -153,7 +148,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    if (W8) for (int s = 0; s < n_stages; ++s) { mbar_init(&fullb[s], 1); mbar_init(&conv[s], 4); }
+    if (W8) for (int s = 0; s < n_stages; ++s) { mbar_init(&fullb[s], 1); mbar_init(&conv[s], 2); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -250,27 +245,29 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   } else if (warp < 4) {
     pdl_wait();
   } else if (W8) {
-    // ---- converters (warps 4-7): e4m3 staging tile -> bf16 operand tile in the SWIZZLE_128B layout.
-    // Thread t takes 16-byte chunk c = i*128 + t of the tile: weight row c >> 2, bytes (c & 3)*16..+16 of
-    // its 64-element k-block, i.e. bf16 chunks 2*(c & 3) and 2*(c & 3) + 1 of the 128-byte operand row,
+    // ---- converters (warps 4-11): e4m3 staging tile -> bf16 operand tile in the SWIZZLE_128B layout.
+    // Four groups of two warps; group g owns k-blocks kb = g (mod 4), so four stages are widened
+    // concurrently (one warp set walking every stage in turn is LATENCY-bound: wait -> LDS -> 14-op chain ->
+    // STS -> fence -> arrive measured ~1200 cycles per stage against 256 for its MMAs).  Thread t of a group
+    // takes 16-byte chunk c = i*64 + t of the tile: weight row c >> 2, bytes (c & 3)*16..+16 of its
+    // 64-element k-block, i.e. bf16 chunks 2*(c & 3) and 2*(c & 3) + 1 of the 128-byte operand row,
     // stored at chunk ^ (row & 7) (TMA's 128-byte swizzle; stage bases are 1024-aligned).
-    const int t = threadIdx.x - 128;
+    const int grp = (warp - 4) >> 1, t = threadIdx.x - 128 - grp * 64;
     constexpr int kB8Off = C::kABytes + C::kBBytes;
-    for (int kb = 0; kb < n_kb; ++kb) {
+    const uint32_t smem0 = smem_u32(smem);
+    for (int kb = grp; kb < n_kb; kb += 4) {
       const int s = kb % n_stages, ph = (kb / n_stages) & 1;
       if (kb >= n_stages) mbar_wait(&empty[s], ph ^ 1);   // the MMAs that read this operand tile are done
       mbar_wait(&fullb[s], ph);
-      uint8_t* st = smem + s * C::kStageBytes;
-      const uint4* src = reinterpret_cast<const uint4*>(st + kB8Off);
-      uint8_t* dstb = st + C::kABytes;
+      const uint32_t st = smem0 + s * C::kStageBytes;
 #pragma unroll
-      for (int i = 0; i < BN * 4 / 128; ++i) {
-        const int c = i * 128 + t, row = c >> 2, ch = (c & 3) * 2;
+      for (int i = 0; i < BN * 4 / 64; ++i) {
+        const int c = i * 64 + t, row = c >> 2, ch = (c & 3) * 2;
         uint4 lo8, hi8;
-        e4m3x16_to_bf16(src[c], lo8, hi8);
-        uint8_t* rowp = dstb + row * 128;
-        *reinterpret_cast<uint4*>(rowp + ((ch ^ (row & 7)) << 4)) = lo8;
-        *reinterpret_cast<uint4*>(rowp + (((ch + 1) ^ (row & 7)) << 4)) = hi8;
+        e4m3x16_to_bf16(lds128(st + kB8Off + c * 16), lo8, hi8);
+        const uint32_t rowp = st + C::kABytes + row * 128;
+        sts128(rowp + ((ch ^ (row & 7)) << 4), lo8);
+        sts128(rowp + (((ch + 1) ^ (row & 7)) << 4), hi8);
       }
       fence_proxy_async();                              // generic-proxy writes -> visible to tcgen05.mma
       __syncwarp();
@@ -282,7 +279,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const __grid_const
   // +3.5 us at T = 256).  For the column-chunked epilogues the four role warps, idle by now, take every
   // other 32-column chunk of their quarter.
   constexpr bool kAllWarps = EPI != 2;
-  if (warp >= 4 || kAllWarps) {
+  if (warp < 8 && (warp >= 4 || kAllWarps)) {
     __syncwarp();
     const int ew = warp & 3;                           // TMEM lane quarter
     if (warp >= 4) pdl_wait();
@@ -532,7 +529,7 @@ int launch8(const void* x, const void* W, const float* wscale, void* y, int M, i
   CUtensorMap ma, mb;
   if (make_map(&ma, x, M, K, BM)) return -1;
   if (make_map_u8(&mb, W, N, K, BN)) return -1;
-  cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI, 1, true>, dim3(n_tiles, m_tiles, splits), dim3(kThreads), C::kSmem, s, ma, mb,
+  cudaError_t e = launch_pdl(gemm_tc_kernel<BN, EPI, 1, true>, dim3(n_tiles, m_tiles, splits), dim3(kThreads8), C::kSmem, s, ma, mb,
                              (bf16*)y, M, N, K, ldy, ea, (int)C::kStages, wscale);
   CBX_REQUIRE(e == cudaSuccess, "gemm_tc (fp8w) launch failed: %s", cudaGetErrorString(e));
   count_launch();

@@ -16,8 +16,8 @@
 // L2) — cheaper than a separate launch.
 //
 // W8 = true: FP8-e4m3 weights with one fp32 scale per output feature (the optional weight-only
-// FP8 path of the north star).  The stream halves (2 KB per warp per item); bytes are widened with
-// cvt.rn.f16x2.e4m3x2 in registers, accumulation stays fp32, and the scale multiplies the finished
+// FP8 path of the north star).  The stream halves (2 KB per warp per item); bytes are widened to f16
+// with integer ops in registers (common.cuh), accumulation stays fp32, and the scale multiplies the finished
 // dot product before the first bf16 rounding point, so y = bf16((x . q) * s) == x . (q * s) up to
 // fp32 summation order — exactly the oracle's "dequantised weights" chain.
 #include <cuda_fp16.h>
@@ -51,15 +51,13 @@ __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
   f[4] = bf_lo(v.z); f[5] = bf_hi(v.z); f[6] = bf_lo(v.w); f[7] = bf_hi(v.w);
 }
 
-// 16 e4m3 bytes -> 16 floats (exact: e4m3 is a subset of f16)
+// 16 e4m3 bytes -> 16 floats = value / 256 (exact; integer widening to f16, common.cuh)
 __device__ __forceinline__ void unpack16_e4m3(const uint4& v, float (&f)[16]) {
   const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     uint32_t lo, hi;
-    asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\t"
-        "cvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
-        : "=r"(lo), "=r"(hi) : "r"(w[i]));
+    e4m3x4_to_f16x2_div256(w[i], lo, hi);
     const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&lo));
     const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&hi));
     f[4 * i] = a.x; f[4 * i + 1] = a.y; f[4 * i + 2] = b.x; f[4 * i + 3] = b.y;
@@ -105,6 +103,16 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
     for (int j = 0; j < NJ; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
   }
   l2_prefetch_slice(a.next_w, a.next_bytes);
+  // W8: the first item's bytes are widened to fp32 BEFORE the wait (3.5 ops per weight that would otherwise sit on
+  // the kernel-to-kernel critical path; measured +0.1 us per kernel at b = 1)
+  float wf[2][W8 ? 32 : 1];
+  if (W8 && item < n_items) {
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      unpack16_e4m3(cur[0][j], *reinterpret_cast<float(*)[16]>(&wf[0][j * 16]));
+      unpack16_e4m3(cur[1][j], *reinterpret_cast<float(*)[16]>(&wf[1][j * 16]));
+    }
+  }
   pdl_wait();
 
   // ---- prologue: activation rows -> shared memory (bf16)
@@ -166,9 +174,6 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       // lane's 16 bytes of load j are elements [j*512 + lane*16, +16) of the segment
 #pragma unroll
       for (int j = 0; j < NJ; ++j) {
-        float fa[16], fb[16];
-        unpack16_e4m3(cur[0][j], fa);
-        unpack16_e4m3(cur[1][j], fb);
 #pragma unroll
         for (int t = 0; t < TT; ++t) {
 #pragma unroll
@@ -177,8 +182,8 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
             unpack8(xs[t * (K / 8) + kseg * 128 + j * 64 + lane * 2 + c], fx);
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-              acc[0][t] = fmaf(fa[c * 8 + e], fx[e], acc[0][t]);
-              acc[1][t] = fmaf(fb[c * 8 + e], fx[e], acc[1][t]);
+              acc[0][t] = fmaf(wf[0][W8 ? j * 16 + c * 8 + e : 0], fx[e], acc[0][t]);
+              acc[1][t] = fmaf(wf[1][W8 ? j * 16 + c * 8 + e : 0], fx[e], acc[1][t]);
             }
           }
         }
@@ -227,7 +232,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       float v0 = 0.f, v1 = 0.f;
 #pragma unroll
       for (int t = 0; t < TT; ++t) if (lane == t) { v0 = acc[0][t]; v1 = acc[1][t]; }
-      if (W8) { v0 *= a.wscale[ra]; v1 *= a.wscale[rb]; }
+      if (W8) { v0 *= a.wscale[ra] * 256.f; v1 *= a.wscale[rb] * 256.f; }
       if (lane < T) {
         const int t = lane;
         if (EPI == EPI_STORE) {
@@ -275,6 +280,13 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
     }
 #pragma unroll
     for (int j = 0; j < NJ; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
+    if (W8 && nitem < n_items) {
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        unpack16_e4m3(cur[0][j], *reinterpret_cast<float(*)[16]>(&wf[0][j * 16]));
+        unpack16_e4m3(cur[1][j], *reinterpret_cast<float(*)[16]>(&wf[1][j * 16]));
+      }
+    }
   }
 }
 
