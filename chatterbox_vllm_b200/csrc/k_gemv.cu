@@ -21,6 +21,7 @@
 // dot product before the first bf16 rounding point, so y = bf16((x . q) * s) == x . (q * s) up to
 // fp32 summation order — exactly the oracle's "dequantised weights" chain.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -69,6 +70,52 @@ __device__ __forceinline__ void item_rows(int item, int& ra, int& rb) {
   if (EPI == EPI_SILU)      { ra = (item >> 4) * 32 + (item & 15); rb = ra + 16; }   // packed gate/up
   else if (EPI == EPI_ROPE) { ra = (item >> 5) * 64 + (item & 31); rb = ra + 32; }   // rotation partners
   else                      { ra = 2 * item; rb = ra + 1; }
+}
+
+// Epilogue of one (item, row t): v0 / v1 are the finished dot products of weight rows ra / rb.
+template <int EPI>
+__device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int ra, int rb, int t, float v0, float v1) {
+  if (EPI == EPI_STORE) {
+    *reinterpret_cast<uint32_t*>(a.y + (size_t)t * a.ldy + ra) = pack_bf16(v0, v1);
+  } else if (EPI == EPI_SILU) {
+    const float g = round_bf16(v0), u = round_bf16(v1);
+    a.y[(size_t)t * a.ldy + item] = __float2bfloat16_rn(g / (1.f + __expf(-g)) * u);
+  } else if (EPI == EPI_RES) {
+    uint32_t* rp = reinterpret_cast<uint32_t*>(a.y + (size_t)t * 1024 + ra);
+    const uint32_t r = *rp;
+    *rp = pack_bf16(round_bf16(v0) + bf_lo(r), round_bf16(v1) + bf_hi(r));
+  } else {                                        // EPI_ROPE
+    const int head48 = item >> 5, i = item & 31, which = head48 >> 4, h = head48 & 15;
+    float o1 = round_bf16(v0), o2 = round_bf16(v1);
+    if (which < 2) {
+      const int p = a.pos[t];
+      const float c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
+      const float s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
+      const float x1 = o1, x2 = o2;
+      o1 = x1 * c - x2 * s;
+      o2 = x2 * c + x1 * s;
+    }
+    const bf16 b1 = __float2bfloat16_rn(o1), b2 = __float2bfloat16_rn(o2);
+    if (which == 0) {
+      bf16* q = a.y + (size_t)t * 3072 + h * 64;
+      q[i] = b1; q[i + 32] = b2;
+    } else {
+      const int64_t sl = a.slot[t];
+      if (sl >= 0) {
+        uint8_t* page = a.kv_layer + (size_t)(sl / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
+        const int tok = (int)(sl % CBX_BLOCK_SIZE);
+        if (which == 1) {                         // K: 16-byte chunks XOR-swizzled by tok & 7
+          uint8_t* kt = page + h * 2048 + tok * 128;
+          const int c1 = (i >> 3) ^ (tok & 7), c2 = ((i + 32) >> 3) ^ (tok & 7);
+          *reinterpret_cast<bf16*>(kt + c1 * 16 + (i & 7) * 2) = b1;
+          *reinterpret_cast<bf16*>(kt + c2 * 16 + (i & 7) * 2) = b2;
+        } else {
+          bf16* vt = reinterpret_cast<bf16*>(page + 32768 + h * 2048 + tok * 128);
+          vt[i] = b1; vt[i + 32] = b2;
+        }
+      }
+    }
+  }
 }
 
 // TT = padded row count (1,2,4); KSEG = K / 1024 (1 or 4); NW = warps per CTA.
@@ -233,50 +280,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
 #pragma unroll
       for (int t = 0; t < TT; ++t) if (lane == t) { v0 = acc[0][t]; v1 = acc[1][t]; }
       if (W8) { v0 *= a.wscale[ra] * 256.f; v1 *= a.wscale[rb] * 256.f; }
-      if (lane < T) {
-        const int t = lane;
-        if (EPI == EPI_STORE) {
-          *reinterpret_cast<uint32_t*>(a.y + (size_t)t * a.ldy + ra) = pack_bf16(v0, v1);
-        } else if (EPI == EPI_SILU) {
-          const float g = round_bf16(v0), u = round_bf16(v1);
-          a.y[(size_t)t * a.ldy + item] = __float2bfloat16_rn(g / (1.f + __expf(-g)) * u);
-        } else if (EPI == EPI_RES) {
-          uint32_t* rp = reinterpret_cast<uint32_t*>(a.y + (size_t)t * 1024 + ra);
-          const uint32_t r = *rp;
-          *rp = pack_bf16(round_bf16(v0) + bf_lo(r), round_bf16(v1) + bf_hi(r));
-        } else {                                        // EPI_ROPE
-          const int head48 = item >> 5, i = item & 31, which = head48 >> 4, h = head48 & 15;
-          float o1 = round_bf16(v0), o2 = round_bf16(v1);
-          if (which < 2) {
-            const int p = a.pos[t];
-            const float c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
-            const float s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
-            const float x1 = o1, x2 = o2;
-            o1 = x1 * c - x2 * s;
-            o2 = x2 * c + x1 * s;
-          }
-          const bf16 b1 = __float2bfloat16_rn(o1), b2 = __float2bfloat16_rn(o2);
-          if (which == 0) {
-            bf16* q = a.y + (size_t)t * 3072 + h * 64;
-            q[i] = b1; q[i + 32] = b2;
-          } else {
-            const int64_t sl = a.slot[t];
-            if (sl >= 0) {
-              uint8_t* page = a.kv_layer + (size_t)(sl / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
-              const int tok = (int)(sl % CBX_BLOCK_SIZE);
-              if (which == 1) {                         // K: 16-byte chunks XOR-swizzled by tok & 7
-                uint8_t* kt = page + h * 2048 + tok * 128;
-                const int c1 = (i >> 3) ^ (tok & 7), c2 = ((i + 32) >> 3) ^ (tok & 7);
-                *reinterpret_cast<bf16*>(kt + c1 * 16 + (i & 7) * 2) = b1;
-                *reinterpret_cast<bf16*>(kt + c2 * 16 + (i & 7) * 2) = b2;
-              } else {
-                bf16* vt = reinterpret_cast<bf16*>(page + 32768 + h * 2048 + tok * 128);
-                vt[i] = b1; vt[i + 32] = b2;
-              }
-            }
-          }
-        }
-      }
+      if (lane < T) gemv_epilogue<EPI>(a, item, ra, rb, lane, v0, v1);
     }
 #pragma unroll
     for (int j = 0; j < NJ; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
@@ -288,6 +292,173 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       }
     }
   }
+}
+
+// ---- stream-ahead form (experiment, off by default: see stream_mode()) ------------------------------
+// The register form above holds a CTA's weights in ~100 registers x 384-512 threads, so two consecutive
+// kernels of the PDL chain never share an SM: kernel n+1 starts its weight loads only when kernel n's
+// CTA on that SM has exited, and every kernel of the b = 1 step pays its own HBM latency (~2 us of a
+// ~4 us kernel; 27 % of the step's HBM roofline).  Here a CTA's weight rows arrive by cp.async.bulk
+// (UBLKCP) into ITS shared memory, issued at entry, before griddepcontrol.wait; the kernel needs few
+// registers and 16-120 KB of shared memory, so the next two or three kernels of the chain are resident
+// — and streaming — while the current one computes.  A CTA owns `ipc` consecutive items (row pairs);
+// after the wait a warp takes every NW-th item, reading weights with conflict-free 128-bit LDS.
+template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
+__global__ void __launch_bounds__(NW * 32, NW == 8 ? 2 : 4) gemv_stream_kernel(const GemvArgs a, const int ipc) {
+  constexpr int K = KSEG * 1024;
+  constexpr int ES = W8 ? 1 : 2;
+  constexpr int ROWB = K * ES;                         // bytes per weight row
+  constexpr int NQ = ROWB / 512;                       // 128-bit loads per lane per row
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  uint8_t* wsm = smem_raw;                             // [ipc][2][ROWB]
+  uint4* xs = reinterpret_cast<uint4*>(smem_raw + (size_t)ipc * 2 * ROWB);   // [TT][K/8] bf16x8
+  uint64_t* bar = reinterpret_cast<uint64_t*>(xs + TT * (K / 8));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_items = a.N / 2, T = a.T;
+  const int i0 = blockIdx.x * ipc;
+  const int nloc = n_items - i0 < ipc ? n_items - i0 : ipc;
+
+  pdl_trigger();
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_init(bar, 1);
+      fence_barrier_init();
+      mbar_arrive_expect_tx(bar, (uint32_t)(nloc * 2 * ROWB));
+    }
+    __syncwarp();
+    const uint8_t* Wb = reinterpret_cast<const uint8_t*>(a.W);
+    for (int idx = lane; idx < 2 * nloc; idx += 32) {
+      int ra, rb;
+      item_rows<EPI>(i0 + (idx >> 1), ra, rb);
+      bulk_g2s(wsm + (size_t)idx * ROWB, Wb + (size_t)((idx & 1) ? rb : ra) * ROWB, ROWB, bar);
+    }
+  }
+  pdl_wait();
+
+  // ---- prologue: activation rows -> shared memory (bf16)
+  if (PRO == PRO_NORM) {
+    if (warp < TT) {
+      uint4 o[4] = {};
+      if (warp < T) {
+        const uint4* xr = reinterpret_cast<const uint4*>(a.x + (size_t)warp * 1024);
+        const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
+        float f[4][8];
+        float ss = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          unpack8(xr[lane + 32 * i], f[i]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ss += f[i][e] * f[i][e];
+        }
+        ss = warp_sum(ss);
+        const float rstd = rsqrtf(ss * (1.0f / 1024.f) + a.eps);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float w[8];
+          unpack8(wr[lane + 32 * i], w);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[i][e] = round_bf16(f[i][e] * rstd) * w[e];
+          o[i] = make_uint4(pack_bf16(f[i][0], f[i][1]), pack_bf16(f[i][2], f[i][3]), pack_bf16(f[i][4], f[i][5]),
+                            pack_bf16(f[i][6], f[i][7]));
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xs[warp * 128 + lane + 32 * i] = o[i];
+    }
+  } else {
+    for (int i = threadIdx.x; i < TT * (K / 8); i += NW * 32) {
+      const int t = i / (K / 8);
+      xs[i] = t < T ? reinterpret_cast<const uint4*>(a.x)[i] : make_uint4(0, 0, 0, 0);
+    }
+  }
+  __syncthreads();                                     // xs complete; the barrier's init is visible to every warp
+  mbar_wait(bar, 0);                                   // the CTA's weight rows have landed
+
+  for (int it = warp; it < nloc; it += NW) {
+    const uint4* wa = reinterpret_cast<const uint4*>(wsm + (size_t)(2 * it) * ROWB);
+    const uint4* wb = reinterpret_cast<const uint4*>(wsm + (size_t)(2 * it + 1) * ROWB);
+    float acc[2][TT];
+#pragma unroll
+    for (int t = 0; t < TT; ++t) acc[0][t] = acc[1][t] = 0.f;
+#pragma unroll 4
+    for (int q = 0; q < NQ; ++q) {
+      const uint4 va = wa[q * 32 + lane], vb = wb[q * 32 + lane];
+      if (W8) {
+        float fa[16], fb[16];
+        unpack16_e4m3(va, fa);
+        unpack16_e4m3(vb, fb);
+#pragma unroll
+        for (int t = 0; t < TT; ++t) {
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float fx[8];
+            unpack8(xs[t * (K / 8) + (q * 32 + lane) * 2 + c], fx);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              acc[0][t] = fmaf(fa[c * 8 + e], fx[e], acc[0][t]);
+              acc[1][t] = fmaf(fb[c * 8 + e], fx[e], acc[1][t]);
+            }
+          }
+        }
+      } else {
+        float fa[8], fb[8];
+        unpack8(va, fa);
+        unpack8(vb, fb);
+#pragma unroll
+        for (int t = 0; t < TT; ++t) {
+          float fx[8];
+          unpack8(xs[t * (K / 8) + q * 32 + lane], fx);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            acc[0][t] = fmaf(fa[e], fx[e], acc[0][t]);
+            acc[1][t] = fmaf(fb[e], fx[e], acc[1][t]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < TT; ++t) { acc[0][t] = warp_sum(acc[0][t]); acc[1][t] = warp_sum(acc[1][t]); }
+    const int item = i0 + it;
+    int ra, rb;
+    item_rows<EPI>(item, ra, rb);
+    float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+    for (int t = 0; t < TT; ++t) if (lane == t) { v0 = acc[0][t]; v1 = acc[1][t]; }
+    if (W8) { v0 *= a.wscale[ra] * 256.f; v1 *= a.wscale[rb] * 256.f; }
+    if (lane < T) gemv_epilogue<EPI>(a, item, ra, rb, lane, v0, v1);
+  }
+}
+
+// env CBX_GEMV_STREAM=1 selects this form.  OFF by default: parity-green (the whole GPU suite passes on it), but
+// MEASURED SLOWER on B200 — b = 1 p50 step 0.696 ms against 0.614 ms for the register form.  The weight
+// latency it hides was not what bounds the step: the chain is bound by its ~2 us of dependent work per
+// kernel (wait release, x rows from L2, norm, FMAs, shuffles, read-modify-write epilogue, exit flush),
+// to which this form adds the mbarrier wait and a second trip of every weight byte through LDS.
+inline bool stream_mode() {
+  static const bool on = getenv("CBX_GEMV_STREAM") && getenv("CBX_GEMV_STREAM")[0] == '1';
+  return on;
+}
+
+template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
+int launch_stream(const GemvArgs& a, cudaStream_t s) {
+  constexpr int ROWB = KSEG * 1024 * (W8 ? 1 : 2);
+  const int n_items = a.N / 2;
+  // one CTA per SM when the items allow it; at least NW/2 items per CTA so the warps have work
+  int ipc = (n_items + 147) / 148;
+  if (ipc < NW / 2) ipc = NW / 2;
+  const int grid = (n_items + ipc - 1) / ipc;
+  const int smem = ipc * 2 * ROWB + TT * KSEG * 1024 * 2 + 16;
+  static int attr_smem = 0;                            // per instantiation
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(gemv_stream_kernel<TT, KSEG, PRO, EPI, NW, W8>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { set_error("gemv_stream smem attribute (%d B): %s", smem, cudaGetErrorString(e)); return -2; }
+    attr_smem = smem;
+  }
+  cudaError_t e = launch_pdl(gemv_stream_kernel<TT, KSEG, PRO, EPI, NW, W8>, dim3(grid), dim3(NW * 32), smem, s, a, ipc);
+  if (e != cudaSuccess) { set_error("gemv_stream launch failed: %s", cudaGetErrorString(e)); return -2; }
+  count_launch();
+  return 0;
 }
 
 template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
@@ -302,6 +473,11 @@ int launch_w(const GemvArgs& a, int grid, cudaStream_t s) {
 
 template <int TT, int KSEG, int PRO, int EPI, int NW>
 int launch(const GemvArgs& a, int grid, cudaStream_t s) {
+  if (stream_mode()) {
+    // stream-ahead form: 8 warps (4 for the two N = 1024 projections, whose CTAs own 4 items)
+    constexpr int SW = (EPI == EPI_RES) ? 4 : 8;
+    return a.wscale ? launch_stream<TT, KSEG, PRO, EPI, SW, true>(a, s) : launch_stream<TT, KSEG, PRO, EPI, SW, false>(a, s);
+  }
   return a.wscale ? launch_w<TT, KSEG, PRO, EPI, NW, true>(a, grid, s) : launch_w<TT, KSEG, PRO, EPI, NW, false>(a, grid, s);
 }
 
