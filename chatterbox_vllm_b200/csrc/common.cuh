@@ -47,6 +47,11 @@ bool pdl_enabled();                        // env CBX_PDL != "0"
 // read what the previous kernel has not written yet.  A pointer whose first load does not depend on
 // another post-wait load must be laundered after the wait: p = pdl_acquire(p).
 // tools/audit_pdl_hoist.py lists every load that ended up before the wait.
+// A second PDL precaution, in the cache rather than the compiler: a load through a `const T* __restrict__`
+// parameter compiles to LDG.E.CONSTANT — the non-coherent read-only path, which PTX only allows for data
+// that is immutable for the kernel's LIFETIME, and a PDL kernel's lifetime starts while its predecessor is
+// still writing.  Rule: pointers to anything an earlier kernel of the chain writes (activations, kv_len /
+// row_seq / pos / slot, partials, logits) are NOT __restrict__; only weights and tables are.
 template <typename T>
 __device__ __forceinline__ const T* pdl_acquire(const T* p) {
   asm volatile("" : "+l"(p)::"memory");

@@ -57,8 +57,8 @@ int launch_decode_mega(const MegaArgs&, cudaStream_t);
 using namespace cbx;
 
 namespace {
-__global__ void __launch_bounds__(128) gather_rows_kernel(const uint4* __restrict__ src,
-                                                          const int32_t* __restrict__ rows,
+__global__ void __launch_bounds__(128) gather_rows_kernel(const uint4* src,
+                                                          const int32_t* rows,
                                                           uint4* __restrict__ dst) {
   pdl_trigger();
   pdl_wait();

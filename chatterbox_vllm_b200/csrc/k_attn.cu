@@ -53,8 +53,8 @@ inline AttnPlan make_plan(int T, int max_kv_len) {
 // Otherwise partials are merged by attn_merge_kernel (large batches: keeps the page stream busy).
 template <bool kTicket>
 __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
-    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt,
-    int bt_stride, const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len,
+    const bf16* qkv, const uint8_t* __restrict__ kv_layer, const int32_t* bt,
+    int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
     bf16* __restrict__ out, float* __restrict__ o_part, float2* __restrict__ ml_part,
     int32_t* __restrict__ counters, int T, int pps, int nsplit) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
 // them.  In (row, page) order the CTA that holds a row's head reaches it last, so merges fall at the
 // end of a CTA's range rather than in the middle of its page stream.
 // plan (int32): [0] total pages, [1] pages per CTA, [2 + 2c], [3 + 2c] = (row, page) where CTA c starts.
-__global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* __restrict__ kv_len, int T, int G,
+__global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* kv_len, int T, int G,
                                                          int32_t* __restrict__ plan) {
   __shared__ int s_first[kPlanMaxRows + 1];            // s_first[r] = flattened index of row r's first page
   __shared__ int s_warp[32];
@@ -305,10 +305,10 @@ __global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* __restri
 }
 
 __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_bal_kernel(
-    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt,
-    int bt_stride, const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len,
+    const bf16* qkv, const uint8_t* __restrict__ kv_layer, const int32_t* bt,
+    int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
     bf16* __restrict__ out, float* __restrict__ o_part, float2* __restrict__ ml_part,
-    int32_t* __restrict__ counters, const int32_t* __restrict__ plan, int T) {
+    int32_t* __restrict__ counters, const int32_t* plan, int T) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
   uint64_t* empty = full + kStages;
@@ -520,8 +520,8 @@ __device__ __forceinline__ float ld_dsmem_f32(const float* local, uint32_t rank)
 
 template <int S>
 __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
-    const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer, const int32_t* __restrict__ bt, int bt_stride,
-    const int32_t* __restrict__ row_seq, const int32_t* __restrict__ kv_len, bf16* __restrict__ out,
+    const bf16* qkv, const uint8_t* __restrict__ kv_layer, const int32_t* bt, int bt_stride,
+    const int32_t* row_seq, const int32_t* kv_len, bf16* __restrict__ out,
     const void* next_w, size_t next_bytes) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmallMaxPages * 4096);
@@ -661,11 +661,11 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
 // items int32 [n][4] = {row0 (first query row in qkv/out), n_q (1..16), block-table row, qb}.
 __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
 }
 __device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
 }
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -673,8 +673,8 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 }
 
 __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
-    const __grid_constant__ CUtensorMap vmap, const bf16* __restrict__ qkv, const uint8_t* __restrict__ kv_layer,
-    const int32_t* __restrict__ bt, int bt_stride, const int4* __restrict__ items, int n_items, bf16* __restrict__ out) {
+    const __grid_constant__ CUtensorMap vmap, const bf16* qkv, const uint8_t* __restrict__ kv_layer,
+    const int32_t* bt, int bt_stride, const int4* items, int n_items, bf16* __restrict__ out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * CBX_PAGE_BYTES);
   uint64_t* empty = full + kStages;
@@ -702,7 +702,11 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
             mbar_wait(&empty[s], ph ^ 1);
             mbar_arrive_expect_tx(&full[s], CBX_PAGE_BYTES);
             bulk_g2s(smem + s * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, 32768, &full[s]);
+#ifdef CBX_PF_NOSWZ
+            bulk_g2s(smem + s * CBX_PAGE_BYTES + 32768, kv_layer + (size_t)blk * CBX_PAGE_BYTES + 32768, 32768, &full[s]);
+#else
             tma_load_2d(smem + s * CBX_PAGE_BYTES + 32768, &vmap, 0, blk * 512 + 256, &full[s]);
+#endif
           }
           ++it;
         }
@@ -724,10 +728,10 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
       const bool l0 = g < im.y, l1 = g + 8 < im.y;
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
-        qa[ks][0] = l0 ? q0[ks * 8] : 0u;
-        qa[ks][1] = l1 ? q1[ks * 8] : 0u;
-        qa[ks][2] = l0 ? q0[ks * 8 + 4] : 0u;
-        qa[ks][3] = l1 ? q1[ks * 8 + 4] : 0u;
+        qa[ks][0] = l0 ? __ldcg(q0 + ks * 8) : 0u;
+        qa[ks][1] = l1 ? __ldcg(q1 + ks * 8) : 0u;
+        qa[ks][2] = l0 ? __ldcg(q0 + ks * 8 + 4) : 0u;
+        qa[ks][3] = l1 ? __ldcg(q1 + ks * 8 + 4) : 0u;
       }
     }
     float m0 = -INFINITY, m1 = -INFINITY, l0s = 0.f, l1s = 0.f;
@@ -737,6 +741,7 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
     for (int pg = 0; pg <= qb; ++pg, ++it) {
       const uint32_t s = it % kStages, ph = (it / kStages) & 1;
       mbar_wait(&full[s], ph);
+      __syncwarp();                                   // ldmatrix / mma below are .aligned: the warp must be converged after the spin
       const uint32_t kt = smem_u32(smem + s * CBX_PAGE_BYTES + h * 2048);
       const uint32_t vt = kt + 32768;
       // ---- S = Q·K^T: keys 0-7 (sc[0]) and 8-15 (sc[1])
@@ -781,12 +786,22 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
       for (int nd = 0; nd < 8; nd += 2) {
         uint32_t vb[4];
         const int key = (mat & 1) * 8 + r8, chunk = nd + (mat >> 1);
+#ifdef CBX_PF_NOSWZ
+        ldsm_x4_trans(vt + key * 128 + (chunk << 4), vb);
+#else
         ldsm_x4_trans(vt + key * 128 + ((chunk ^ (key & 7)) << 4), vb);
+#endif
         o[nd][0] *= cr0; o[nd][1] *= cr0; o[nd][2] *= cr1; o[nd][3] *= cr1;
         o[nd + 1][0] *= cr0; o[nd + 1][1] *= cr0; o[nd + 1][2] *= cr1; o[nd + 1][3] *= cr1;
         mma_bf16_16816(o[nd], pa, vb[0], vb[1]);
         mma_bf16_16816(o[nd + 1], pa, vb[2], vb[3]);
       }
+      // ptxas is free to schedule the arrive ABOVE the MMAs that consume the last ldmatrix (it did: SASS LDSM,
+      // SYNCS.ARRIVE, HMMA), so nothing guaranteed that the shared-memory read had been performed when the producer
+      // saw the stage empty and let the TMA engine (async proxy) overwrite it: some heads of ~3 % of the rows came
+      // out with a neighbouring page's K/V, differently on every launch.  The proxy fence (MEMBAR.ALL.CTA +
+      // FENCE.VIEW.ASYNC) completes this thread's reads before the release.
+      fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[s]);
     }
@@ -807,9 +822,9 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_prefill_kernel(
 }
 
 // Combine split partials: 256 threads per row, thread = 4 consecutive d of one head.
-__global__ void __launch_bounds__(256) attn_merge_kernel(const float* __restrict__ o_part,
-                                                         const float2* __restrict__ ml_part,
-                                                         const int32_t* __restrict__ kv_len,
+__global__ void __launch_bounds__(256) attn_merge_kernel(const float* o_part,
+                                                         const float2* ml_part,
+                                                         const int32_t* kv_len,
                                                          bf16* __restrict__ out, int pps, int nsplit) {
   const int row = blockIdx.x, t = threadIdx.x, h = t >> 4;
   pdl_trigger();

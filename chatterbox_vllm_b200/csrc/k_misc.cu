@@ -58,8 +58,8 @@ extern "C" int cbx_pool_free(cbx_pool* p, const int32_t* ids, int n) {
 }
 
 // ---------------------------------------------------------------- slot mapping --------
-__global__ void slot_mapping_kernel(const int32_t* __restrict__ bt, int bt_stride,
-                                    const int32_t* __restrict__ req, const int32_t* __restrict__ pos,
+__global__ void slot_mapping_kernel(const int32_t* bt, int bt_stride,
+                                    const int32_t* __restrict__ req, const int32_t* pos,
                                     int64_t* __restrict__ slot, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -83,9 +83,9 @@ extern "C" int cbx_slot_mapping(const int32_t* bt, int bt_stride, const int32_t*
 // One CTA (128 threads) per row r in [0,2B): copies the 2 KB embedding row and thread 0
 // does the row's index arithmetic.
 __global__ void __launch_bounds__(128) decode_prepare_kernel(
-    const uint4* __restrict__ speech_emb, const int32_t* __restrict__ last_tok,
-    const int32_t* __restrict__ finished, const int32_t* __restrict__ seq_len,
-    const int32_t* __restrict__ bt, int bt_stride, uint4* __restrict__ x, int32_t* __restrict__ pos,
+    const uint4* __restrict__ speech_emb, const int32_t* last_tok,
+    const int32_t* finished, const int32_t* seq_len,
+    const int32_t* bt, int bt_stride, uint4* __restrict__ x, int32_t* __restrict__ pos,
     int64_t* __restrict__ slot, int32_t* __restrict__ kv_len, int32_t* __restrict__ row_seq,
     int32_t* __restrict__ head_rows, int B) {
   const int r = blockIdx.x, b = r % B;
@@ -167,7 +167,7 @@ extern "C" int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, con
 // MODE 2: x arrives as `splits` fp32 split-K partials [splits][T][1024] of the projection that
 //         closes the residual branch: x = bf16(sum of partials), then as MODE 1.
 template <int MODE>
-__global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* __restrict__ x, uint4* __restrict__ res,
+__global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* x, uint4* __restrict__ res,
                                                       const uint4* __restrict__ w, uint4* __restrict__ out,
                                                       float eps, int splits, int T) {
   const int r = blockIdx.x, t = threadIdx.x;
@@ -243,8 +243,8 @@ extern "C" int cbx_rmsnorm_reduce(const void* partials, int splits, void* residu
 // Then every thread moves one 16-byte chunk of v.  K chunks land XOR-swizzled (chunk ^
 // (tok & 7)) so the attention kernel's per-token 128-bit reads are bank-conflict-free.
 __global__ void __launch_bounds__(128) rope_kv_append_kernel(uint4* __restrict__ qkv,
-                                                             const int32_t* __restrict__ pos,
-                                                             const int64_t* __restrict__ slot,
+                                                             const int32_t* pos,
+                                                             const int64_t* slot,
                                                              const uint4* __restrict__ cos_sin,
                                                              uint8_t* __restrict__ kv_layer) {
   const int r = blockIdx.x, t = threadIdx.x;
@@ -318,9 +318,9 @@ extern "C" int cbx_pack_gate_up(const void* src, void* dst, int I, int K, void* 
 // SOS (exclusive) and the first EOS; drop ids >= sos (6561); cap at guard_cap (tts.py:466-486).
 // One CTA per request; order-preserving compaction with a ballot scan; int64 out as S3Gen takes it.
 namespace {
-__global__ void __launch_bounds__(256) postprocess_tokens_kernel(const int32_t* __restrict__ out_tokens,
-                                                                 const int32_t* __restrict__ n_out, int out_stride,
-                                                                 const int32_t* __restrict__ slots, int sos, int eos,
+__global__ void __launch_bounds__(256) postprocess_tokens_kernel(const int32_t* out_tokens,
+                                                                 const int32_t* n_out, int out_stride,
+                                                                 const int32_t* slots, int sos, int eos,
                                                                  int tail_crop, const int32_t* __restrict__ guard_cap,
                                                                  int64_t* __restrict__ dst, int dst_stride,
                                                                  const int32_t* __restrict__ dst_rows,

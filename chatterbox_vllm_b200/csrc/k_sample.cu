@@ -222,9 +222,9 @@ __device__ __forceinline__ float cfg_pen(float cc, float uu, float cfg, bool see
 // pair_map == NULL: CTA i samples pair i from logits rows i (cond) and B+i (uncond).
 // pair_map != NULL (admission of new pairs into a running batch): CTA i samples pair pair_map[i] from
 // logits rows i and n_sub+i; every other pair's state is left alone.
-__global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* __restrict__ logits,
+__global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* logits,
                                                                  cbx_sampler_state st, int B, const NextStep nx,
-                                                                 const int32_t* __restrict__ pair_map, int n_sub) {
+                                                                 const int32_t* pair_map, int n_sub) {
   __shared__ Red red;
   __shared__ Radix rx;
   const int tid = threadIdx.x;

@@ -325,7 +325,10 @@ class T3Engine:
             self.buffer("slot", (T,), torch.int64).copy_(ops.slot_mapping(self.block_table, d_rseq, d_pos))
             ops.prefill_embed(d_desc, cond, self.text_emb, self.text_pos, self.speech_emb, self.speech_pos, out=x[:T])
             items = ops.prefill_items(starts, plens, btrows).to(dev)       # causal attention: 16 query rows per item
-            check(load().cbx_engine_set_prefill_items(self._h, items.data_ptr(), items.shape[0]), "set_prefill_items")
+            if os.environ.get("CBX_PREFILL_ROWWISE") == "1":      # debugging aid: causal prefill row by row through the decode kernel
+                items = items[:0]
+            check(load().cbx_engine_set_prefill_items(self._h, items.data_ptr() if items.shape[0] else None, items.shape[0]),
+                  "set_prefill_items")
             try:
                 self.forward(T, max(P[j0:j1]))
             finally:

@@ -580,3 +580,20 @@ def test_engine_long_context_high_block_occupancy(ops):
     assert_stream_parity([got[i] for i in probe], w, [reqs[i] for i in probe], eng.cfg_scale, n_steps, first_exact=0,
                          min_agree=0.85, temperature=0.0, repetition_penalty=2.0)
     eng.close()
+
+
+def test_engine_prefill_and_decode_are_deterministic_at_scale(ops):
+    """Same job twice => same bits, at a size where rows are cut across CTAs, prefill runs in several
+    chunks of tcgen05 pair GEMMs and the attention rings wrap many times (16 pairs x prefix 200, 6 layers,
+    48 steps, greedy + sampled requests mixed)."""
+    from chatterbox_vllm_b200.engine import Request, SamplingParams, T3Engine
+    from chatterbox_vllm_b200.synthetic import random_cond_emb, random_prompt, random_state_dict
+    eng = T3Engine(random_state_dict(6, device="cuda", head_scale=16.0), device="cuda:0", max_pairs=16, max_model_len=320)
+    reqs = []
+    for i in range(16):
+        sp = SamplingParams(temperature=0.0 if i % 4 == 0 else 0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=48, ignore_eos=True)
+        reqs.append(Request(random_prompt(165, seed=i), random_cond_emb(i), sp, uid=1 + i))
+    first = eng.generate(reqs)
+    for _ in range(3):
+        assert eng.generate(reqs) == first
+    eng.close()

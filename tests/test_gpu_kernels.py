@@ -484,3 +484,27 @@ def test_cond_encoder_matches_reference_modules_fp32():
             assert float((got2 - want2).abs().max()) <= COND_REL_TOL * float(want2.abs().max()), f"n_prompt={n2}"
     with pytest.raises(ValueError):
         enc(spk, tok[:0])
+
+
+def test_paged_attention_prefill_is_deterministic(ops):
+    """Regression for a write-after-read race in the prefill attention ring: ptxas scheduled the stage-release
+    mbarrier arrive above the MMAs consuming the last ldmatrix, so the TMA refill of a stage could overtake a
+    shared-memory read still in flight — a few heads of a few 16-row items then saw a neighbouring page, differently
+    on every launch (inside the parity tolerance at test sizes; found by running BASELINE config 2 twice at full
+    size).  Fixed with a proxy fence before the release; identical inputs must now give identical bits."""
+    torch.manual_seed(0)
+    S, P = 32, 200
+    nblk = -(-P // 16)
+    kv = (torch.randn(((S * nblk + 1) * 65536) // 2, device="cuda") * 0.5).to(BF16).view(torch.uint8)
+    bt = torch.zeros(S, 64, dtype=torch.int32, device="cuda")
+    bt[:, :nblk] = (torch.randperm(S * nblk, device="cuda").to(torch.int32) + 1).view(S, nblk)
+    qkv = torch.randn(S * P, 3072, device="cuda").to(BF16)
+    items = ops.prefill_items([i * P for i in range(S)], [P] * S, list(range(S))).cuda()
+    out = torch.zeros(S * P, 1024, dtype=BF16, device="cuda")
+    ref = None
+    for _ in range(12):
+        ops.paged_attn_prefill(qkv, kv, bt, items, out=out)
+        cur = out.clone()
+        if ref is None:
+            ref = cur
+        assert torch.equal(cur, ref), "prefill attention: same inputs, different bits"
