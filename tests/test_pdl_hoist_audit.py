@@ -12,8 +12,9 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "chatterbox_vllm_b200", "libcbx_t3.so")
-# weight prefetch before the wait is the point of these two (k_gemv.cu / k_gemm.cu headers)
-WEIGHT_PREFETCH = ("gemv_fused_kernel", "gemm_tc_kernel")
+# weight prefetch before the wait is the point of these (k_gemv.cu / k_gemm.cu headers); the stream-ahead GEMV
+# experiment issues its weight rows as bulk copies (UBLKCP) there
+WEIGHT_PREFETCH = ("gemv_fused_kernel", "gemv_stream_kernel", "gemm_tc_kernel")
 
 
 @pytest.mark.skipif(shutil.which("cuobjdump") is None or not os.path.exists(SO), reason="needs cuobjdump and the built library")
@@ -23,3 +24,15 @@ def test_no_activation_load_hoisted_above_griddepcontrol_wait():
     flagged = [l for l in out.splitlines() if "before the wait" in l and not l.startswith(WEIGHT_PREFETCH)]
     assert not flagged, "loads hoisted above griddepcontrol.wait:\n" + "\n".join(flagged)
     assert any(l.startswith("paged_attn_decode_bal_kernel") and l.endswith("clean") for l in out.splitlines()), out[:400]
+
+
+@pytest.mark.skipif(shutil.which("cuobjdump") is None or not os.path.exists(SO), reason="needs cuobjdump and the built library")
+def test_no_shared_memory_read_in_flight_when_a_ring_stage_is_released():
+    """Every mbarrier arrive that hands a shared-memory stage back to the TMA producer must come after the warp's
+    LDS / LDSM of that stage have been PERFORMED (their results consumed, or a MEMBAR in between).  ptxas once
+    scheduled the prefill-attention release above the MMAs consuming the last ldmatrix; the refill then overtook
+    the read and a few heads saw the next page (tools/audit_stage_release.py walks the SASS)."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "audit_stage_release.py"), SO], capture_output=True, text=True)
+    assert r.returncode == 0 and "UNSAFE" not in r.stdout, r.stdout
+    for k in ("paged_attn_prefill_kernel", "paged_attn_decode_bal_kernel", "paged_attn_decode_kernel<true>"):
+        assert any(l.startswith(k) and ": ok" in l for l in r.stdout.splitlines()), r.stdout[:600]
