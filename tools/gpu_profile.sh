@@ -2,11 +2,11 @@
 # ncu evidence for the bench step: (1) launch lists with device times (B = 128 pairs and B = 1), (2) --set full
 # captures of the dominant kernels.  Each ncu run follows a plain run of the same command that exited 0.
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --ctx0 204 --no-cpu-baseline --no-e2e --no-b1"
+CMD="python bench.py --steps 2 --warmup 3 --ctx0 204 --no-cpu-baseline --no-e2e --no-b1 --no-fp8"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 echo "launch list rc=$?"
-CMD1="python bench.py --pairs 1 --steps 2 --warmup 3 --ctx0 300 --no-cpu-baseline --no-e2e --no-b1"
+CMD1="python bench.py --pairs 1 --steps 2 --warmup 3 --ctx0 300 --no-cpu-baseline --no-e2e --no-b1 --no-fp8"
 $CMD1 > gpurun_out/plain_b1.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches_B1.csv $CMD1 > gpurun_out/ncu_launches_b1.log 2>&1
 echo "launch list B1 rc=$?"
