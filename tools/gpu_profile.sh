@@ -20,3 +20,11 @@ prof gemm_tc gemm_tc 1000 4                 # decode-sized (M = 256): QKV / O / 
 prof gemm_tc_prefill gemm_tc 300 4          # prefill-sized (M = 16000): tensor-pipe utilisation
 prof paged_attn_prefill paged_attn_prefill 40 2
 prof cfg_sample cfg_sample 2 3
+# FP8-e4m3 weight path (reported separately): launch list of the same step on FP8 weights + the W8 GEMM form
+CMD8="python bench.py --weights fp8_e4m3 --steps 2 --warmup 3 --ctx0 204 --no-cpu-baseline --no-e2e --no-b1"
+$CMD8 > gpurun_out/plain_fp8.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file gpurun_out/launches_fp8.csv $CMD8 > gpurun_out/ncu_launches_fp8.log 2>&1
+echo "launch list fp8 rc=$?"
+$CMD8 > gpurun_out/plain_fp8.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:gemm_tc -s 1000 -c 4 -f -o gpurun_out/prof_gemm_tc_fp8w $CMD8 > gpurun_out/ncu_gemm_tc_fp8w.log 2>&1
+echo "full gemm_tc_fp8w rc=$?"

@@ -37,7 +37,8 @@ for f in sorted(os.listdir(go)):
                        "algorithmic_bytes_same_launch": meta.get("algorithmic_bytes_per_launch"),
                        "source": f"profiles/{tag}_ncu_full_paged_attn_decode.txt"},
                       open(os.path.join(pr, "attn_traffic.json"), "w"))
-for f, out in (("launches.csv", f"{tag}_launches_B128.txt"), ("launches_B1.csv", f"{tag}_launches_B1.txt")):
+for f, out in (("launches.csv", f"{tag}_launches_B128.txt"), ("launches_B1.csv", f"{tag}_launches_B1.txt"),
+               ("launches_fp8.csv", f"{tag}_launches_B128_fp8w.txt")):
     p = os.path.join(go, f)
     if os.path.exists(p):
         txt = subprocess.run([sys.executable, os.path.join(root, "tools", "launch_summary.py"), p], capture_output=True, text=True).stdout
