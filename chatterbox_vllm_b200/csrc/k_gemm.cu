@@ -283,6 +283,15 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
     __syncwarp();
     const int ew = warp & 3;                           // TMEM lane quarter
     if (warp >= 4) pdl_wait();
+    // EPI 2: this row's position / KV slot and its cos|sin line do not depend on the accumulator — fetch them
+    // while the MMAs run (pos -> cos/sin would otherwise be two dependent L2 round trips after the last MMA)
+    int pf_pos = 0;
+    int64_t pf_slot = -1;
+    if (EPI == 2 && m0 + ew * 32 + lane < M) {
+      pf_pos = ea.pos[m0 + ew * 32 + lane];
+      pf_slot = ea.slot[m0 + ew * 32 + lane];
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(ea.cos_sin + (size_t)pf_pos * 64));
+    }
     mbar_wait(tmem_full, 0);
     if (threadIdx.x == 128) PROF(5);
     tc_fence_after();
@@ -300,7 +309,7 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
         const int head48 = (n0 >> 6) + hh, which = head48 >> 4, h = head48 & 15;
         uint32_t o1[16], o2[16];
         if (which < 2) {
-          const int p = ea.pos[row];
+          const int p = pf_pos;
           const uint4* cs = reinterpret_cast<const uint4*>(ea.cos_sin + (size_t)p * 64);
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -331,7 +340,7 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
             dst[4 + c] = make_uint4(o2[4 * c], o2[4 * c + 1], o2[4 * c + 2], o2[4 * c + 3]);
           }
         } else {
-          const int64_t sl = ea.slot[row];
+          const int64_t sl = pf_slot;
           if (sl >= 0) {
             uint8_t* page = ea.kv_layer + (size_t)(sl / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
             const int tok = (int)(sl % CBX_BLOCK_SIZE);

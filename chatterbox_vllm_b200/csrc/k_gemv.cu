@@ -73,8 +73,36 @@ __device__ __forceinline__ void item_rows(int item, int& ra, int& rb) {
 }
 
 // Epilogue of one (item, row t): v0 / v1 are the finished dot products of weight rows ra / rb.
+// Operands of the epilogue that do not depend on the dot products: fetched right after griddepcontrol.wait for a
+// warp's first item, so their L2 round trips (pos -> cos/sin is two dependent ones) overlap the prologue and the
+// FMAs instead of following them on the kernel-to-kernel critical path.
+struct EpiPrefetch {
+  bool valid;
+  uint32_t res;          // EPI_RES: the residual pair
+  float c, s;            // EPI_ROPE: cos / sin of (pos[t], i)
+  int64_t slot;          // EPI_ROPE: KV slot of row t
+};
+
 template <int EPI>
-__device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int ra, int rb, int t, float v0, float v1) {
+__device__ __forceinline__ EpiPrefetch gemv_epilogue_prefetch(const GemvArgs& a, int item, int t) {
+  EpiPrefetch pf = {true, 0u, 1.f, 0.f, -1};
+  if (EPI == EPI_RES) {
+    pf.res = *reinterpret_cast<const uint32_t*>(a.y + (size_t)t * 1024 + 2 * item);
+  } else if (EPI == EPI_ROPE) {
+    const int head48 = item >> 5, i = item & 31, which = head48 >> 4;
+    if (which < 2) {
+      const int p = a.pos[t];
+      pf.c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
+      pf.s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
+    }
+    if (which > 0) pf.slot = a.slot[t];
+  }
+  return pf;
+}
+
+template <int EPI>
+__device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int ra, int rb, int t, float v0, float v1,
+                                              const EpiPrefetch pf = EpiPrefetch{false, 0u, 1.f, 0.f, -1}) {
   if (EPI == EPI_STORE) {
     *reinterpret_cast<uint32_t*>(a.y + (size_t)t * a.ldy + ra) = pack_bf16(v0, v1);
   } else if (EPI == EPI_SILU) {
@@ -82,15 +110,19 @@ __device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int r
     a.y[(size_t)t * a.ldy + item] = __float2bfloat16_rn(g / (1.f + __expf(-g)) * u);
   } else if (EPI == EPI_RES) {
     uint32_t* rp = reinterpret_cast<uint32_t*>(a.y + (size_t)t * 1024 + ra);
-    const uint32_t r = *rp;
+    const uint32_t r = pf.valid ? pf.res : *rp;
     *rp = pack_bf16(round_bf16(v0) + bf_lo(r), round_bf16(v1) + bf_hi(r));
   } else {                                        // EPI_ROPE
     const int head48 = item >> 5, i = item & 31, which = head48 >> 4, h = head48 & 15;
     float o1 = round_bf16(v0), o2 = round_bf16(v1);
     if (which < 2) {
-      const int p = a.pos[t];
-      const float c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
-      const float s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
+      float c, s;
+      if (pf.valid) { c = pf.c; s = pf.s; }
+      else {
+        const int p = a.pos[t];
+        c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
+        s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
+      }
       const float x1 = o1, x2 = o2;
       o1 = x1 * c - x2 * s;
       o2 = x2 * c + x1 * s;
@@ -100,7 +132,7 @@ __device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int r
       bf16* q = a.y + (size_t)t * 3072 + h * 64;
       q[i] = b1; q[i + 32] = b2;
     } else {
-      const int64_t sl = a.slot[t];
+      const int64_t sl = pf.valid ? pf.slot : a.slot[t];
       if (sl >= 0) {
         uint8_t* page = a.kv_layer + (size_t)(sl / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
         const int tok = (int)(sl % CBX_BLOCK_SIZE);
@@ -161,6 +193,10 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
     }
   }
   pdl_wait();
+  EpiPrefetch pf = {false, 0u, 1.f, 0.f, -1};
+  const int item_first = item;
+  if ((EPI == EPI_RES || EPI == EPI_ROPE) && item < n_items && kseg == 0 && lane < T)
+    pf = gemv_epilogue_prefetch<EPI>(a, item, lane);
 
   // ---- prologue: activation rows -> shared memory (bf16)
   if (PRO == PRO_NORM) {
@@ -280,7 +316,10 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
 #pragma unroll
       for (int t = 0; t < TT; ++t) if (lane == t) { v0 = acc[0][t]; v1 = acc[1][t]; }
       if (W8) { v0 *= a.wscale[ra] * 256.f; v1 *= a.wscale[rb] * 256.f; }
-      if (lane < T) gemv_epilogue<EPI>(a, item, ra, rb, lane, v0, v1);
+      if (lane < T) {
+        if (item == item_first) gemv_epilogue<EPI>(a, item, ra, rb, lane, v0, v1, pf);
+        else gemv_epilogue<EPI>(a, item, ra, rb, lane, v0, v1);
+      }
     }
 #pragma unroll
     for (int j = 0; j < NJ; ++j) { cur[0][j] = nxt[0][j]; cur[1][j] = nxt[1][j]; }
