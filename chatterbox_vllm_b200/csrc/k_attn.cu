@@ -534,14 +534,20 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
   if (threadIdx.x < kSmallMaxPages) mbar_init(&bars[threadIdx.x], 1);
   fence_barrier_init();
   l2_prefetch_slice(next_w, next_bytes);              // a later projection's weights -> L2 while we wait
+  // Page ids of this CTA's share of the row, read BEFORE the wait: the block table is written at admission and
+  // row_seq is re-staged with the same value every step, so neither depends on the kernels this one waits for —
+  // kv_len (how many of the ids are live) does, and is read after the wait.  Takes the row_seq -> block-table
+  // round trips off the kernel-to-kernel critical path (one of the designed pre-wait loads, see the SASS audit).
+  int pre_blk = 0;
+  if (warp == 0 && rank + lane * S < bt_stride) pre_blk = bt[(int64_t)row_seq[row] * bt_stride + rank + lane * S];
   __syncthreads();
   pdl_wait();
 
-  const int len = kv_len[row];
+  const int len = pdl_acquire(kv_len)[row];
   const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
   const int n_local = n_pages > rank ? (n_pages - rank + S - 1) / S : 0;   // pages rank, rank+S, ...
   if (warp == 0 && lane < n_local) {
-    const int blk = bt[(int64_t)row_seq[row] * bt_stride + rank + lane * S];
+    const int blk = pre_blk;
     const uint8_t* src = kv_layer + (size_t)blk * CBX_PAGE_BYTES + h * 2048;
     mbar_arrive_expect_tx(&bars[lane], 4096);
     bulk_g2s(smem + lane * 4096, src, 2048, &bars[lane]);
