@@ -543,7 +543,18 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
   __syncthreads();
   pdl_wait();
 
-  const int len = pdl_acquire(kv_len)[row];
+  // q and kv_len are requested together (both come from the awaited kernels); nothing consumes either before both
+  // loads are in flight, so the page copies start one L2 round trip after the wait, not two
+  const int t16 = lane & 15, half = lane >> 4;        // QK mapping
+  const int tg = lane >> 3, c = lane & 7;             // PV mapping
+  const float qscale = 0.125f * kLog2e;
+  uint4 qraw[4];
+  {
+    const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) qraw[i] = qp[i];
+  }
+  const int len = kv_len[row];
   const int n_pages = (len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
   const int n_local = n_pages > rank ? (n_pages - rank + S - 1) / S : 0;   // pages rank, rank+S, ...
   if (warp == 0 && lane < n_local) {
@@ -553,20 +564,14 @@ __global__ void __launch_bounds__(kSmallWarps * 32) paged_attn_small_kernel(
     bulk_g2s(smem + lane * 4096, src, 2048, &bars[lane]);
     bulk_g2s(smem + lane * 4096 + 2048, src + 32768, 2048, &bars[lane]);
   }
-  const int t16 = lane & 15, half = lane >> 4;        // QK mapping
-  const int tg = lane >> 3, c = lane & 7;             // PV mapping
-  const float qscale = 0.125f * kLog2e;
   float q[32];
-  {
-    const uint4* qp = reinterpret_cast<const uint4*>(qkv + (size_t)row * 3072 + h * 64 + half * 32);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint4 v = qp[i];
-      q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
-      q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
-      q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
-      q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
-    }
+  for (int i = 0; i < 4; ++i) {
+    const uint4 v = qraw[i];
+    q[i * 8 + 0] = bf_lo(v.x) * qscale; q[i * 8 + 1] = bf_hi(v.x) * qscale;
+    q[i * 8 + 2] = bf_lo(v.y) * qscale; q[i * 8 + 3] = bf_hi(v.y) * qscale;
+    q[i * 8 + 4] = bf_lo(v.z) * qscale; q[i * 8 + 5] = bf_hi(v.z) * qscale;
+    q[i * 8 + 6] = bf_lo(v.w) * qscale; q[i * 8 + 7] = bf_hi(v.w) * qscale;
   }
   float m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll

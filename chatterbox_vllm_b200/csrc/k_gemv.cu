@@ -81,28 +81,36 @@ struct EpiPrefetch {
   uint32_t res;          // EPI_RES: the residual pair
   float c, s;            // EPI_ROPE: cos / sin of (pos[t], i)
   int64_t slot;          // EPI_ROPE: KV slot of row t
+  int pos;               // EPI_ROPE: position of row t (first-level load; cos / sin follow in phase B)
 };
 
+// phase A, right after the wait: loads whose addresses are known
 template <int EPI>
 __device__ __forceinline__ EpiPrefetch gemv_epilogue_prefetch(const GemvArgs& a, int item, int t) {
-  EpiPrefetch pf = {true, 0u, 1.f, 0.f, -1};
+  EpiPrefetch pf = {true, 0u, 1.f, 0.f, -1, 0};
   if (EPI == EPI_RES) {
     pf.res = *reinterpret_cast<const uint32_t*>(a.y + (size_t)t * 1024 + 2 * item);
   } else if (EPI == EPI_ROPE) {
-    const int head48 = item >> 5, i = item & 31, which = head48 >> 4;
-    if (which < 2) {
-      const int p = a.pos[t];
-      pf.c = __bfloat162float(a.cos_sin[(size_t)p * 64 + i]);
-      pf.s = __bfloat162float(a.cos_sin[(size_t)p * 64 + 32 + i]);
-    }
+    const int which = item >> 9;                       // (item >> 5) >> 4
+    if (which < 2) pf.pos = a.pos[t];
     if (which > 0) pf.slot = a.slot[t];
   }
   return pf;
 }
+// phase B, after the activation rows have been requested: the loads that depend on phase A (cos / sin of pos) —
+// placed earlier they would stall the in-order issue of everything behind them for one L2 round trip
+template <int EPI>
+__device__ __forceinline__ void gemv_epilogue_prefetch2(const GemvArgs& a, int item, EpiPrefetch& pf) {
+  if (EPI == EPI_ROPE && (item >> 9) < 2) {
+    const int i = item & 31;
+    pf.c = __bfloat162float(a.cos_sin[(size_t)pf.pos * 64 + i]);
+    pf.s = __bfloat162float(a.cos_sin[(size_t)pf.pos * 64 + 32 + i]);
+  }
+}
 
 template <int EPI>
 __device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int ra, int rb, int t, float v0, float v1,
-                                              const EpiPrefetch pf = EpiPrefetch{false, 0u, 1.f, 0.f, -1}) {
+                                              const EpiPrefetch pf = EpiPrefetch{false, 0u, 1.f, 0.f, -1, 0}) {
   if (EPI == EPI_STORE) {
     *reinterpret_cast<uint32_t*>(a.y + (size_t)t * a.ldy + ra) = pack_bf16(v0, v1);
   } else if (EPI == EPI_SILU) {
@@ -193,10 +201,10 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
     }
   }
   pdl_wait();
-  EpiPrefetch pf = {false, 0u, 1.f, 0.f, -1};
+  EpiPrefetch pf = {false, 0u, 1.f, 0.f, -1, 0};
   const int item_first = item;
-  if ((EPI == EPI_RES || EPI == EPI_ROPE) && item < n_items && kseg == 0 && lane < T)
-    pf = gemv_epilogue_prefetch<EPI>(a, item, lane);
+  const bool do_pf = (EPI == EPI_RES || EPI == EPI_ROPE) && item < n_items && kseg == 0 && lane < T;
+  if (do_pf) pf = gemv_epilogue_prefetch<EPI>(a, item, lane);
 
   // ---- prologue: activation rows -> shared memory (bf16)
   if (PRO == PRO_NORM) {
@@ -234,6 +242,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       xs[i] = t < T ? reinterpret_cast<const uint4*>(a.x)[i] : make_uint4(0, 0, 0, 0);
     }
   }
+  if (do_pf) gemv_epilogue_prefetch2<EPI>(a, item_first, pf);
   __syncthreads();
 
   // ---- main loop over this warp's items (CTA-uniform trip count when KSEG > 1)
