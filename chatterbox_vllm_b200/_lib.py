@@ -73,6 +73,7 @@ _PROTOS = {
     "cbx_layer_gate_up": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
     "cbx_head_logits": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
     "cbx_cfg_sample": (C.c_int, [vp, C.POINTER(SamplerState), C.c_int, vp]),
+    "cbx_debug_sampler_radix_pivot": (C.c_int, [C.c_int]),
     "cbx_decode_prepare": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_prefill_embed": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_cond_workspace_bytes": (C.c_int64, [C.c_int]),

@@ -38,7 +38,7 @@ __device__ __forceinline__ uint32_t fkey(float f) {      // order-preserving flo
 }
 
 struct Red {
-  float f[kWarps];
+  float f[kWarps], g[kWarps];
   int i[kWarps];
   uint32_t u[kWarps];
 };
@@ -81,16 +81,25 @@ __device__ __forceinline__ void block_argmax(float& v, int& idx, Red& red) {
   __syncthreads();
 }
 // exclusive prefix sum of one int per thread in thread order; also returns the block total
-__device__ __forceinline__ int block_excl_scan(int v, int& total, Red& red) {
+// block_sum(a), block_sum(b) and an exclusive block scan of v behind ONE barrier pair (same summation orders as the separate
+// forms, so the same bits): a block barrier of 1024 threads costs ~450-900 cycles here (tools/dbg_sampler_stamps.py).
+__device__ __forceinline__ int block_sum2_excl_scan(float& a, float& b, int v, int& total, Red& red) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  a = warp_sum(a);
+  b = warp_sum(b);
   int incl = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const int t = __shfl_up_sync(0xffffffffu, incl, o);
     if (lane >= o) incl += t;
   }
-  if (lane == 31) red.i[w] = incl;
+  // one storing lane: with lane 0 and lane 31 both storing at index w, nvcc 12.9 formed the address as base + (tid >> 3)
+  // — right for lane 0 only — and lane 31 faulted with "misaligned address"
+  const int warp_incl = __shfl_sync(0xffffffffu, incl, 31);
+  if (lane == 0) { red.f[w] = a; red.g[w] = b; red.i[w] = warp_incl; }
   __syncthreads();
+  a = warp_sum(red.f[lane]);
+  b = warp_sum(red.g[lane]);
   int wt = red.i[lane], winc = wt;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -129,12 +138,13 @@ struct Radix {
   unsigned long long above, target;
   int digit;
 };
-__device__ __forceinline__ void bin_add(Radix& rx, int d, unsigned long long w) {
+__device__ __forceinline__ void bin_add(uint32_t* lo, uint32_t* hi, int d, unsigned long long w) {
   const uint32_t wl = (uint32_t)w, wh = (uint32_t)(w >> 32);
-  const uint32_t old = atomicAdd(&rx.lo[d], wl);
+  const uint32_t old = atomicAdd(&lo[d], wl);
   const uint32_t carry = (old + wl < old) ? 1u : 0u;   // exactly one adder sees each wrap
-  if (wh | carry) atomicAdd(&rx.hi[d], wh + carry);
+  if (wh | carry) atomicAdd(&hi[d], wh + carry);
 }
+__device__ __forceinline__ void bin_add(Radix& rx, int d, unsigned long long w) { bin_add(rx.lo, rx.hi, d, w); }
 __device__ __forceinline__ unsigned long long quant40(float e) { return __float2ull_rz(e * 1099511627776.f); }
 
 template <bool kCount>
@@ -213,6 +223,90 @@ __device__ uint32_t radix_select(const float (&l)[NP], const float (&e)[NP], uin
   return n_pass == 0 ? kmax : prefix;
 }
 
+// Top-p pivot without the radix passes (each costs 5-9 k cycles on the one SM a pair has: four block barriers, a
+// 10-element loop in 1024 threads and a serial scan in warp 0; four of them were half of the launch).
+//   1. one histogram over kNB LINEAR buckets of (mt - l): monotone in l, so a bucket boundary is a threshold in l; only
+//      ids whose integer weight e*2^40 is non-zero take part (d < 28), and they spread over the buckets instead of
+//      crowding into the few (sign, exponent) digits of a float key;
+//   2. one 64-bit block scan finds the bucket in which the descending cumulative weight reaches the target;
+//   3. the bucket's members (a few dozen) are gathered and ranked all-pairs on their EXACT keys: the pivot is the key
+//      with  above < target <= above + weight(key)  — the same key the radix passes return, weights are integers so
+//      no order of addition matters.
+// More than kCap members (near-constant logits): the radix passes take over.
+constexpr int kNB = kThreads, kCap = 256;
+constexpr float kBucketScale = (float)kNB / 28.f;
+struct Bucket {
+  uint32_t lo[kNB], hi[kNB];
+  unsigned long long wsum[kWarps], mw[kCap];
+  uint32_t mkey[kCap];
+  unsigned long long above, target;
+  int bucket, cnt;
+  uint32_t pivot;
+};
+__device__ __forceinline__ int bucket_of(float mt, float l) { return min(kNB - 1, (int)((mt - l) * kBucketScale)); }
+
+__device__ uint32_t bucket_select(const float (&l)[NP], const float (&e)[NP], float mt, uint32_t kmax, float top_p, Bucket& bk,
+                                  Radix& rx, Red& red) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  bk.lo[tid] = 0; bk.hi[tid] = 0;
+  if (tid == 0) bk.cnt = 0;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < NP; ++j) {
+    const unsigned long long w = quant40(e[j]);
+    if (w) bin_add(bk.lo, bk.hi, bucket_of(mt, l[j]), w);
+  }
+  __syncthreads();
+  const unsigned long long v = ((unsigned long long)bk.hi[tid] << 32) | bk.lo[tid];
+  unsigned long long incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  const unsigned long long warp_incl = __shfl_sync(0xffffffffu, incl, 31);    // lane 0 stores: see block_sum2_excl_scan
+  if (lane == 0) bk.wsum[warp] = warp_incl;
+  __syncthreads();
+  const unsigned long long wt = bk.wsum[lane];
+  unsigned long long winc = wt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long t = __shfl_up_sync(0xffffffffu, winc, o);
+    if (lane >= o) winc += t;
+  }
+  const unsigned long long total = __shfl_sync(0xffffffffu, winc, 31);
+  const unsigned long long excl = __shfl_sync(0xffffffffu, winc - wt, warp) + incl - v;
+  unsigned long long target = (unsigned long long)((double)top_p * (double)total);
+  if (target < 1) target = 1;
+  if (excl < target && excl + v >= target) { bk.bucket = tid; bk.above = excl; bk.target = target; }   // exactly one bucket
+  __syncthreads();
+  const int pb = bk.bucket;
+#pragma unroll
+  for (int j = 0; j < NP; ++j) {
+    const unsigned long long w = quant40(e[j]);
+    if (w && bucket_of(mt, l[j]) == pb) {
+      const int pos = atomicAdd(&bk.cnt, 1);
+      if (pos < kCap) { bk.mkey[pos] = fkey(l[j]); bk.mw[pos] = w; }
+    }
+  }
+  __syncthreads();
+  const int n = bk.cnt;
+  if (n > kCap) return radix_select<false>(l, e, kmax, 0ull, top_p, rx, red);
+  if (tid < n) {
+    const uint32_t ki = bk.mkey[tid];
+    unsigned long long a = bk.above, eq = 0;
+    for (int j = 0; j < n; ++j) {
+      const uint32_t kj = bk.mkey[j];
+      const unsigned long long wj = bk.mw[j];
+      if (kj > ki) a += wj;
+      else if (kj == ki) eq += wj;
+    }
+    if (a < bk.target && a + eq >= bk.target) bk.pivot = ki;            // ties write the same key
+  }
+  __syncthreads();
+  return bk.pivot;
+}
+
 __device__ __forceinline__ float cfg_pen(float cc, float uu, float cfg, bool seen, float rep, float inv_rep) {
   float v = round_bf16(cc + round_bf16(cfg * round_bf16(cc - uu)));   // t3.py:732, one bf16 rounding per op
   if (seen) v = v * (v > 0.f ? inv_rep : rep);                         // _custom_ops.py:360-373
@@ -222,11 +316,15 @@ __device__ __forceinline__ float cfg_pen(float cc, float uu, float cfg, bool see
 // pair_map == NULL: CTA i samples pair i from logits rows i (cond) and B+i (uncond).
 // pair_map != NULL (admission of new pairs into a running batch): CTA i samples pair pair_map[i] from
 // logits rows i and n_sub+i; every other pair's state is left alone.
+// kRadixPivot = true: the top-p pivot comes from the radix passes instead of bucket_select — the checker build of the
+// same kernel (cbx_debug_sampler_radix_pivot), against which the GPU tests require bit-identical tokens.
+template <bool kRadixPivot>
 __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* logits,
                                                                  cbx_sampler_state st, int B, const NextStep nx,
                                                                  const int32_t* pair_map, int n_sub) {
   __shared__ Red red;
   __shared__ Radix rx;
+  __shared__ Bucket bk;
   const int tid = threadIdx.x;
   pdl_trigger();
   pdl_wait();
@@ -306,7 +404,8 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
     // ---- top-p: keep token iff the mass ranked strictly above it is < p
     if (top_p < 1.0f) {
       const float target = top_p * z;
-      const uint32_t kp = radix_select<false>(l, e, kmax, 0ull, top_p, rx, red);
+      const uint32_t kp = kRadixPivot ? radix_select<false>(l, e, kmax, 0ull, top_p, rx, red)
+                                      : bucket_select(l, e, mt, kmax, top_p, bk, rx, red);
       float g = 0.f, pv = 0.f; int nt = 0;
 #pragma unroll
       for (int j = 0; j < NP; ++j) {
@@ -314,10 +413,8 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
         if (k > kp && l[j] != -INFINITY) g += e[j];
         else if (k == kp) { ++nt; pv += e[j]; }
       }
-      g = block_sum(g, red);
-      pv = block_sum(pv, red);                            // = (#ties)·e(v*)
-      int total;
-      const int before = block_excl_scan(nt, total, red);  // tie rank in id order
+      int total;                                          // g, pv = (#ties)·e(v*), tie rank in id order
+      const int before = block_sum2_excl_scan(g, pv, nt, total, red);
       const float ev = total > 0 ? pv / (float)total : 0.f;
       int n_keep = total;
       if (ev > 0.f) {
@@ -342,7 +439,10 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
     float best = -1.f; int bi = V;
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
-      if (e[j] > 0.f) {
+      // The kept maximum has e = 1 and 1 <= z <= 8194, so its score is >= (1/8194)/17.4 (-log u <= 25 ln 2); an element
+      // with e < 1e-14 scores <= 1e-14/2.98e-8 (-log u >= 2^-25): it can never win, and skipping it keeps denormal
+      // e / z (the slow path of the IEEE division, +10 us on peaked logits) out of the loop.  Same winner, bit for bit.
+      if (e[j] >= 1e-14f) {
         const int i = id0 + j;
         const uint32_t x = philox_word0((uint32_t)i, step, (uint32_t)uid, (uint32_t)(uid >> 32), (uint32_t)seed,
                                         (uint32_t)(seed >> 32));
@@ -387,19 +487,21 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
 }  // namespace
 
 namespace cbx {
+static int g_radix_pivot = 0;
 int init_sample() { return 0; }
 
 int launch_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, const NextStep& nx, cudaStream_t s,
                       const int32_t* pair_map, int n_sub) {
   if (B <= 0 || (pair_map && n_sub <= 0)) return 0;
-  cudaError_t e = launch_pdl(cfg_sample_kernel, dim3(pair_map ? n_sub : B), dim3(kThreads), 0, s, (const bf16*)logits, *st,
-                             B, nx, pair_map, n_sub);
+  cudaError_t e = launch_pdl(g_radix_pivot ? cfg_sample_kernel<true> : cfg_sample_kernel<false>, dim3(pair_map ? n_sub : B),
+                             dim3(kThreads), 0, s, (const bf16*)logits, *st, B, nx, pair_map, n_sub);
   CBX_REQUIRE(e == cudaSuccess, "cfg_sample launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
 }
 }  // namespace cbx
 
+extern "C" int cbx_debug_sampler_radix_pivot(int on) { cbx::g_radix_pivot = on; return 0; }
 extern "C" int cbx_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, void* stream) {
   return cbx::launch_cfg_sample(logits, st, B, cbx::NextStep(), (cudaStream_t)stream, nullptr, 0);
 }

@@ -182,6 +182,10 @@ typedef struct cbx_sampler_state {
   int out_stride; int stop_token; float cfg_scale;
 } cbx_sampler_state;
 int cbx_cfg_sample(const void* logits, const cbx_sampler_state* st, int B, void* stream);
+/* Test hook: on != 0 makes every later sampler launch of this process find the top-p pivot with the MSB-first radix passes
+ * (the first implementation, kept as the fallback for near-constant rows) instead of the bucket histogram + exact
+ * ranking; both must emit the same tokens bit for bit (tests/test_gpu_engine.py). */
+int cbx_debug_sampler_radix_pivot(int on);
 
 /* t3.py:503-514 (decode) — x[r] = speech_emb[last_tok[r % B]] for r in [0,2B), plus the
  * per-step index work: pos[r] = seq_len[r]; slot[r] from the block table (-1 for finished

@@ -103,6 +103,45 @@ def test_sampler_random_matches_oracle_stream(ops, kw):
     assert agree >= 0.97 * B, f"only {agree}/{B} rows match the oracle stream"
 
 
+@pytest.mark.parametrize("kw", [dict(temperature=0.5, top_p=0.5, scale=0.65), dict(temperature=0.5, top_p=0.5, scale=10.0),
+                                dict(temperature=0.3, top_p=0.1), dict(temperature=1.0, top_p=0.9, quantize=True),
+                                dict(temperature=1.0, top_p=0.999, scale=1.0), dict(temperature=0.7, top_p=0.8, min_p=0.02),
+                                dict(temperature=0.5, top_p=0.5, top_k=40, quantize=True)])
+def test_sampler_bucket_pivot_equals_radix_pivot(ops, kw):
+    """The top-p pivot found by the bucket histogram + exact ranking is the key the MSB-first radix passes find: the
+    same launch with the radix form (cbx_debug_sampler_radix_pivot) must emit the same token in every row.  Rows 0-5
+    are degenerate on purpose: constant logits and two-valued logits put thousands of ids into one bucket (the radix
+    fallback inside bucket_select), a single dominant id leaves one member, -inf-like tails leave zero weights."""
+    from chatterbox_vllm_b200._lib import load
+    B = 128
+    quant = kw.pop("quantize", False)
+    scale = kw.pop("scale", 3.0)
+    logits, sb, _, _ = _sampler_case(ops, B, 11, quantize=quant, scale=scale, **kw)
+    g = torch.Generator().manual_seed(5)
+    two = torch.where(torch.rand(8194, generator=g) < 0.3, 2.0, 1.5).to(BF16).cuda()
+    for half in (0, B):
+        logits[half + 0, :8194] = 1.25
+        logits[half + 1, :8194] = two
+        logits[half + 2, :8194] = -3.0
+        logits[half + 2, 777] = 30.0
+        logits[half + 3, :4000] = -120.0
+        logits[half + 4, :8194] = two * 40
+        logits[half + 5, :8194] = 0.0
+    toks = []
+    try:
+        for radix in (0, 1):
+            load().cbx_debug_sampler_radix_pivot(radix)
+            sb.n_out.fill_(3), sb.finished.zero_(), sb.n_finished.zero_()
+            seen0 = sb.seen.clone()                    # the bitmap gains the emitted token: restored for the second form
+            ops.cfg_sample(logits, sb, B)
+            toks.append(sb.last_tok.cpu().numpy().copy())
+            sb.seen.copy_(seen0)
+    finally:
+        load().cbx_debug_sampler_radix_pivot(0)
+    assert (toks[0] == toks[1]).all(), np.nonzero(toks[0] != toks[1])[0][:10]
+    assert ((toks[0] >= 0) & (toks[0] < 8194)).all()
+
+
 def test_sampler_distribution_chi2(ops):
     """4096 independent draws (different uid per row) of one distribution."""
     B = 4096
