@@ -32,6 +32,24 @@ struct NextStep {             // optional fused "decode_prepare" for the followi
 }  // namespace cbx
 namespace {
 
+// Loads pinned where they are written (asm volatile): nvcc otherwise sinks them below the early exit / next to their
+// first use, which puts one more L2 round trip into the serial chain of this one-CTA-per-pair kernel.
+__device__ __forceinline__ uint4 ld_now_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_now_u32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint64_t ld_now_u64(const void* p) {
+  uint64_t v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+  return v;
+}
+
 __device__ __forceinline__ uint32_t fkey(float f) {      // order-preserving float -> uint32
   const uint32_t u = __float_as_uint(f);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
@@ -329,22 +347,39 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
   pdl_trigger();
   pdl_wait();
   const int b = pair_map ? pair_map[blockIdx.x] : (int)blockIdx.x;
-  if (st.finished[b]) return;
-  const int n_prev = st.n_out[b];
-  const int len_c = st.seq_len[b], len_u = st.seq_len[B + b];
-  const float rep = st.rep_pen[b], cfg = st.cfg_scale, inv_rep = 1.0f / rep;
-  const float temp = st.temperature[b], min_p = st.min_p[b], top_p = st.top_p[b];
-  const int top_k = st.top_k[b];
-
-  // ---- load: ids [8·tid, 8·tid+8) (+ 8192, 8193 on the last thread); CFG merge + repetition penalty
+  // the two logits rows and the seen byte are requested BEFORE the finished flag is looked at: one L2 round trip for the
+  // whole prologue instead of two (a finished pair's loads are simply dropped)
   const bf16* lc = logits + (size_t)(pair_map ? blockIdx.x : b) * CBX_LOGITS_LD;
   const bf16* lu = logits + (size_t)(pair_map ? n_sub + blockIdx.x : B + b) * CBX_LOGITS_LD;
   const uint32_t* seen = st.seen + (size_t)b * CBX_SEEN_WORDS;
+  const uint4 vc = ld_now_u4(reinterpret_cast<const uint4*>(lc) + tid), vu = ld_now_u4(reinterpret_cast<const uint4*>(lu) + tid);
+  const uint32_t seen_word = ld_now_u32(seen + (tid >> 2));
+  const uint64_t seed = ld_now_u64(st.seed + b), uid = ld_now_u64(st.uid + b);     // used by the race, 10 us later
+  const int n_prev = (int)ld_now_u32(st.n_out + b);
+  const int len_c = (int)ld_now_u32(st.seq_len + b), len_u = (int)ld_now_u32(st.seq_len + B + b);
+  const float rep = __uint_as_float(ld_now_u32(st.rep_pen + b)), cfg = st.cfg_scale;
+  const float temp = __uint_as_float(ld_now_u32(st.temperature + b)), min_p = __uint_as_float(ld_now_u32(st.min_p + b));
+  const float top_p = __uint_as_float(ld_now_u32(st.top_p + b));
+  const int top_k = (int)ld_now_u32(st.top_k + b);
+  const int max_out = (int)ld_now_u32(st.max_out + b), ignore_eos = (int)ld_now_u32(st.ignore_eos + b);
+  int next_block = 0;                                      // block-table entry of the NEXT position (known before sampling)
+  if (nx.res != nullptr && (tid == 0 || tid == 128)) {
+    const int p = (tid ? len_u : len_c) + 1;
+    next_block = (int)ld_now_u32(nx.bt + (int64_t)((tid >> 7) * B + b) * nx.bt_stride + p / CBX_BLOCK_SIZE);
+  }
+  uint32_t tail_c = 0, tail_u = 0, tail_seen = 0;          // ids 8192, 8193 live on the last thread
+  if (tid == kThreads - 1) {
+    tail_c = ld_now_u32(lc + 8192), tail_u = ld_now_u32(lu + 8192);
+    tail_seen = ld_now_u32(seen + CBX_SEEN_WORDS - 1);
+  }
+  if (ld_now_u32(st.finished + b)) return;     // volatile like the loads above, so it cannot be scheduled ahead of them
+  const float inv_rep = 1.0f / rep;
+
+  // ---- load: ids [8·tid, 8·tid+8) (+ 8192, 8193 on the last thread); CFG merge + repetition penalty
   const int id0 = tid * 8;
   float l[NP], e[NP];
   {
-    const uint4 vc = reinterpret_cast<const uint4*>(lc)[tid], vu = reinterpret_cast<const uint4*>(lu)[tid];
-    const uint32_t sb = (seen[tid >> 2] >> ((tid & 3) * 8)) & 0xffu;
+    const uint32_t sb = (seen_word >> ((tid & 3) * 8)) & 0xffu;
     const uint32_t cw[4] = {vc.x, vc.y, vc.z, vc.w}, uw[4] = {vu.x, vu.y, vu.z, vu.w};
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -354,10 +389,8 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
     }
     l[8] = l[9] = -INFINITY;
     if (tid == kThreads - 1) {
-      const uint32_t sw = seen[CBX_SEEN_WORDS - 1];
-#pragma unroll
-      for (int j = 0; j < 2; ++j)
-        l[8 + j] = cfg_pen(__bfloat162float(lc[8192 + j]), __bfloat162float(lu[8192 + j]), cfg, (sw >> j) & 1u, rep, inv_rep);
+      l[8] = cfg_pen(bf_lo(tail_c), bf_lo(tail_u), cfg, tail_seen & 1u, rep, inv_rep);
+      l[9] = cfg_pen(bf_hi(tail_c), bf_hi(tail_u), cfg, (tail_seen >> 1) & 1u, rep, inv_rep);
     }
   }
   // ---- greedy argmax on the penalised logits (ties -> lowest id)
@@ -434,7 +467,6 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
       z = block_sum(z2, red);
     }
     // ---- exponential race over survivors: argmax (e_i / z) / Exp(1)_i   (topk_topp_sampler.py:395-416)
-    const uint64_t seed = st.seed[b], uid = st.uid[b];
     const uint32_t step = (uint32_t)n_prev;
     float best = -1.f; int bi = V;
 #pragma unroll
@@ -455,7 +487,7 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
     tok = bi;
   }
 
-  const bool fin = (tok == st.stop_token && !st.ignore_eos[b]) || n_prev + 1 >= st.max_out[b];
+  const bool fin = (tok == st.stop_token && !ignore_eos) || n_prev + 1 >= max_out;
   if (nx.res != nullptr && tid < 256) {
     // ---- next decode step's inputs (t3.py:503-514 + block_table.py:357-377): both pair members are
     // fed speech_emb[tok]; position = the slot this token's K/V will occupy.
@@ -466,8 +498,7 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
       nx.pos[r] = p;
       nx.row_seq[r] = r;
       nx.kv_len[r] = fin ? 0 : p + 1;
-      nx.slot[r] = fin ? (int64_t)-1
-                       : (int64_t)nx.bt[(int64_t)r * nx.bt_stride + p / CBX_BLOCK_SIZE] * CBX_BLOCK_SIZE + p % CBX_BLOCK_SIZE;
+      nx.slot[r] = fin ? (int64_t)-1 : (int64_t)next_block * CBX_BLOCK_SIZE + p % CBX_BLOCK_SIZE;
     }
   }
   // ---- emit + bookkeeping (one thread)
@@ -475,7 +506,7 @@ __global__ void __launch_bounds__(kThreads, 1) cfg_sample_kernel(const bf16* log
     st.out_tokens[(size_t)b * st.out_stride + n_prev] = tok;
     st.n_out[b] = n_prev + 1;
     st.last_tok[b] = tok;
-    st.seen[(size_t)b * CBX_SEEN_WORDS + (tok >> 5)] |= 1u << (tok & 31);
+    atomicOr(&st.seen[(size_t)b * CBX_SEEN_WORDS + (tok >> 5)], 1u << (tok & 31));   // RED.OR: no read round trip before exit
     st.seq_len[b] = len_c + 1;
     st.seq_len[B + b] = len_u + 1;
     if (fin) {
