@@ -175,6 +175,8 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* x, uint4* __r
   const uint4 wv = w[t];                               // weights: independent of the previous kernel
   pdl_wait();
   float f[8];
+  uint4 q = make_uint4(0, 0, 0, 0);                   // requested with the first loads, not after the slice loop
+  if (MODE >= 1) q = res[(size_t)r * 128 + t];
   if (MODE == 2) {
     const float4* p = reinterpret_cast<const float4*>(x) + ((size_t)r * 128 + t) * 2;
     float4 a = p[0], b = p[1];
@@ -191,7 +193,6 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* x, uint4* __r
     f[4] = bf_lo(v.z); f[5] = bf_hi(v.z); f[6] = bf_lo(v.w); f[7] = bf_hi(v.w);
   }
   if (MODE >= 1) {
-    uint4 q = res[(size_t)r * 128 + t];
     float g[8] = {bf_lo(q.x), bf_hi(q.x), bf_lo(q.y), bf_hi(q.y), bf_lo(q.z), bf_hi(q.z), bf_lo(q.w), bf_hi(q.w)};
 #pragma unroll
     for (int i = 0; i < 8; ++i) f[i] = round_bf16(f[i] + g[i]);
@@ -212,6 +213,39 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* x, uint4* __r
   out[(size_t)r * 128 + t] =
       make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
+// The engine's form (o_proj / down_proj leave 4 K-slices): 256 threads per row, four elements each, so a thread has just
+// five loads — residual + one float4 per slice — and they are all in flight together.  The general kernel above, with
+// eight elements per thread and the slice loop left to the compiler, fetched in four register-reusing waves plus the
+// residual at the end: five L2 round trips in a kernel that is nothing but latency.  Same order of adds per element.
+__global__ void __launch_bounds__(256) rmsnorm_reduce4_kernel(const float4* part, uint2* res, const uint2* __restrict__ w,
+                                                              uint2* out, float eps, int T) {
+  const int r = blockIdx.x, t = threadIdx.x;
+  pdl_trigger();
+  uint2 wv;                                            // weights: independent of the previous kernel.  ld.volatile, or ptxas
+  asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(wv.x), "=r"(wv.y) : "l"(w + t));   // sinks it to its use
+  pdl_wait();
+  const float4* p = part + (size_t)r * 256 + t;
+  const size_t zs = (size_t)T * 256;
+  const uint2 q = res[(size_t)r * 256 + t];
+  const float4 a0 = p[0], a1 = p[zs], a2 = p[2 * zs], a3 = p[3 * zs];
+  float f[4] = {round_bf16(((a0.x + a1.x) + a2.x) + a3.x), round_bf16(((a0.y + a1.y) + a2.y) + a3.y),
+                round_bf16(((a0.z + a1.z) + a2.z) + a3.z), round_bf16(((a0.w + a1.w) + a2.w) + a3.w)};
+  const float g[4] = {bf_lo(q.x), bf_hi(q.x), bf_lo(q.y), bf_hi(q.y)};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) f[i] = round_bf16(f[i] + g[i]);
+  res[(size_t)r * 256 + t] = make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]));
+  float ss = (f[0] * f[0] + f[1] * f[1]) + (f[2] * f[2] + f[3] * f[3]);
+  ss = warp_sum(ss);
+  __shared__ float sums[8];
+  if ((t & 31) == 0) sums[t >> 5] = ss;
+  __syncthreads();
+  const float tot = ((sums[0] + sums[1]) + (sums[2] + sums[3])) + ((sums[4] + sums[5]) + (sums[6] + sums[7]));
+  const float rstd = rsqrtf(tot * (1.0f / CBX_HIDDEN) + eps);
+  const float wf[4] = {bf_lo(wv.x), bf_hi(wv.x), bf_lo(wv.y), bf_hi(wv.y)};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) f[i] = round_bf16(f[i] * rstd) * wf[i];
+  out[(size_t)r * 256 + t] = make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]));
+}
 extern "C" int cbx_rmsnorm(const void* x, void* residual, const void* w, void* out, int T, float eps,
                            void* stream) {
   if (T <= 0) return 0;
@@ -230,8 +264,11 @@ extern "C" int cbx_rmsnorm_reduce(const void* partials, int splits, void* residu
                                   float eps, void* stream) {
   if (T <= 0) return 0;
   CBX_REQUIRE(splits >= 1 && residual != nullptr, "cbx_rmsnorm_reduce: bad arguments");
-  cudaError_t e = launch_pdl(rmsnorm_kernel<2>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)partials,
-                             (uint4*)residual, (const uint4*)w, (uint4*)out, eps, splits, T);
+  cudaError_t e = splits == 4
+      ? launch_pdl(rmsnorm_reduce4_kernel, dim3(T), dim3(256), 0, (cudaStream_t)stream, (const float4*)partials,
+                   (uint2*)residual, (const uint2*)w, (uint2*)out, eps, T)
+      : launch_pdl(rmsnorm_kernel<2>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)partials,
+                   (uint4*)residual, (const uint4*)w, (uint4*)out, eps, splits, T);
   CBX_REQUIRE(e == cudaSuccess, "rmsnorm_reduce launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
