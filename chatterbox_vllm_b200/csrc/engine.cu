@@ -28,7 +28,8 @@ int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t, const
 int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, cudaStream_t, const void* next_w = nullptr,
                       size_t next_bytes = 0, const float* wscale = nullptr);
 void attn_set_prefetch(const void*, size_t);
-int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
+int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
+              const int32_t* row_seq);
 int paged_attn_decode_ex(const void*, const void*, const int32_t*, int, const int32_t*, const int32_t*, void*, void*, int32_t*,
                          int, int, bool, void*);
 int gemv_norm_head(const void*, const void*, const void*, void*, int, int, int, float, cudaStream_t, const float* wscale = nullptr);
@@ -294,7 +295,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
   bool pending = false;                                // down-proj partials not yet folded into res
   // decode attention cuts the step's pages into equal per-CTA ranges: one plan serves all layers
   static const bool plan_each = getenv("CBX_ATTN_PLAN_EACH") != nullptr;   // debugging aid: rebuild the plan per layer
-  const bool have_plan = !plan_each && e->n_prefill_items == 0 && !(sk & 2) && attn_plan(e->kv_len, T, e->attn_scratch, s) == 0;
+  const bool have_plan = !plan_each && e->n_prefill_items == 0 && !(sk & 2) && attn_plan(e->kv_len, T, e->attn_scratch, s, e->block_table, e->bt_stride, e->row_seq) == 0;
   const bool pf = e->l2_prefetch;
   for (int li = 0; li < e->w.n_layers; ++li) {
     uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;

@@ -31,7 +31,9 @@ constexpr float kLog2e = 1.4426950408889634f;
 
 // balanced variant: 2 partial slots per CTA (o fp32 [1024], (m, l) per head), then the range plan
 constexpr int kPlanMaxRows = 4095;              // 1024 threads x 4 rows, and entry [T] for the total
-constexpr int kPlanInts = 2 + 2 * 148;
+constexpr int kPlanFirst = 2 + 2 * 148;         // [kPlanFirst] = 1 when the first-page ids below are filled in
+constexpr int kPrimed = 3;                      // = kStages of the balanced kernel: the first ring fill
+constexpr int kPlanInts = kPlanFirst + 1 + kPrimed * 148;
 constexpr int64_t kBalScratchBytes = 2 * 148 * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + kPlanInts * 4 + 256;
 
 struct AttnPlan { int pps; int nsplit; };
@@ -244,9 +246,13 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_kernel(
 // CTA, slot 1 for a row continued by the next — and the CTA holding the row's last ticket merges
 // them.  In (row, page) order the CTA that holds a row's head reaches it last, so merges fall at the
 // end of a CTA's range rather than in the middle of its page stream.
-// plan (int32): [0] total pages, [1] pages per CTA, [2 + 2c], [3 + 2c] = (row, page) where CTA c starts.
+// plan (int32): [0] total pages, [1] pages per CTA, [2 + 2c], [3 + 2c] = (row, page) where CTA c starts;
+// [kPlanFirst] = 1 and [kPlanFirst + 1 + 3c + j] = physical id of the j-th page of CTA c's stream when the block table is
+// given: the attention producer then issues its first ring fill straight after reading the plan, instead of after two more
+// dependent L2 round trips (kv_len / row_seq of its start row, then the block-table entries) — per launch, 30 per step.
 __global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* kv_len, int T, int G,
-                                                         int32_t* __restrict__ plan) {
+                                                         int32_t* __restrict__ plan, const int32_t* bt, int bt_stride,
+                                                         const int32_t* row_seq) {
   __shared__ int s_first[kPlanMaxRows + 1];            // s_first[r] = flattened index of row r's first page
   __shared__ int s_warp[32];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -301,7 +307,17 @@ __global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* kv_len, 
       row = lo; page = g0 - s_first[lo];
     }
     plan[2 + 2 * t] = row; plan[3 + 2 * t] = page;
+    if (bt != nullptr) {                               // the first kPrimed pages of this range, in stream order
+      const int n = min(kPrimed, min(q, total - g0));
+      int r = row, pg = page;
+      for (int j = 0; j < n; ++j) {
+        while (r < T && pg >= s_first[r + 1] - s_first[r]) { ++r; pg = 0; }
+        plan[kPlanFirst + 1 + kPrimed * t + j] = r < T ? bt[(int64_t)row_seq[r] * bt_stride + pg] : 0;
+        ++pg;
+      }
+    }
   }
+  if (t == 0) plan[kPlanFirst] = bt != nullptr ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_bal_kernel(
@@ -325,14 +341,36 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_bal_kernel(
   plan = pdl_acquire(plan);
   kv_len = pdl_acquire(kv_len);
 
-  const int total = plan[0], per = plan[1];
+  // everything this CTA needs from the plan in ONE round trip: ld.volatile keeps the six loads together (plain loads were
+  // scheduled behind the branches that use them: flag -> branch -> ids, two more dependent trips)
+  auto ld_now = [](const int32_t* p) {
+    int v;
+    asm volatile("ld.volatile.global.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+  };
+  const int total = ld_now(plan), per = ld_now(plan + 1);
+  int row = ld_now(plan + 2 + 2 * blockIdx.x), pg = ld_now(plan + 3 + 2 * blockIdx.x);
+  const int has_first = ld_now(plan + kPlanFirst);
+  const int first_blk = ld_now(plan + kPlanFirst + 1 + kPrimed * blockIdx.x + min(lane, kPrimed - 1));
   const int g0 = min((int)blockIdx.x * per, total);
   int rem = min(per, total - g0);                      // pages this CTA still has to stream
-  int row = plan[2 + 2 * blockIdx.x], pg = plan[3 + 2 * blockIdx.x];
   uint32_t it = 0;
 
   if (warp == kConsumerWarps) {
     // ------------------------------------------------------------ producer warp
+    // first ring fill from the page ids the plan kernel resolved (one L2 round trip after the wait instead of three)
+    static_assert(kPrimed == kStages, "the primed copies are exactly the first ring fill: no empty-barrier wait");
+    uint32_t primed = 0;
+    if (has_first) {
+      primed = (uint32_t)max(0, min(kPrimed, rem));
+      for (uint32_t j = 0; j < primed; ++j) {
+        const int blk = __shfl_sync(0xffffffffu, first_blk, j);
+        if (lane == 0) {
+          mbar_arrive_expect_tx(&full[j], CBX_PAGE_BYTES);
+          bulk_g2s(smem + j * CBX_PAGE_BYTES, kv_layer + (size_t)blk * CBX_PAGE_BYTES, CBX_PAGE_BYTES, &full[j]);
+        }
+      }
+    }
     while (rem > 0) {
       const int n_pages = (kv_len[row] + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
       if (n_pages == 0) { ++row; continue; }
@@ -343,7 +381,7 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attn_decode_bal_kernel(
         const int my_blk = lane < nb ? btr[pb + lane] : 0;
         for (int j = 0; j < nb; ++j) {
           const int blk = __shfl_sync(0xffffffffu, my_blk, j);
-          if (lane == 0) {
+          if (lane == 0 && it >= primed) {
             const uint32_t s = it % kStages, ph = (it / kStages) & 1;
             mbar_wait(&empty[s], ph ^ 1);
             mbar_arrive_expect_tx(&full[s], CBX_PAGE_BYTES);
@@ -901,7 +939,8 @@ void attn_set_prefetch(const void* w, size_t bytes) { g_next_w = w; g_next_bytes
 int paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                          const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch, int32_t* counters,
                          int T, int max_kv_len, bool have_plan, void* stream);
-int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
+int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
+              const int32_t* row_seq);
 static bool balanced_on() {
   static const bool on = !(getenv("CBX_ATTN_BALANCED") && getenv("CBX_ATTN_BALANCED")[0] == '0');
   return on;
@@ -912,9 +951,13 @@ static int32_t* plan_of(void* scratch) {
 }
 // Page-range plan shared by every layer of a decode step (kv_len is the same for all 30 launches).
 // Returns 1 when the balanced variant does not apply to T rows.
-int cbx::attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream) {
+// block_table / row_seq (may be NULL): when given, each range's first pages are resolved here, once for all layers.
+int cbx::attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
+                   const int32_t* row_seq) {
   if (T <= 4 || T > kPlanMaxRows || !balanced_on() || scratch == nullptr) return 1;
-  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, 148, plan_of(scratch));
+  if (row_seq == nullptr) block_table = nullptr;
+  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, 148, plan_of(scratch),
+                             block_table, bt_stride, row_seq);
   CBX_REQUIRE(e == cudaSuccess, "attn_plan launch failed: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
@@ -927,7 +970,7 @@ extern "C" int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, cons
 }
 extern "C" int cbx_attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream) {
   if (T <= 0 || cbx::init_attn()) return -1;
-  return cbx::attn_plan(kv_len, T, scratch, stream);
+  return cbx::attn_plan(kv_len, T, scratch, stream, nullptr, 0, nullptr);
 }
 extern "C" int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_layer, const int32_t* block_table,
                                              int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
@@ -965,7 +1008,7 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
   }
   if (T > 4 && T <= kPlanMaxRows && balanced_on()) {
     CBX_REQUIRE(scratch != nullptr && counters != nullptr, "cbx_paged_attn_decode: scratch / counters is NULL");
-    if (!have_plan && attn_plan(kv_len, T, scratch, stream)) return -1;
+    if (!have_plan && attn_plan(kv_len, T, scratch, stream, block_table, bt_stride, row_seq)) return -1;
     float* o_part = reinterpret_cast<float*>(scratch);
     float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)2 * 148 * CBX_HIDDEN);
     cudaError_t e = launch_pdl(paged_attn_decode_bal_kernel, dim3(max_ctas), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,
