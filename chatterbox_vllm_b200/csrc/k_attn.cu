@@ -309,11 +309,19 @@ __global__ void __launch_bounds__(1024) attn_plan_kernel(const int32_t* kv_len, 
     plan[2 + 2 * t] = row; plan[3 + 2 * t] = page;
     if (bt != nullptr) {                               // the first kPrimed pages of this range, in stream order
       const int n = min(kPrimed, min(q, total - g0));
-      int r = row, pg = page;
-      for (int j = 0; j < n; ++j) {
+      int r = row, pg = page, rr[kPrimed], pp[kPrimed], sq[kPrimed];
+#pragma unroll
+      for (int j = 0; j < kPrimed; ++j) {              // (row, page) of the three pages from shared memory only ...
         while (r < T && pg >= s_first[r + 1] - s_first[r]) { ++r; pg = 0; }
-        plan[kPlanFirst + 1 + kPrimed * t + j] = r < T ? bt[(int64_t)row_seq[r] * bt_stride + pg] : 0;
+        rr[j] = min(r, T - 1); pp[j] = r < T ? pg : 0;
         ++pg;
+      }
+#pragma unroll
+      for (int j = 0; j < kPrimed; ++j) sq[j] = row_seq[rr[j]];          // ... then two rounds of three loads, not six in a chain
+#pragma unroll
+      for (int j = 0; j < kPrimed; ++j) {
+        const int blk = bt[(int64_t)sq[j] * bt_stride + pp[j]];
+        if (j < n) plan[kPlanFirst + 1 + kPrimed * t + j] = blk;
       }
     }
   }
