@@ -141,7 +141,19 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on STDOUT at communicator creation when NCCL_DEBUG asks for it; the contract is
+        # ONE JSON line there, so stdout points at stderr until the communicator exists
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     B, K, W = args.pairs, args.steps, args.warmup
     L0 = max(PREFIX + 1 + W, PREFIX + GEN // 2 - K // 2)        # context at the first timed step
     if args.ctx0 is not None:
