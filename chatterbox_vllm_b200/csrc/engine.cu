@@ -324,8 +324,18 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                                          last ? (size_t)CBX_SPEECH_VOCAB * 1024 * 2 : (size_t)3072 * 1024 * 2, e->sgu[li])) return -1;
       if (!(sk & 16) && gemv_residual(e->act, e->wd[li], e->res, T, 4096, s, nullptr, 0, e->sd[li])) return -1;
     } else if (splits > 1) {
-      if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s, e->so[li])) return -1;
-      if (cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
+      static const bool o_unsplit = getenv("CBX_O_UNSPLIT") && getenv("CBX_O_UNSPLIT")[0] == '1';   // experiment
+      static const bool o_split2 = getenv("CBX_O_UNSPLIT") && getenv("CBX_O_UNSPLIT")[0] == '2';    // experiment: 2 K-slices
+      if (o_split2 && splits == 4) {
+        if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, 2, s, e->so[li])) return -1;
+        if (cbx_rmsnorm_reduce(e->part, 2, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
+      } else if (o_unsplit) {
+        if (!(sk & 4) && gemm_residual(e->attn, e->wo[li], e->res, T, 1024, 1024, s, e->so[li])) return -1;
+        if (cbx_rmsnorm(e->res, nullptr, e->ln2[li], e->h, T, eps, s)) return -1;
+      } else {
+        if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s, e->so[li])) return -1;
+        if (cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
+      }
       if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s, e->sgu[li])) return -1;
       if (!(sk & 16) && gemm_partials(e->act, e->wd[li], e->part, T, 1024, 4096, splits, s, e->sd[li])) return -1;
       pending = true;

@@ -217,6 +217,7 @@ __global__ void __launch_bounds__(128) rmsnorm_kernel(const uint4* x, uint4* __r
 // five loads — residual + one float4 per slice — and they are all in flight together.  The general kernel above, with
 // eight elements per thread and the slice loop left to the compiler, fetched in four register-reusing waves plus the
 // residual at the end: five L2 round trips in a kernel that is nothing but latency.  Same order of adds per element.
+template <int S>
 __global__ void __launch_bounds__(256) rmsnorm_reduce4_kernel(const float4* part, uint2* res, const uint2* __restrict__ w,
                                                               uint2* out, float eps, int T) {
   const int r = blockIdx.x, t = threadIdx.x;
@@ -227,9 +228,13 @@ __global__ void __launch_bounds__(256) rmsnorm_reduce4_kernel(const float4* part
   const float4* p = part + (size_t)r * 256 + t;
   const size_t zs = (size_t)T * 256;
   const uint2 q = res[(size_t)r * 256 + t];
-  const float4 a0 = p[0], a1 = p[zs], a2 = p[2 * zs], a3 = p[3 * zs];
-  float f[4] = {round_bf16(((a0.x + a1.x) + a2.x) + a3.x), round_bf16(((a0.y + a1.y) + a2.y) + a3.y),
-                round_bf16(((a0.z + a1.z) + a2.z) + a3.z), round_bf16(((a0.w + a1.w) + a2.w) + a3.w)};
+  float4 a[S];
+#pragma unroll
+  for (int z = 0; z < S; ++z) a[z] = p[z * zs];
+  float4 sum = a[0];
+#pragma unroll
+  for (int z = 1; z < S; ++z) { sum.x += a[z].x; sum.y += a[z].y; sum.z += a[z].z; sum.w += a[z].w; }
+  float f[4] = {round_bf16(sum.x), round_bf16(sum.y), round_bf16(sum.z), round_bf16(sum.w)};
   const float g[4] = {bf_lo(q.x), bf_hi(q.x), bf_lo(q.y), bf_hi(q.y)};
 #pragma unroll
   for (int i = 0; i < 4; ++i) f[i] = round_bf16(f[i] + g[i]);
@@ -265,7 +270,10 @@ extern "C" int cbx_rmsnorm_reduce(const void* partials, int splits, void* residu
   if (T <= 0) return 0;
   CBX_REQUIRE(splits >= 1 && residual != nullptr, "cbx_rmsnorm_reduce: bad arguments");
   cudaError_t e = splits == 4
-      ? launch_pdl(rmsnorm_reduce4_kernel, dim3(T), dim3(256), 0, (cudaStream_t)stream, (const float4*)partials,
+      ? launch_pdl(rmsnorm_reduce4_kernel<4>, dim3(T), dim3(256), 0, (cudaStream_t)stream, (const float4*)partials,
+                   (uint2*)residual, (const uint2*)w, (uint2*)out, eps, T)
+      : splits == 2
+      ? launch_pdl(rmsnorm_reduce4_kernel<2>, dim3(T), dim3(256), 0, (cudaStream_t)stream, (const float4*)partials,
                    (uint2*)residual, (const uint2*)w, (uint2*)out, eps, T)
       : launch_pdl(rmsnorm_kernel<2>, dim3(T), dim3(128), 0, (cudaStream_t)stream, (const uint4*)partials,
                    (uint4*)residual, (const uint4*)w, (uint4*)out, eps, splits, T);
