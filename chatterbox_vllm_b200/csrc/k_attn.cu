@@ -980,6 +980,11 @@ extern "C" int cbx_attn_plan(const int32_t* kv_len, int T, void* scratch, void* 
   if (T <= 0 || cbx::init_attn()) return -1;
   return cbx::attn_plan(kv_len, T, scratch, stream, nullptr, 0, nullptr);
 }
+extern "C" int cbx_attn_plan_paged(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table,
+                                   int bt_stride, const int32_t* row_seq) {
+  if (T <= 0 || cbx::init_attn()) return -1;
+  return cbx::attn_plan(kv_len, T, scratch, stream, block_table, bt_stride, row_seq);
+}
 extern "C" int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_layer, const int32_t* block_table,
                                              int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
                                              void* scratch, int32_t* counters, int T, int max_kv_len, void* stream) {

@@ -138,7 +138,8 @@ def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: i
         _attn_planned.pop(key, None)
     fn = load().cbx_paged_attn_decode
     if plan == "make":
-        rc = load().cbx_attn_plan(_p(kv_len, torch.int32), T, _p(ws[0]), _stream())
+        rc = load().cbx_attn_plan_paged(_p(kv_len, torch.int32), T, _p(ws[0]), _stream(), _p(block_table, torch.int32),
+                                        block_table.stride(0), _p(row_seq, torch.int32))
         if rc < 0:
             check(rc, "attn_plan")
         _attn_planned[key] = T if rc == 0 else 0

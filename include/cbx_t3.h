@@ -129,6 +129,11 @@ int cbx_paged_attn_decode(const void* qkv, const void* kv_layer, const int32_t* 
  * cbx_paged_attn_decode) and launches each layer with cbx_paged_attn_decode_planned.
  * cbx_paged_attn_decode builds the plan itself on every call. */
 int cbx_attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream);
+/* Same, with the block table the layers will use: the plan then also holds the first three physical page ids of every
+ * range, so each layer's attention launch starts its page stream one L2 round trip after its wait instead of three.
+ * block_table / row_seq must be the ones later passed to cbx_paged_attn_decode_planned. */
+int cbx_attn_plan_paged(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table,
+                        int bt_stride, const int32_t* row_seq);
 int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_layer, const int32_t* block_table,
                                   int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
                                   void* out, void* scratch, int32_t* counters, int T, int max_kv_len,
