@@ -189,6 +189,14 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
 #pragma unroll
     for (int j = 0; j < NJ; ++j) { cur[0][j] = ld_stream(wa + j * 32); cur[1][j] = ld_stream(wb + j * 32); }
   }
+  // RMSNorm weights of the norm prologue: also independent of the previous kernel.  Left where they are used they were
+  // fetched after the row's sum of squares — one more L2 round trip on the critical path of three kernels per layer.
+  uint4 lnw[4] = {};
+  if (PRO == PRO_NORM && warp < TT) {
+    const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) lnw[i] = ld_stream(wr + lane + 32 * i);
+  }
   l2_prefetch_slice(a.next_w, a.next_bytes);
   // W8: the first item's bytes are widened to fp32 BEFORE the wait (3.5 ops per weight that would otherwise sit on
   // the kernel-to-kernel critical path; measured +0.1 us per kernel at b = 1)
@@ -212,7 +220,6 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
       uint4 o[4] = {};
       if (warp < T) {
         const uint4* xr = reinterpret_cast<const uint4*>(a.x + (size_t)warp * 1024);
-        const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
         float f[4][8];
         float ss = 0.f;
 #pragma unroll
@@ -226,7 +233,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           float w[8];
-          unpack8(wr[lane + 32 * i], w);
+          unpack8(lnw[i], w);
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[i][e] = round_bf16(f[i][e] * rstd) * w[e];
           o[i] = make_uint4(pack_bf16(f[i][0], f[i][1]), pack_bf16(f[i][2], f[i][3]), pack_bf16(f[i][4], f[i][5]),
