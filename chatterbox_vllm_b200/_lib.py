@@ -64,6 +64,7 @@ _PROTOS = {
     "cbx_attn_scratch_bytes": (C.c_int64, [C.c_int, C.c_int]),
     "cbx_attn_num_splits": (C.c_int, [C.c_int, C.c_int]),
     "cbx_paged_attn_decode": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_paged_attn_decode_static": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, vp]),
     "cbx_attn_plan": (C.c_int, [vp, C.c_int, vp, vp]),
     "cbx_attn_plan_paged": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, vp]),
     "cbx_paged_attn_decode_planned": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),

@@ -1058,6 +1058,51 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
   return 0;
 }
 
+// ---- allocation-free decode attention ----------------------------------------------------------
+// No counterpart in the reference; added for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The
+// balanced kernel's scratch (2 partial slots per CTA + the page-range plan) and the per-row ticket
+// counters live in ONE file-scope device array, kStaticScratchBytes on every GPU that loads the
+// library.  The array's name is a host-side stand-in in host code: the device address is resolved
+// once per device with cudaGetSymbolAddress (with that device current) and passed to the kernels.
+namespace {
+constexpr int kStaticMaxRows = kPlanMaxRows;                                       // 4095 query rows
+constexpr size_t kStaticPartBytes = ((size_t)kBalScratchBytes + 255) / 256 * 256;  // partials + plan
+constexpr size_t kStaticScratchBytes = kStaticPartBytes + (size_t)(kStaticMaxRows + 1) * 4;   // + tickets
+constexpr int kStaticMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) unsigned char g_attn_static_scratch[kStaticScratchBytes];
+static unsigned char* g_attn_static_ptr[kStaticMaxDevices];   // device address of the array, per device ordinal
+
+extern "C" int cbx_paged_attn_decode_static(const void* qkv, const void* kv_layer, const int32_t* block_table,
+                                            int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
+                                            int T, int max_kv_len, void* stream) {
+  if (T == 0) return 0;
+  CBX_REQUIRE(T > 4 && T <= kStaticMaxRows,
+              "cbx_paged_attn_decode_static: T=%d outside 5..%d rows (the static scratch is sized for the balanced "
+              "kernel; T <= 4 needs no scratch: call cbx_paged_attn_decode with scratch = NULL)", T, kStaticMaxRows);
+  CBX_REQUIRE(cbx::balanced_on(), "cbx_paged_attn_decode_static: CBX_ATTN_BALANCED=0 disables the kernel this entry uses");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  CBX_REQUIRE(e == cudaSuccess && dev >= 0 && dev < kStaticMaxDevices, "cbx_paged_attn_decode_static: cudaGetDevice: %s",
+              cudaGetErrorString(e));
+  if (g_attn_static_ptr[dev] == nullptr) {            // set-up, once per device, that device current
+    unsigned char* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_attn_static_scratch);
+    CBX_REQUIRE(e == cudaSuccess && p != nullptr, "cbx_paged_attn_decode_static: cudaGetSymbolAddress: %s",
+                cudaGetErrorString(e));
+    g_attn_static_ptr[dev] = p;
+  }
+  unsigned char* base = g_attn_static_ptr[dev];
+  int32_t* counters = reinterpret_cast<int32_t*>(base + kStaticPartBytes);
+  // every call shares the array and it keeps the last call's contents: the tickets must start at zero (a launch that
+  // ran to completion leaves them zero, one that was aborted does not); partials and plan are written before being read
+  e = cudaMemsetAsync(counters, 0, (size_t)T * 4, (cudaStream_t)stream);
+  CBX_REQUIRE(e == cudaSuccess, "cbx_paged_attn_decode_static: clearing the tickets: %s", cudaGetErrorString(e));
+  return cbx::paged_attn_decode_ex(qkv, kv_layer, block_table, bt_stride, row_seq, kv_len, out, base, counters, T,
+                                   max_kv_len, false, stream);
+}
+
 // Causal attention for prefill rows whose K/V are already in the cache (vllm flash_attn.py:796-800,
 // prefill form).  items: device int32 [n_items][4] = {row0, n_q, block-table row, query block}.
 extern "C" int cbx_paged_attn_prefill(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,

@@ -151,6 +151,16 @@ def paged_attn_decode(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: i
     return out
 
 
+def paged_attn_decode_static(qkv, kv_layer, block_table, row_seq, kv_len, max_kv_len: int, out):
+    """cbx_paged_attn_decode_static: the allocation-free form (scratch lives inside the library; 5 <= T <= 4095).
+    The caller passes `out`; nothing is allocated here either."""
+    check(load().cbx_paged_attn_decode_static(_p(qkv, BF16), _p(kv_layer), _p(block_table, torch.int32),
+                                              block_table.stride(0), _p(row_seq, torch.int32), _p(kv_len, torch.int32),
+                                              _p(out, BF16), qkv.shape[0], max_kv_len, _stream()),
+          "paged_attn_decode_static")
+    return out
+
+
 def prefill_items(row_starts: list[int], lens: list[int], bt_rows: list[int]) -> torch.Tensor:
     """Host helper: int32 [n,4] items {row0, n_q, block-table row, query block} for sequences whose
     prefix rows start at row_starts[i] (positions 0..lens[i]-1), longest items first (they are dealt

@@ -139,6 +139,21 @@ int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_layer, const i
                                   void* out, void* scratch, int32_t* counters, int T, int max_kv_len,
                                   void* stream);
 
+/* Allocation-free form of cbx_paged_attn_decode.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same inputs, output and arithmetic as cbx_paged_attn_decode, but the
+ * scratch (split partials + page-range plan) and the ticket counters live in a file-scope device array inside
+ * the library (k_attn.cu, ~1.27 MB, held by every GPU that loads the library until exit), so the caller passes
+ * neither.  Limit: 5 <= T <= 4095 query rows (the balanced kernel's range; T <= 4 needs no scratch — call
+ * cbx_paged_attn_decode with scratch = counters = NULL); other T returns -1 with a message.  The call itself
+ * performs no cudaMalloc / cudaFree / allocating library call.  All calls on a device SHARE the array: the
+ * tickets are cleared on the caller's stream at every call, but two calls that overlap on the GPU (different
+ * streams, or graph branches) race — serialise them.  The first call on a device resolves the array's device
+ * address (cudaGetSymbolAddress); make that call outside graph capture. */
+int cbx_paged_attn_decode_static(const void* qkv, const void* kv_layer, const int32_t* block_table,
+                                 int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* out,
+                                 int T, int max_kv_len, void* stream);
+
 /* Prefill form of the same attention (causal, many query rows per sequence): an item is 16
  * consecutive query rows of one sequence (query block qb = first position / 16), which attend to
  * KV pages 0..qb; each page is loaded once per item.  The rows' K/V must already be in the cache
