@@ -146,13 +146,17 @@ class EmbeddingTables:
 
 def _positions_from_side(side: torch.Tensor, n: int, limit: int):
     """Text positions of a mid-prefix slice = ones per row of the triangular code, minus 1
-    (t3.py:631-633,668-669).  None when the rows are not such a code (the reference then raises
+    (t3.py:631-633,668-669).  The reference indexes its position table with ``text_pos.tolist()`` — a
+    list of Python FLOATS, which torch truncates toward zero and wraps when negative — so a slice whose
+    side rows are not a position code (cond rows reached without their 695 marker) still yields rows:
+    ``text_emb[id] + text_pos[trunc(rowsum - 1)]``.  Reproduced as executed (pinned by
+    tests/golden/t3_glue.npz).  None when an index falls outside the table (the reference then raises
     inside its try block and falls back to zeros)."""
     if len(side) < n:
         return None
-    s = side[:n].float().sum(dim=1) - 1
-    pos = s.round().long()
-    if n and (not torch.equal(pos.float(), s) or int(pos.min()) < 0 or int(pos.max()) >= limit):
+    pos = (side[:n].float().sum(dim=1) - 1).trunc().long()
+    pos = torch.where(pos < 0, pos + limit, pos)
+    if n and (int(pos.min()) < 0 or int(pos.max()) >= limit):
         return None
     return pos
 
@@ -205,7 +209,11 @@ def assemble_input_embeddings(input_ids: torch.Tensor, multimodal_embeddings, tb
                 if pos is None:
                     out.append(zeros)
                     continue
-                text = text_rows(ids[:-1], pos)
+                try:                                                               # (the reference has no guard on this branch
+                    text = text_rows(ids[:-1], pos)                                # and would raise into the engine: zeros here)
+                except IndexError:
+                    out.append(zeros)
+                    continue
                 out.append(pair([text, sos], [torch.zeros_like(text), sos]))
         elif n == 1 and first in (PREFILL_COND_END_TOKEN, PREFILL_COND_START_TOKEN):   # lone 696 / 695 (t3.py:646-660)
             m = side.to(dt)
@@ -215,7 +223,11 @@ def assemble_input_embeddings(input_ids: torch.Tensor, multimodal_embeddings, tb
             if pos is None:
                 out.append(zeros)
                 continue
-            text = text_rows(ids, pos)
+            try:                                                                   # the reference's try/except (t3.py:666-685):
+                text = text_rows(ids, pos)                                         # an id outside the text table -> zeros
+            except IndexError:
+                out.append(zeros)
+                continue
             out.append(torch.cat([text, torch.zeros_like(text)], dim=1))
         else:                                                                      # unknown: keep alignment (t3.py:686-700)
             out.append(zeros)

@@ -10,6 +10,9 @@ Fixtures and what pins them:
   sampler_vllm.npz     vLLM 0.22 torch sampler ops on seeded logits
   block_pool_vllm.json vLLM 0.22 BlockPool on a scripted admit/finish sequence
   prompt_lengths.json  reference tokenizer.json + benchmark.py chunker on docs/benchmark-text-1.txt
+  t3_glue.npz          the REFERENCE'S OWN models/t3/t3.py glue (T3MultiModalProcessor.apply, split_prefill_decode,
+                       get_input_embeddings, compute_logits, create_triangular_matrix) executed from /root/reference with
+                       the vllm imports stubbed, on oracle.glue_cases inputs
   cond_enc.npz         the REFERENCE'S OWN T3CondEnc / Perceiver modules (models/t3/modules/cond_enc.py,
                        perceiver.py) run on seeded weights and inputs (oracle.cond_ref.random_*)
 """
@@ -176,14 +179,247 @@ def cond_enc():
     np.savez_compressed(os.path.join(OUT, "cond_enc.npz"), **out)
 
 
+def load_reference_t3():
+    """Executes the reference's models/t3/t3.py FROM /root/reference with every vllm import replaced by an
+    inert stub (the file needs vLLM 0.9/0.10 internals that vLLM 0.22 no longer has; none of them takes part
+    in the functions pinned here).  Its sibling modules (learned_pos_emb, t3_config, cond_enc, perceiver)
+    are the reference's real files.  Returns (module, restore) — call restore() to put sys.modules back."""
+    import types
+    saved = dict(sys.modules)
+
+    class _Generic:
+        def __class_getitem__(cls, item):
+            return cls
+
+    def stub(name, **attrs):
+        m = types.ModuleType(name)
+        m.__dict__.update(attrs)
+        m.__path__ = []
+        sys.modules[name] = m
+        return m
+
+    for k in [k for k in sys.modules if k == "vllm" or k.startswith("vllm.")]:
+        del sys.modules[k]
+    blank = lambda n: type(n, (), {})  # noqa: E731
+
+    class _Registry:
+        @staticmethod
+        def register_processor(*a, **k):
+            return lambda cls: cls
+
+    class _Captured(dict):      # MultiModalKwargs.from_items([...from_elems(...build_elems(data=[x]))]) -> {"conditionals": [x]}
+        @classmethod
+        def from_items(cls, items):
+            return cls(conditionals=[d for it in items for d in it])
+
+    class _Item:
+        @staticmethod
+        def from_elems(elems):
+            return elems
+
+    class _Field:
+        def build_elems(self, modality, key, data):
+            return list(data)
+
+    stub("vllm")
+    stub("vllm.config", VllmConfig=blank("VllmConfig"), ModelConfig=blank("ModelConfig"))
+    stub("vllm.model_executor"), stub("vllm.model_executor.layers"), stub("vllm.model_executor.models")
+    stub("vllm.model_executor.layers.logits_processor", LogitsProcessor=blank("LogitsProcessor"))
+    stub("vllm.model_executor.layers.vocab_parallel_embedding", ParallelLMHead=blank("ParallelLMHead"))
+    stub("vllm.model_executor.models.interfaces", MultiModalEmbeddings=object, SupportsMultiModal=blank("SupportsMultiModal"))
+    stub("vllm.model_executor.models.interfaces_base", VllmModelForTextGeneration=blank("VllmModelForTextGeneration"))
+    stub("vllm.model_executor.models.llama", LlamaModel=blank("LlamaModel"))
+    stub("vllm.model_executor.sampling_metadata", SamplingMetadata=blank("SamplingMetadata"))
+    stub("vllm.multimodal", MULTIMODAL_REGISTRY=_Registry)
+    stub("vllm.multimodal.inputs", MultiModalKwargs=_Captured, MultiModalKwargsItem=_Item, MultiModalBatchedField=_Field)
+    stub("vllm.multimodal.parse", MultiModalDataParser=blank("MultiModalDataParser"),
+         ModalityDataItems=type("ModalityDataItems", (_Generic,), {"__init__": lambda self, data, modality: setattr(self, "data", data)}))
+    stub("vllm.multimodal.processing", BaseMultiModalProcessor=type("BaseMultiModalProcessor", (_Generic,), {}),
+         BaseProcessingInfo=blank("BaseProcessingInfo"), MultiModalDataDict=dict, MultiModalDataItems=dict,
+         MultiModalFieldConfig=blank("MultiModalFieldConfig"), PromptUpdate=blank("PromptUpdate"),
+         MultiModalInputs=dict, PlaceholderRange=lambda **kw: dict(kw))
+    stub("vllm.multimodal.profiling", BaseDummyInputsBuilder=blank("BaseDummyInputsBuilder"))
+    stub("vllm.sequence", IntermediateTensors=blank("IntermediateTensors"))
+    base = f"{REF}/src/chatterbox_vllm"
+    for name, path in (("chatterbox_vllm", base), ("chatterbox_vllm.models", base + "/models"),
+                       ("chatterbox_vllm.models.t3", base + "/models/t3")):
+        m = types.ModuleType(name)          # package shells: the real __init__ files import vllm
+        m.__path__ = [path]
+        sys.modules[name] = m
+    spec = importlib.util.spec_from_file_location("chatterbox_vllm.models.t3.t3", base + "/models/t3/t3.py")
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["chatterbox_vllm.models.t3.t3"] = mod
+    spec.loader.exec_module(mod)
+
+    def restore():
+        for k in list(sys.modules):
+            if k not in saved:
+                del sys.modules[k]
+        sys.modules.update(saved)
+    return mod, restore
+
+
+def reference_t3_model(ref, variant: str, cfg_scale: float, head=None, dtype=torch.float32):
+    """A bare object carrying exactly the attributes the reference's methods read, with the reference's
+    UNBOUND functions attached (t3.py:318-343 builds the same attributes from the checkpoint)."""
+    from oracle import glue_cases as gc
+    tb = gc.tables(variant)
+    t3conf = ref.T3Config.multilingual() if variant == "mtl" else ref.T3Config()
+
+    class Bare:
+        split_prefill_decode = ref.T3VllmModel.split_prefill_decode
+        get_input_embeddings = ref.T3VllmModel.get_input_embeddings
+        compute_logits = ref.T3VllmModel.compute_logits
+
+    m = Bare()
+    m.t3conf, m.dim, m.cfg_scale = t3conf, t3conf.n_channels, cfg_scale
+    m.text_emb = torch.nn.Embedding.from_pretrained(tb["text_emb"].to(dtype))
+    m.speech_emb = torch.nn.Embedding.from_pretrained(tb["speech_emb"].to(dtype))
+    # t3.py:371-377: the precomputed tables are LearnedPositionEmbeddings.get_fixed_embedding(arange)[0]
+    tp = ref.LearnedPositionEmbeddings(t3conf.max_text_tokens + 2, m.dim)
+    tp.emb.weight.data.copy_(tb["text_pos"])
+    sp = ref.LearnedPositionEmbeddings(t3conf.max_speech_tokens + 4, m.dim)
+    sp.emb.weight.data.copy_(tb["speech_pos"])
+    with torch.no_grad():
+        m.precomputed_text_pos_emb = tp.get_fixed_embedding(torch.arange(t3conf.max_text_tokens + 2))[0].to(dtype)
+        m.precomputed_speech_pos_emb = sp.get_fixed_embedding(torch.arange(t3conf.max_speech_tokens + 4))[0].to(dtype)
+    if head is not None:
+        m.speech_head = types_ns(weight=head.to(dtype))
+        m.seen_logits = []
+
+        def logits_processor(lm_head, hidden, _meta):          # vLLM LogitsProcessor: hidden @ lm_head.weight.T (fp32 accumulate)
+            lg = (hidden.float() @ lm_head.weight.float().T).to(hidden.dtype)
+            m.seen_logits.append(lg)
+            return lg
+        m.logits_processor = logits_processor
+    return m
+
+
+def types_ns(**kw):
+    import types
+    return types.SimpleNamespace(**kw)
+
+
+def t3_glue():
+    """The reference's own t3.py glue (apply / split_prefill_decode / get_input_embeddings / compute_logits /
+    create_triangular_matrix) run on oracle.glue_cases inputs -> tests/golden/t3_glue.npz."""
+    from oracle import glue_cases as gc
+    ref, restore = load_reference_t3()
+    out = {}
+    try:
+        assert (ref.PREFILL_COND_START_TOKEN, ref.PREFILL_COND_END_TOKEN, ref.PREFILL_END_TOKEN,
+                ref.CONDITIONING_SIZE, ref.SPEECH_TOKEN_OFFSET) == (695, 696, 697, 34, 1000)
+        out["tri_5x9"] = ref.create_triangular_matrix(5, 9).numpy()
+        out["tri_40x1024_digest"] = np.array(gc.digest(ref.create_triangular_matrix(40, 1024).numpy()))
+
+        class BareProc:                                       # T3MultiModalProcessor.apply on a tokeniser-free shell
+            apply = ref.T3MultiModalProcessor.apply
+
+            def _to_mm_items(self, mm_data):
+                return mm_data
+
+            def _apply_hf_processor(self, prompt, mm_items, kw, tok_kw, return_mm_hashes=False):
+                return list(prompt), None, None, False        # (prompt_ids, mm_kwargs, mm_hashes, is_update_applied)
+
+        for name, variant, n_text, ids_seed, cond_seed in gc.prefix_cases():
+            ids, cond = gc.text_ids(variant, n_text, ids_seed), gc.cond_emb(cond_seed)
+            r = BareProc().apply(ids, {"conditionals": [cond]}, {})
+            final_ids, side = r["prompt_token_ids"], r["mm_kwargs"]["conditionals"][0]
+            ph = r["mm_placeholders"]["conditionals"][0]
+            P = len(final_ids)
+            out[f"{name}/text_ids"] = np.array(ids, np.int64)
+            out[f"{name}/final_prompt_ids"] = np.array(final_ids, np.int64)
+            out[f"{name}/placeholder"] = np.array([ph["offset"], ph["length"]], np.int64)
+            out[f"{name}/side_digest"] = np.array(gc.digest(side.numpy()))
+            out[f"{name}/side_sample"] = gc.sample(side.numpy())
+            out[f"{name}/side_rowsum_tail"] = side[34:].sum(1).numpy()
+            model = reference_t3_model(ref, variant, 0.5)
+            ids_t = torch.tensor(final_ids)
+            with torch.no_grad():
+                full = model.get_input_embeddings(ids_t, [side])
+            assert full.shape == (P, 2048)
+            out[f"{name}/full_digest"] = np.array(gc.digest(full.numpy()))
+            out[f"{name}/full_sample"] = gc.sample(full.numpy())
+            if name == "en_short":
+                out[f"{name}/full"] = full.numpy()
+            # every chunk split of App. C: each slice goes through the reference as its own call, side rows sliced alike
+            for cuts in gc.chunk_splits(P):
+                edges = [0, *cuts, P]
+                for a, b in zip(edges[:-1], edges[1:]):
+                    with torch.no_grad():
+                        e = model.get_input_embeddings(ids_t[a:b], [side[a:b]])
+                    assert e.shape == (b - a, 2048), (name, cuts, a, b, e.shape)
+                    key = f"{name}/chunk_{a}_{b}"
+                    if key + "_digest" not in out:
+                        out[key + "_digest"] = np.array(gc.digest(e.numpy()))
+                        out[key + "_equals_full_rows"] = np.array(bool(torch.equal(e, full[a:b])))
+            # mixed batch: decode tokens of two running requests, a whole new prefix, one more decode token
+            dec = torch.tensor([1000 + 17, 1000 + 6561, 1000 + 4242])
+            mixed_ids = torch.cat([dec[:2], ids_t, dec[2:]])
+            with torch.no_grad():
+                segs = model.split_prefill_decode(mixed_ids, [side])
+                mixed = model.get_input_embeddings(mixed_ids, [side])
+                pure = model.get_input_embeddings(dec, None)
+            out[f"{name}/mixed_seg_lens"] = np.array([len(s[0]) for s in segs], np.int64)
+            out[f"{name}/mixed_seg_prefill"] = np.array([s[1] is not None for s in segs])
+            out[f"{name}/mixed_digest"] = np.array(gc.digest(mixed.numpy()))
+            out[f"{name}/decode_digest"] = np.array(gc.digest(pure.numpy()))
+            out[f"{name}/decode_sample"] = gc.sample(pure.numpy(), 211)
+        # two requests' prefixes back to back in one batch (vLLM batches prefills), second one cut short by the budget
+        (n0, v0, t0, s0, c0), (n1, _, t1, s1, c1) = gc.prefix_cases()[0], gc.prefix_cases()[1]
+        model = reference_t3_model(ref, "en", 0.5)
+        reqs = []
+        for (t, s, c) in ((t0, s0, c0), (t1, s1, c1)):
+            r = BareProc().apply(gc.text_ids("en", t, s), {"conditionals": [gc.cond_emb(c)]}, {})
+            reqs.append((torch.tensor(r["prompt_token_ids"]), r["mm_kwargs"]["conditionals"][0]))
+        cut = 40
+        ids2 = torch.cat([reqs[0][0], reqs[1][0][:cut]])
+        with torch.no_grad():
+            segs = model.split_prefill_decode(ids2, [reqs[0][1], reqs[1][1][:cut]])
+            both = model.get_input_embeddings(ids2, [reqs[0][1], reqs[1][1][:cut]])
+        out["two_prefixes/seg_lens"] = np.array([len(s[0]) for s in segs], np.int64)
+        out["two_prefixes/cut"] = np.array(cut)
+        out["two_prefixes/digest"] = np.array(gc.digest(both.numpy()))
+        # CHATTERBOX_STRIP_LLM_EOS (t3.py:209-221,437-447): id 2 dropped from the walk
+        os.environ["CHATTERBOX_STRIP_LLM_EOS"] = "1"
+        try:
+            ids3 = torch.tensor([695, 2, 5, 2, 697, 1003, 2, 1004])
+            segs = model.split_prefill_decode(ids3, [torch.zeros(5, 1024)])
+            out["strip_eos/seg_ids"] = np.array([t for s in segs for t in s[0].tolist()] , np.int64)
+            out["strip_eos/seg_lens"] = np.array([len(s[0]) for s in segs], np.int64)
+        finally:
+            del os.environ["CHATTERBOX_STRIP_LLM_EOS"]
+        # compute_logits (t3.py:725-739) at cfg 0.0 / 0.5 / 1.3, fp32 and bf16 (the dtype the reference runs in)
+        head, hid = gc.speech_head(), gc.hidden_rows(2, 5)
+        for dt, tag in ((torch.float32, "f32"), (torch.bfloat16, "bf16")):
+            for cfg in gc.CFG_SCALES:
+                model = reference_t3_model(ref, "en", cfg, head=head, dtype=dt)
+                with torch.no_grad():
+                    lg = model.compute_logits(hid.to(dt), None)
+                assert lg.shape == (2, 9194) and torch.isinf(lg[:, :1000]).all() and (lg[:, :1000] < 0).all()
+                body = lg[:, 1000:].float().numpy()
+                key = f"logits/{tag}/cfg{cfg}"
+                out[key + "/merged"] = body.astype(np.float32) if dt == torch.float32 else lg[:, 1000:].view(torch.int16).numpy()
+                if cfg == gc.CFG_SCALES[0]:
+                    c, u = model.seen_logits
+                    out[f"logits/{tag}/cond"] = c.float().numpy() if dt == torch.float32 else c.view(torch.int16).numpy()
+                    out[f"logits/{tag}/uncond"] = u.float().numpy() if dt == torch.float32 else u.view(torch.int16).numpy()
+    finally:
+        restore()
+    np.savez_compressed(os.path.join(OUT, "t3_glue.npz"), **out)
+    print("t3_glue keys:", len(out), "bytes:", os.path.getsize(os.path.join(OUT, "t3_glue.npz")))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     only = sys.argv[1:]
-    for fn in (hf_backbone, rope, sampler, block_pool, prompt_lengths, cond_enc):
+    for fn in (hf_backbone, rope, sampler, block_pool, prompt_lengths, cond_enc, t3_glue):
         if only and fn.__name__ not in only:
             continue
         try:
             fn()
             print("ok  ", fn.__name__)
         except Exception as e:
+            import traceback
+            traceback.print_exc()
             print("FAIL", fn.__name__, repr(e))

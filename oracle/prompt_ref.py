@@ -11,9 +11,13 @@ Restates (reference file:line):
   tts.py:448-465                  stop cut, tail crop, de-offset, < 6561 filter
   models/s3tokenizer/__init__.py:38-78  drop_invalid_tokens
 
-PARITY STATUS: unpinned by reference tests (none exist); the layout arithmetic is
-pinned by the README's own log line (28 754 prompt tokens for the 154 chunks of
-docs/benchmark-text-1.txt — README.md:151; tests/golden/prompt_lengths.json).
+PARITY STATUS: the reference has no tests; final_prompt_ids / side_tensor are pinned bit for bit
+to the reference's own T3MultiModalProcessor.apply executed from /root/reference
+(tests/golden/t3_glue.npz, tests/test_reference_glue.py); punc_norm and the chunker to the
+reference's own text_utils.py / benchmark.py (tests/golden/prompt_lengths.json), and the layout
+arithmetic to the README's log line (28 754 prompt tokens for the 154 chunks of
+docs/benchmark-text-1.txt — README.md:151).  The pre-cap / post-processing functions restate
+tts.py and are unpinned (tts.py needs librosa / s3tokenizer / diffusers to import).
 """
 from __future__ import annotations
 

@@ -5,11 +5,20 @@ Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline``
 (``chatterbox_vllm_b200``) never does; it fails loudly when the CUDA library is
 missing.
 
-PARITY STATUS: **unpinned by the reference** — the reference repo
-(iMash-io/chatterbox-vllm @ 8d61738) ships no tests, golden vectors or fixtures
-for this path and its ``t3.py`` cannot be imported against
-the installed vLLM 0.22.  This restatement is therefore pinned against what
-*can* run here (see ``oracle/make_golden.py``):
+PARITY STATUS: the reference repo (iMash-io/chatterbox-vllm @ 8d61738) ships no tests, golden
+vectors or fixtures for this path.  Pinned instead by outputs of the
+reference's OWN code run in the build container (``oracle/make_golden.py``, committed under
+``tests/golden/``; nothing at test time reads /root/reference):
+  * **the T3 glue — pinned**: ``models/t3/t3.py`` is executed from /root/reference with its vllm
+    imports stubbed; ``T3VllmModel.get_input_embeddings`` / ``split_prefill_decode`` /
+    ``compute_logits``, ``T3MultiModalProcessor.apply`` and ``create_triangular_matrix`` run on
+    seeded inputs (``oracle/glue_cases.py``) -> ``t3_glue.npz``; ``prefill_embeds``,
+    ``decode_embed``, ``cfg_merge`` (cfg 0.0 / 0.5 / 1.3, fp32 and bf16) and ``head`` below are
+    held to it bit for bit (``tests/test_reference_glue.py``);
+  * the conditioning encoder — pinned the same way (``cond_enc.npz``, ``oracle/cond_ref.py``);
+  * **the Llama backbone, attention and the sampler chain — unpinned by the reference** (their
+    arithmetic lives in un-vendored ``vllm==0.10.0`` / ``torch 2.7.1`` kernels that cannot run
+    here); pinned against what can:
   * ``transformers.LlamaModel`` (fp32) for the 30-layer backbone, llama3 RoPE
     and KV-cache decode — the same HF module the original Chatterbox wraps;
   * vLLM 0.22's own CPU-runnable pieces (llama3 ``_compute_inv_freq``,
