@@ -24,9 +24,9 @@ int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStre
 int gemv_qkv_rope(const void*, const void*, const void*, const void*, const int32_t*, const int64_t*, void*, void*, int,
                   float, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0, const float* wscale = nullptr);
 int gemv_residual(const void*, const void*, void*, int, int, cudaStream_t, const void* next_w = nullptr, size_t next_bytes = 0,
-                  const float* wscale = nullptr);
+                  const float* wscale = nullptr, void* zero_ptr = nullptr, int zero_bytes = 0, const void* res_in = nullptr);
 int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, cudaStream_t, const void* next_w = nullptr,
-                      size_t next_bytes = 0, const float* wscale = nullptr);
+                      size_t next_bytes = 0, const float* wscale = nullptr, const void* acc = nullptr, void* res_out = nullptr);
 void attn_set_prefetch(const void*, size_t);
 int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
               const int32_t* row_seq);
@@ -42,6 +42,10 @@ int launch_decode_prepare(const void*, const int32_t*, const int32_t*, const int
 int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t, const int32_t* pair_map = nullptr,
                       int n_sub = 0);
 int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
+bool layer_attn_block_supported(int T, int max_kv_len);
+int layer_attn_block(const void* res, const void* ln_w, const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos,
+                     const int64_t* slot, void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq,
+                     const int32_t* kv_len, void* acc, void* q_out, int T, float eps, cudaStream_t s);
 struct MegaArgs {
   const bf16* ln1[32]; const bf16* wqkv[32]; const bf16* wo[32];
   const bf16* ln2[32]; const bf16* wgu[32]; const bf16* wd[32];
@@ -84,6 +88,7 @@ struct cbx_engine {
   // workspace carve-up
   bf16 *res, *h, *qkv, *attn, *act, *hs, *logits;
   int32_t *pos, *kv_len, *row_seq, *head_rows, *attn_counters;
+  unsigned long long* block_acc;   // [4][1024] fixed-point O-proj accumulator of the fused attention block (zero between layers)
   int64_t* slot;
   void* attn_scratch;
   float* part;                 // split-K partials [4][split_max_rows][1024] fp32 
@@ -121,6 +126,7 @@ static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
   p = take((R + 1024) * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256); if (e) e->attn_scratch = p;
   p = take((size_t)4 * 512 * 1024 * 4); if (e) e->part = (float*)p;
   p = take(256); if (e) e->mega_sync = (unsigned*)p;
+  p = take(4 * 1024 * 8); if (e) e->block_acc = (unsigned long long*)p;
   p = take(mega_ws_bytes()); if (e) e->mega_ws = (uint8_t*)p;
   return off;
 }
@@ -151,6 +157,7 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   // split-K attention tickets start at zero and reset themselves
   cudaMemset(e->attn_counters, 0, (size_t)cfg->max_rows * 4);
   cudaMemset(e->mega_sync, 0, 256);
+  cudaMemset(e->block_acc, 0, 4 * 1024 * 8);
   cudaMemset(e->mega_ws, 0, mega_ws_bytes());
   if (const char* v = getenv("CBX_MEGA")) e->mega = v[0] != '0';
   if (const char* v = getenv("CBX_SKIP")) e->skip = atoi(v);
@@ -299,6 +306,23 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
   const bool pf = e->l2_prefetch;
   for (int li = 0; li < e->w.n_layers; ++li) {
     uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;
+    // T <= 4, bf16 weights, context within the fused block's page buffer: the attention half of the layer is ONE kernel
+    // (k_block.cu): [norm+QKV+RoPE+append+attention+O+res] [norm+gate_up+SiLU] [down+res] = 3 launches per layer
+    const bool fused = T <= 4 && !e->fp8 && !sk && !pf && e->n_prefill_items == 0 && layer_attn_block_supported(T, max_kv_len);
+    if (fused) {
+      // the block leaves the O-proj output in block_acc; gate_up's norm prologue closes the residual branch from it
+      // (bf16(bf16(o) + res), written by its CTA 0 to buffer h — NOT in place: the other CTAs still read res); the
+      // down-proj kernel adds its output to h's rows, writes res, and clears block_acc for the next layer
+      if (layer_attn_block(e->res, e->ln1[li], e->wqkv[li], e->wo[li], e->w.cos_sin, e->pos, e->slot, kv, e->block_table,
+                           e->bt_stride, e->row_seq, e->kv_len, e->block_acc, nullptr, T, eps, s)) return -1;
+      static const bool noacc = getenv("CBX_BLOCK_NOACC") != nullptr;   // profiling aid: gate_up ignores the accumulator (garbage)
+      if (gemv_norm_gate_up(e->res, e->ln2[li], e->wgu[li], e->act, T, eps, s, nullptr, 0, e->sgu[li], noacc ? nullptr : e->block_acc, e->h)) return -1;
+      if (gemv_residual(e->act, e->wd[li], e->res, T, 4096, s, nullptr, 0, e->sd[li], e->block_acc, 4 * 1024 * 8, noacc ? nullptr : e->h)) return -1;
+      if (e->trace)
+        cudaMemcpyAsync(e->trace + (size_t)li * T * CBX_HIDDEN, e->res, (size_t)T * CBX_HIDDEN * 2,
+                        cudaMemcpyDeviceToDevice, s);
+      continue;
+    }
     if (T <= 4) {
       // each kernel pulls a LATER kernel's weights into L2 (QKV -> Wo, attention -> Wgu, O -> Wd, gate_up -> next Wqkv)
       if (!(sk & 1) && gemv_qkv_rope(e->res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos, e->slot, e->qkv, kv, T, eps, s,

@@ -45,6 +45,15 @@ struct GemvArgs {
   float eps;
   const void* next_w;     // weights of a later kernel in the chain, prefetched into L2 (may be NULL)
   size_t next_bytes;
+  // after the fused attention block (k_block.cu): the O-proj output of the T rows waits in a 64-bit fixed-point
+  // accumulator.  PRO_NORM with acc != NULL first closes the residual branch, x = bf16(bf16(acc * 2^-32) + x), CTA 0
+  // writing the rows back to res_wb; a kernel given zero_ptr clears that many bytes after its wait (the down-proj
+  // kernel hands the accumulator back empty).
+  const unsigned long long* acc;
+  bf16* res_wb;           // NOT the buffer x points at: the other CTAs are still reading that one
+  const bf16* res_in;     // EPI_RES: the residual that is added (NULL = y, in place)
+  void* zero_ptr;
+  int zero_bytes;
 };
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
@@ -89,7 +98,7 @@ template <int EPI>
 __device__ __forceinline__ EpiPrefetch gemv_epilogue_prefetch(const GemvArgs& a, int item, int t) {
   EpiPrefetch pf = {true, 0u, 1.f, 0.f, -1, 0};
   if (EPI == EPI_RES) {
-    pf.res = *reinterpret_cast<const uint32_t*>(a.y + (size_t)t * 1024 + 2 * item);
+    pf.res = *reinterpret_cast<const uint32_t*>((a.res_in ? a.res_in : a.y) + (size_t)t * 1024 + 2 * item);
   } else if (EPI == EPI_ROPE) {
     const int which = item >> 9;                       // (item >> 5) >> 4
     if (which < 2) pf.pos = a.pos[t];
@@ -118,7 +127,7 @@ __device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int r
     a.y[(size_t)t * a.ldy + item] = __float2bfloat16_rn(g / (1.f + __expf(-g)) * u);
   } else if (EPI == EPI_RES) {
     uint32_t* rp = reinterpret_cast<uint32_t*>(a.y + (size_t)t * 1024 + ra);
-    const uint32_t r = pf.valid ? pf.res : *rp;
+    const uint32_t r = pf.valid ? pf.res : *reinterpret_cast<const uint32_t*>((a.res_in ? a.res_in : a.y) + (size_t)t * 1024 + ra);
     *rp = pack_bf16(round_bf16(v0) + bf_lo(r), round_bf16(v1) + bf_hi(r));
   } else {                                        // EPI_ROPE
     const int head48 = item >> 5, i = item & 31, which = head48 >> 4, h = head48 & 15;
@@ -192,10 +201,23 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
   // RMSNorm weights of the norm prologue: also independent of the previous kernel.  Left where they are used they were
   // fetched after the row's sum of squares — one more L2 round trip on the critical path of three kernels per layer.
   uint4 lnw[4] = {};
-  if (PRO == PRO_NORM && warp < TT) {
+  const bool fold_acc = PRO == PRO_NORM && a.acc != nullptr;     // CTA-uniform
+  if (PRO == PRO_NORM && warp < TT && !fold_acc) {
     const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
 #pragma unroll
     for (int i = 0; i < 4; ++i) lnw[i] = ld_stream(wr + lane + 32 * i);
+  }
+  // accumulator form of the prologue: ALL warps share the rows (thread -> 16-byte chunk ci = tid + k * NW * 32 of the
+  // TT x 128 chunks), so its norm weights are fetched in that mapping
+  constexpr int kFoldIters = (TT * 128 + NW * 32 - 1) / (NW * 32);
+  uint4 lnc[kFoldIters] = {};
+  if (fold_acc) {
+    const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
+#pragma unroll
+    for (int k = 0; k < kFoldIters; ++k) {
+      const int ci = threadIdx.x + k * NW * 32;
+      if (ci < TT * 128) lnc[k] = ld_stream(wr + (ci & 127));
+    }
   }
   l2_prefetch_slice(a.next_w, a.next_bytes);
   // W8: the first item's bytes are widened to fp32 BEFORE the wait (3.5 ops per weight that would otherwise sit on
@@ -209,13 +231,85 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
     }
   }
   pdl_wait();
+  if (a.zero_ptr != nullptr) {
+    uint4* z = reinterpret_cast<uint4*>(a.zero_ptr);
+    for (int i = blockIdx.x * (NW * 32) + threadIdx.x; i < a.zero_bytes / 16; i += gridDim.x * (NW * 32)) z[i] = make_uint4(0, 0, 0, 0);
+  }
   EpiPrefetch pf = {false, 0u, 1.f, 0.f, -1, 0};
   const int item_first = item;
   const bool do_pf = (EPI == EPI_RES || EPI == EPI_ROPE) && item < n_items && kseg == 0 && lane < T;
   if (do_pf) pf = gemv_epilogue_prefetch<EPI>(a, item, lane);
 
   // ---- prologue: activation rows -> shared memory (bf16)
-  if (PRO == PRO_NORM) {
+  if (PRO == PRO_NORM && fold_acc) {
+    // After the fused attention block: the rows' O-proj output waits in the 64-bit fixed-point accumulator.  Close the
+    // residual branch, x = bf16(bf16(acc * 2^-32) + x) (CTA 0 writes the rows back), then normalise.  Spread over all
+    // warps: done by warps < TT alone, the 1024 64-bit conversions per lane-row cost 0.9 us per layer at b = 1.
+    __shared__ float s_ss[4][16];
+    float ssl[TT];
+#pragma unroll
+    for (int t = 0; t < TT; ++t) ssl[t] = 0.f;
+    uint4 xv[kFoldIters], av[kFoldIters][4];
+#pragma unroll
+    for (int k = 0; k < kFoldIters; ++k) {             // every load of the thread in flight together
+      const int ci = threadIdx.x + k * NW * 32;
+      if (ci < TT * 128 && (ci >> 7) < T) {
+        xv[k] = reinterpret_cast<const uint4*>(a.x)[ci];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) av[k][q] = reinterpret_cast<const uint4*>(a.acc)[ci * 4 + q];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kFoldIters; ++k) {
+      const int ci = threadIdx.x + k * NW * 32;
+      if (ci < TT * 128) {
+        const int t = ci >> 7;                         // warp-uniform: 32 consecutive chunks lie in one row
+        uint4 o = make_uint4(0, 0, 0, 0);
+        if (t < T) {
+          float f[8];
+          unpack8(xv[k], f);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const long long lo = (long long)(((unsigned long long)av[k][q].y << 32) | av[k][q].x);
+            const long long hi = (long long)(((unsigned long long)av[k][q].w << 32) | av[k][q].z);
+            f[2 * q] = round_bf16(round_bf16((float)lo * (1.f / 4294967296.f)) + f[2 * q]);
+            f[2 * q + 1] = round_bf16(round_bf16((float)hi * (1.f / 4294967296.f)) + f[2 * q + 1]);
+          }
+          o = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+          if (blockIdx.x == 0) reinterpret_cast<uint4*>(a.res_wb)[ci] = o;
+          float ss = 0.f;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ss += f[e] * f[e];
+#pragma unroll
+          for (int tt = 0; tt < TT; ++tt) if (tt == t) ssl[tt] += ss;
+        }
+        xs[ci] = o;                                    // the new residual row, not yet normalised
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < TT; ++t) {
+      const float v = warp_sum(ssl[t]);
+      if (lane == 0) s_ss[t][warp] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kFoldIters; ++k) {
+      const int ci = threadIdx.x + k * NW * 32;
+      if (ci < TT * 128 && (ci >> 7) < T) {
+        const int t = ci >> 7;
+        float ss = 0.f;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) ss += s_ss[t][w]; // warp order: every thread (and every CTA) gets the same bits
+        const float rstd = rsqrtf(ss * (1.0f / 1024.f) + a.eps);
+        float f[8], w[8];
+        unpack8(xs[ci], f);
+        unpack8(lnc[k], w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = round_bf16(f[e] * rstd) * w[e];
+        xs[ci] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+      }
+    }
+  } else if (PRO == PRO_NORM) {
     if (warp < TT) {
       uint4 o[4] = {};
       if (warp < T) {
@@ -581,18 +675,20 @@ int gemv_qkv_rope(const void* res, const void* ln_w, const void* Wqkv, const voi
 }
 // res = bf16(bf16(x·W^T) + res), N = 1024, K in {1024, 4096}.
 int gemv_residual(const void* x, const void* W, void* res, int T, int K, cudaStream_t s, const void* next_w,
-                  size_t next_bytes, const float* wscale) {
+                  size_t next_bytes, const float* wscale, void* zero_ptr, int zero_bytes, const void* res_in) {
   GemvArgs a = {};
-  a.next_w = next_w; a.next_bytes = next_bytes; a.wscale = wscale;
+  a.next_w = next_w; a.next_bytes = next_bytes; a.wscale = wscale; a.zero_ptr = zero_ptr; a.zero_bytes = zero_bytes;
+  a.res_in = (const bf16*)res_in;
   a.x = (const bf16*)x; a.W = W; a.y = (bf16*)res; a.T = T; a.N = 1024; a.ldy = 1024;
   if (K == 1024) return dispatch_t<1, PRO_COPY, EPI_RES, 4>(a, grid_for(512, 4), s);
   return dispatch_t<4, PRO_COPY, EPI_RES, 16>(a, grid_for(512, 4), s);
 }
 // act = SiLU(g)·u of RMSNorm(res)·ln_w · Wgu^T (packed gate/up), act [T, 4096].
 int gemv_norm_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, int T, float eps, cudaStream_t s,
-                      const void* next_w, size_t next_bytes, const float* wscale) {
+                      const void* next_w, size_t next_bytes, const float* wscale, const void* acc, void* res_out) {
   GemvArgs a = {};
   a.next_w = next_w; a.next_bytes = next_bytes; a.wscale = wscale;
+  a.acc = (const unsigned long long*)acc; a.res_wb = (bf16*)res_out;   // acc != NULL: CTA 0 writes the closed residual rows there
   a.x = (const bf16*)res; a.ln_w = (const bf16*)ln_w; a.W = Wgu; a.y = (bf16*)act;
   a.T = T; a.N = 8192; a.ldy = 4096; a.eps = eps;
   return dispatch_t<1, PRO_NORM, EPI_SILU, 14>(a, grid_for(4096, 14), s);

@@ -12,6 +12,8 @@
 //
 // Specified tie rules (the reference leaves them to sort order): argmax → lowest id; top-p
 // boundary ties → lowest ids kept first; top-k keeps every token tied with the k-th value.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 using namespace cbx;

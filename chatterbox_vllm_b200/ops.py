@@ -201,6 +201,25 @@ def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5, 
     return qkv
 
 
+_block_ws: dict = {}
+
+
+def layer_attn_block(res, ln_w, wqkv, wo, cos_sin, pos, slot, kv_layer, block_table, row_seq, kv_len, max_kv_len: int,
+                     eps: float = 1e-5, q_out=None):
+    """cbx_layer_attn_block: norm + QKV + RoPE + KV append + paged attention + O-proj + residual in one launch
+    (T <= 4 rows).  Updates `res` and the KV pages in place."""
+    T = res.shape[0]
+    ws = _block_ws.get(res.device)
+    if ws is None:
+        ws = torch.zeros(load().cbx_layer_attn_block_scratch_bytes(), dtype=torch.uint8, device=res.device)
+        _block_ws[res.device] = ws
+    check(load().cbx_layer_attn_block(_p(res, BF16), _p(ln_w, BF16), _p(wqkv, BF16), _p(wo, BF16), _p(cos_sin, BF16),
+                                      _p(pos, torch.int32), _p(slot, torch.int64), _p(kv_layer), _p(block_table, torch.int32),
+                                      block_table.stride(0), _p(row_seq, torch.int32), _p(kv_len, torch.int32), _p(ws),
+                                      _p(q_out, BF16), T, max_kv_len, eps, _stream()), "layer_attn_block")
+    return res
+
+
 def linear_residual(x, W, res):
     """res += x·Wᵀ in place (N = 1024)."""
     T, K = x.shape

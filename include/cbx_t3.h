@@ -178,6 +178,20 @@ int cbx_linear_residual(const void* x, const void* W, void* res, int T, int K, v
 /* act[T,4096] = SiLU(g)·u of RMSNorm(res)·ln_w·Wgu^T, Wgu packed by cbx_pack_gate_up (llama.py:117-119). */
 int cbx_layer_gate_up(const void* res, const void* ln_w, const void* Wgu, void* act, void* h_scratch, int T,
                       float eps, void* stream);
+/* The attention half of a layer as ONE launch for T <= 4 rows (llama.py:212-226,316-326 + flash_attn.py:796-800,
+ * 850-874): res += Wo · attention(RoPE(Wqkv · RMSNorm(res)·ln_w)) with the new token's K/V appended to page slot[t]
+ * — 16 clusters (one per head) of 6 CTAs; bf16 weights only.  row t attends to positions [0, kv_len[t]) of
+ * block-table row row_seq[t], the new token (position kv_len[t]-1) included; kv_len[t] = 0 leaves the row's
+ * attention output zero.  scratch: cbx_layer_attn_block_scratch_bytes() bytes, zero before first use (left
+ * zero): the 16 heads add their O-proj partials into it as 64-bit fixed point, so the sum is order-independent.  q_out: optional [T,3072] buffer receiving the rotated q (columns 0..1023), else NULL.
+ * cbx_layer_attn_block_supported(T, max_kv_len) says whether the context fits the kernel's shared-memory page
+ * buffer (T = 1: 3841 tokens, 2: 1921, 3-4: 961); the engine falls back to the three-kernel chain otherwise. */
+int64_t cbx_layer_attn_block_scratch_bytes(void);
+int cbx_layer_attn_block_supported(int T, int max_kv_len);
+int cbx_layer_attn_block(void* res, const void* ln_w, const void* Wqkv, const void* Wo, const void* cos_sin,
+                         const int32_t* pos, const int64_t* slot, void* kv_layer, const int32_t* block_table,
+                         int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* scratch, void* q_out,
+                         int T, int max_kv_len, float eps, void* stream);
 /* logits[T, CBX_LOGITS_LD] = RMSNorm(res)·norm_w · Whead[8194,1024]^T (llama.py:430 + t3.py:729-730). */
 int cbx_head_logits(const void* res, const void* norm_w, const void* Whead, void* logits, void* h_scratch,
                     int T, float eps, void* stream);
