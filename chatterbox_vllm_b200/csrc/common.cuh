@@ -17,6 +17,10 @@ namespace cbx {
 // ---- error plumbing ---------------------------------------------------------------
 void set_error(const char* fmt, ...);
 int  count_launch();                       // ++ global launch counter; returns 0
+// SMs of the current device (queried once), capped at kMaxSms: the persistent kernels launch one CTA per SM and the
+// attention page-range plan is laid out for at most kMaxSms ranges (B200: 148)
+constexpr int kMaxSms = 148;
+int  sm_count();
 #define CBX_CHECK_LAUNCH(name)                                                   \
   do {                                                                           \
     cudaError_t e__ = cudaGetLastError();                                        \

@@ -264,6 +264,7 @@ extern "C" int cbx_head_logits_fp8w(const void* res, const void* norm_w, const v
   CBX_REQUIRE(wscale != nullptr, "cbx_head_logits_fp8w: NULL scale");
   return head_logits(res, norm_w, Whead8, wscale, logits, h_scratch, T, eps, stream);
 }
+static void drop_graphs(cbx_engine* e);
 // Switch a created engine to FP8-e4m3 projection weights (cbx_quantize_fp8_rows output).  Embeddings, norms,
 // KV cache, activations and the sampler are unchanged (bf16 / fp32).  Graphs captured before the switch are dropped.
 extern "C" int cbx_engine_set_fp8_weights(cbx_engine* e, const cbx_fp8_weights* f) {
@@ -282,8 +283,7 @@ extern "C" int cbx_engine_set_fp8_weights(cbx_engine* e, const cbx_fp8_weights* 
   e->fp8 = true;
   e->mega = false;                                     // the persistent-kernel experiment is bf16 only
   e->l2_prefetch = false;
-  for (auto& g : e->graphs) cudaGraphExecDestroy(g.second.first);
-  e->graphs.clear();
+  drop_graphs(e);
   return 0;
 }
 
@@ -385,12 +385,21 @@ extern "C" int cbx_engine_forward(cbx_engine* e, int T, int max_kv_len, void* st
 
 extern "C" int cbx_engine_set_prefill_items(cbx_engine* e, const int32_t* items, int n_items) {
   CBX_REQUIRE(e != nullptr && (n_items == 0 || items != nullptr), "cbx_engine_set_prefill_items: bad arguments");
+  if ((n_items > 0) != (e->n_prefill_items > 0)) drop_graphs(e);
   e->prefill_items = items; e->n_prefill_items = n_items;
   return 0;
 }
 
+// A captured step bakes in everything forward_layers reads from the engine (trace pointer, split choice, weights):
+// whoever changes one of those drops the captured graphs, so a later replay can never touch a freed buffer.
+static void drop_graphs(cbx_engine* e) {
+  for (auto& g : e->graphs) cudaGraphExecDestroy(g.second.first);
+  e->graphs.clear();
+}
+
 extern "C" int cbx_engine_set_trace(cbx_engine* e, void* trace) {
   CBX_REQUIRE(e != nullptr, "cbx_engine_set_trace: NULL engine");
+  if ((bf16*)trace != e->trace) drop_graphs(e);
   e->trace = (bf16*)trace;
   return 0;
 }
@@ -474,13 +483,16 @@ extern "C" int cbx_engine_decode(cbx_engine* e, int B, int n_steps, int max_kv_l
     auto itr = e->graphs.find(key);
     if (itr == e->graphs.end()) {
       // warm the lazily-initialised function attributes / tensor maps outside capture
-      cudaGraph_t g;
       const int64_t c0 = launches();
       CBX_REQUIRE(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess, "begin capture failed");
       const int rc = decode_step(e, B, bucket, s);
+      cudaGraph_t g = nullptr;
       cudaError_t ce = cudaStreamEndCapture(s, &g);
-      CBX_REQUIRE(rc == 0, "decode_step failed during capture: %s", cbx_last_error());
-      CBX_REQUIRE(ce == cudaSuccess, "end capture: %s", cudaGetErrorString(ce));
+      if (rc != 0 || ce != cudaSuccess) {
+        if (g) cudaGraphDestroy(g);                    // the partial capture is not kept
+        CBX_REQUIRE(rc == 0, "decode_step failed during capture: %s", cbx_last_error());
+        CBX_REQUIRE(false, "end capture: %s", cudaGetErrorString(ce));
+      }
       const int64_t nodes = launches() - c0;
       cudaGraphExec_t ex;
       ce = cudaGraphInstantiate(&ex, g, 0);

@@ -31,16 +31,16 @@ constexpr float kLog2e = 1.4426950408889634f;
 
 // balanced variant: 2 partial slots per CTA (o fp32 [1024], (m, l) per head), then the range plan
 constexpr int kPlanMaxRows = 4095;              // 1024 threads x 4 rows, and entry [T] for the total
-constexpr int kPlanFirst = 2 + 2 * 148;         // [kPlanFirst] = 1 when the first-page ids below are filled in
+constexpr int kPlanFirst = 2 + 2 * kMaxSms;         // [kPlanFirst] = 1 when the first-page ids below are filled in
 constexpr int kPrimed = 3;                      // = kStages of the balanced kernel: the first ring fill
-constexpr int kPlanInts = kPlanFirst + 1 + kPrimed * 148;
-constexpr int64_t kBalScratchBytes = 2 * 148 * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + kPlanInts * 4 + 256;
+constexpr int kPlanInts = kPlanFirst + 1 + kPrimed * kMaxSms;
+constexpr int64_t kBalScratchBytes = 2 * kMaxSms * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + kPlanInts * 4 + 256;
 
 struct AttnPlan { int pps; int nsplit; };
 inline AttnPlan make_plan(int T, int max_kv_len) {
   int max_pages = (max_kv_len + CBX_BLOCK_SIZE - 1) / CBX_BLOCK_SIZE;
   if (max_pages < 1) max_pages = 1;
-  int want = (148 * 6 + T - 1) / T;                 // splits per row to get ~6 items per SM
+  int want = (sm_count() * 6 + T - 1) / T;                 // splits per row to get ~6 items per SM
   if (want < 1) want = 1;
   if (want > 32) want = 32;
   if (want > max_pages) want = max_pages;
@@ -954,7 +954,7 @@ static bool balanced_on() {
   return on;
 }
 static int32_t* plan_of(void* scratch) {
-  return reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(scratch) + 2 * 148 * (CBX_HIDDEN * 4 + CBX_HEADS * 8));
+  return reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(scratch) + 2 * kMaxSms * (CBX_HIDDEN * 4 + CBX_HEADS * 8));
 }
 }
 // Page-range plan shared by every layer of a decode step (kv_len is the same for all 30 launches).
@@ -964,7 +964,7 @@ int cbx::attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, co
                    const int32_t* row_seq) {
   if (T <= 4 || T > kPlanMaxRows || !balanced_on() || scratch == nullptr) return 1;
   if (row_seq == nullptr) block_table = nullptr;
-  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, 148, plan_of(scratch),
+  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, sm_count(), plan_of(scratch),
                              block_table, bt_stride, row_seq);
   CBX_REQUIRE(e == cudaSuccess, "attn_plan launch failed: %s", cudaGetErrorString(e));
   count_launch();
@@ -996,7 +996,7 @@ extern "C" int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_lay
 int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                               const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch,
                               int32_t* counters, int T, int max_kv_len, bool have_plan, void* stream) {
-  const int max_ctas = 148;
+  const int max_ctas = sm_count();
   if (T <= 0) return 0;
   if (cbx::init_attn()) return -1;
   {
@@ -1023,7 +1023,7 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
     CBX_REQUIRE(scratch != nullptr && counters != nullptr, "cbx_paged_attn_decode: scratch / counters is NULL");
     if (!have_plan && attn_plan(kv_len, T, scratch, stream, block_table, bt_stride, row_seq)) return -1;
     float* o_part = reinterpret_cast<float*>(scratch);
-    float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)2 * 148 * CBX_HIDDEN);
+    float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)2 * kMaxSms * CBX_HIDDEN);
     cudaError_t e = launch_pdl(paged_attn_decode_bal_kernel, dim3(max_ctas), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,
                                (const bf16*)qkv, (const uint8_t*)kv_layer, block_table, bt_stride, row_seq, kv_len, (bf16*)out,
                                o_part, ml_part, counters, (const int32_t*)plan_of(scratch), T);
@@ -1109,7 +1109,7 @@ extern "C" int cbx_paged_attn_prefill(const void* qkv, const void* kv_layer, con
                                       const int32_t* items, int n_items, void* out, void* stream) {
   if (n_items <= 0) return 0;
   if (cbx::init_attn()) return -1;
-  const int grid = n_items < 148 ? n_items : 148;
+  const int grid = n_items < sm_count() ? n_items : sm_count();
   CUtensorMap vmap;
   if (cbx::make_kv_rows_map(&vmap, kv_layer)) return -1;
   cudaError_t e = launch_pdl(paged_attn_prefill_kernel, dim3(grid), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,

@@ -554,7 +554,7 @@ int launch(const void* x, const void* W, void* y, int M, int N, int K, int ldy, 
   if (make_map(&ma, x, M, K, BM)) return -1;
   if (make_map(&mb, W, N, K, BN)) return -1;
   static const int shallow_env = getenv("CBX_GEMM_SHALLOW") ? atoi(getenv("CBX_GEMM_SHALLOW")) : 1;
-  const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * 148;
+  const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * sm_count();
   const int n_stages = shallow ? C::kStagesShallow : C::kStages;
   const int smem_bytes = shallow ? C::kSmemShallow : C::kSmem;
 #ifdef CBX_GEMM_PROF
@@ -583,7 +583,7 @@ int launch_pair(const void* x, const void* W, void* y, int M, int N, int K, int 
   if (make_map(&ma, x, M, K, BM)) return -1;
   if (make_map(&mb, W, N, K, BN / 2)) return -1;
   static const int shallow_env = getenv("CBX_GEMM_SHALLOW") ? atoi(getenv("CBX_GEMM_SHALLOW")) : 1;
-  const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * 148;
+  const bool shallow = shallow_env != 0 && (int64_t)n_tiles * m_tiles * splits >= 2 * sm_count();
   const int n_stages = shallow ? C::kStagesShallow : C::kStages;
   const int smem_bytes = shallow ? C::kSmemShallow : C::kSmem;
   cudaError_t e = launch_pdl_cluster(gemm_tc_kernel<BN, EPI, 2>, dim3(m_tiles, n_tiles, splits), dim3(kThreads), smem_bytes, s, 2,
@@ -640,23 +640,23 @@ int gemm_qkv_rope(const void* h, const void* Wqkv, void* qkv, const void* cos_si
                   const int64_t* slot, void* kv_layer, int M, cudaStream_t s, const float* wscale) {
   EpiArgs ea = {(const bf16*)cos_sin, pos, slot, (uint8_t*)kv_layer};
   if (wscale) {
-    if ((M + BM - 1) / BM * 24 >= 2 * 148) return launch8<128, 2>(h, Wqkv, wscale, qkv, M, 3072, 1024, 3072, s, ea);
+    if ((M + BM - 1) / BM * 24 >= 2 * sm_count()) return launch8<128, 2>(h, Wqkv, wscale, qkv, M, 3072, 1024, 3072, s, ea);
     return launch8<64, 2>(h, Wqkv, wscale, qkv, M, 3072, 1024, 3072, s, ea);
   }
   if (const int w = pair_width(M, 8192)) return launch_pair_w<2>(w, h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   // prefill-sized M: 128-wide tiles (two heads per tile) halve the activation re-reads
-  if ((M + BM - 1) / BM * 24 >= 2 * 148) return launch<128, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
+  if ((M + BM - 1) / BM * 24 >= 2 * sm_count()) return launch<128, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
   return launch<64, 2>(h, Wqkv, qkv, M, 3072, 1024, 3072, s, ea);
 }
 // EPI 3: res[M, N] = bf16(bf16(x·W^T) + res), N % 32 == 0.
 int gemm_residual(const void* x, const void* W, void* res, int M, int N, int K, cudaStream_t s, const float* wscale) {
   CBX_REQUIRE(N % 128 == 0 && K % BK == 0, "gemm_residual: bad shape N=%d K=%d", N, K);
   if (wscale) {
-    const bool narrow8 = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
+    const bool narrow8 = (int64_t)((M + BM - 1) / BM) * (N / 128) < sm_count();
     return narrow8 ? launch8<64, 3>(x, W, wscale, res, M, N, K, N, s) : launch8<128, 3>(x, W, wscale, res, M, N, K, N, s);
   }
   if (const int w = pair_width(M, 4096)) return launch_pair_w<3>(w, x, W, res, M, N, K, N, s);
-  const bool narrow = (int64_t)((M + BM - 1) / BM) * (N / 128) < 148;
+  const bool narrow = (int64_t)((M + BM - 1) / BM) * (N / 128) < sm_count();
   return narrow ? launch<64, 3>(x, W, res, M, N, K, N, s) : launch<128, 3>(x, W, res, M, N, K, N, s);
 }
 // EPI 4: part[splits][M][N] fp32 = per-K-slice partial products (no rounding); N % 64 == 0.

@@ -593,7 +593,7 @@ int launch_stream(const GemvArgs& a, cudaStream_t s) {
   constexpr int ROWB = KSEG * 1024 * (W8 ? 1 : 2);
   const int n_items = a.N / 2;
   // one CTA per SM when the items allow it; at least NW/2 items per CTA so the warps have work
-  int ipc = (n_items + 147) / 148;
+  int ipc = (n_items + sm_count() - 1) / sm_count();
   if (ipc < NW / 2) ipc = NW / 2;
   const int grid = (n_items + ipc - 1) / ipc;
   const int smem = ipc * 2 * ROWB + TT * KSEG * 1024 * 2 + 16;
@@ -640,7 +640,7 @@ int dispatch_t(const GemvArgs& a, int grid, cudaStream_t s) {
 // one warp per item when that needs <= one CTA per SM, else 148 CTAs looping
 inline int grid_for(int n_items, int items_per_cta) {
   const int g = (n_items + items_per_cta - 1) / items_per_cta;
-  return g < 148 ? g : 148;
+  return g < sm_count() ? g : sm_count();
 }
 }  // namespace
 

@@ -19,6 +19,17 @@ void set_error(const char* fmt, ...) {
 }
 int count_launch() { ++g_launches; return 0; }
 int64_t launches() { return g_launches; }
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      n = v < kMaxSms ? v : kMaxSms;
+    else
+      return kMaxSms;
+  }
+  return n;
+}
 bool pdl_enabled() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("CBX_PDL"); v = (e && e[0] == '0') ? 0 : 1; }

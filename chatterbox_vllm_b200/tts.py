@@ -104,13 +104,16 @@ class ChatterboxTTS:
     def __init__(self, target_device: str, max_model_len: int, t3: T3Engine, tokenizer,
                  emotion_adv_fc: torch.Tensor | None = None, default_cond_emb: torch.Tensor | None = None,
                  default_s3gen_ref: dict | None = None, vocoder: Callable | None = None,
-                 conditioner: Callable | None = None, variant: str = "english"):
+                 conditioner: Callable | None = None, variant: str = "english", default_conds: dict | None = None):
         self.target_device, self.max_model_len = target_device, max_model_len
         self.t3, self.tokenizer, self.variant = t3, tokenizer, variant
         self.emotion_adv_fc = emotion_adv_fc          # cond_enc.emotion_adv_fc.weight [1024, 1] fp32
         self.cond_encoder = None                      # T3CondEncoder when the checkpoint carries cond_enc.*
         self.default_cond_emb, self.default_s3gen_ref = default_cond_emb, default_s3gen_ref or {}
         self.vocoder, self.conditioner = vocoder, conditioner
+        # conds.pt of the checkpoint (tts.py:52-62 `Conditionals.load`): {"t3": {speaker_emb [1,256], cond_prompt_speech_tokens
+        # [1,150], ...}, "gen": S3Gen reference dict} — the built-in voice used when no audio prompt is given
+        self.default_conds = default_conds
         self._cond_cache: dict = {}
         self.last_t3_seconds = 0.0
 
@@ -124,7 +127,7 @@ class ChatterboxTTS:
                         max_batch_size: int = 10, variant: str = "english", **kwargs) -> "ChatterboxTTS":
         """Build from an in-memory T3 checkpoint (key layout of t3_cfg.safetensors) — used with
         random-init weights where there is no network."""
-        extra = {k: kwargs.pop(k) for k in ("default_cond_emb", "default_s3gen_ref", "vocoder", "conditioner")
+        extra = {k: kwargs.pop(k) for k in ("default_cond_emb", "default_s3gen_ref", "vocoder", "conditioner", "default_conds")
                  if k in kwargs}
         max_pairs = kwargs.pop("max_pairs", None) or kwargs.pop("max_num_seqs", None) or max_batch_size
         eng = T3Engine(state_dict, device=target_device if target_device != "cuda" else "cuda:0",
@@ -139,25 +142,29 @@ class ChatterboxTTS:
                                              device=str(eng.device))
         return tts
 
+    T3_WEIGHTS = {"english": "t3_cfg.safetensors", "multilingual": "t3_23lang.safetensors"}     # tts.py:104
+
     @classmethod
     def from_local(cls, ckpt_dir: Union[str, Path], target_device: str = "cuda", max_model_len: int = 1000,
                    compile: bool = False, max_batch_size: int = 10, variant: str = "english",
                    s3gen_use_fp16: bool = False, **kwargs) -> "ChatterboxTTS":
         """tts.py:91-158.  ``compile`` / ``s3gen_use_fp16`` are accepted for signature compatibility
-        (the engine always replays CUDA graphs; S3Gen is not part of this path)."""
+        (the engine always replays CUDA graphs; S3Gen is not part of this path).  ``tokenizer=`` overrides
+        the text tokenizer (default: EnTokenizer / MTLTokenizer resolved from ckpt_dir, as the reference's
+        vLLM tokenizer registry would).  conds.pt, when present, becomes the built-in voice (tts.py:151)."""
         from safetensors.torch import load_file
-        from .tokenizer import EnTokenizer
+        from .tokenizer import EnTokenizer, MTLTokenizer
         ckpt_dir = Path(ckpt_dir)
-        if variant != "english":
-            raise NotImplementedError("multilingual text front-end (MTLTokenizer) is out of this path's scope; "
-                                      "use from_state_dict with your own tokenizer")
-        sd = load_file(str(ckpt_dir / "t3_cfg.safetensors"))
-        tok = EnTokenizer.from_pretrained(str(ckpt_dir))
-        tts = cls.from_state_dict(sd, tok, target_device, max_model_len, max_batch_size, variant, **kwargs)
+        if variant not in cls.T3_WEIGHTS:
+            raise ValueError(f"variant {variant!r}: expected 'english' or 'multilingual'")
+        sd = load_file(str(ckpt_dir / cls.T3_WEIGHTS[variant]))
+        tok = kwargs.pop("tokenizer", None)
+        if tok is None:
+            tok = (EnTokenizer if variant == "english" else MTLTokenizer).from_pretrained(str(ckpt_dir))
         conds = ckpt_dir / "conds.pt"
-        if conds.exists() and tts.conditioner is not None:
-            tts.default_conds_path = str(conds)
-        return tts
+        if conds.exists() and "default_conds" not in kwargs:
+            kwargs["default_conds"] = torch.load(str(conds), weights_only=True, map_location="cpu")
+        return cls.from_state_dict(sd, tok, target_device, max_model_len, max_batch_size, variant, **kwargs)
 
     @classmethod
     def from_pretrained(cls, repo_id: str = REPO_ID, revision: str = "1b475dffa71fb191cb6d5901215eb6f55635a9b6",
@@ -169,6 +176,17 @@ class ChatterboxTTS:
             local_path = hf_hub_download(repo_id=repo_id, filename=fpath, revision=revision)
         return cls.from_local(Path(local_path).parent, *args, variant="english", **kwargs)
 
+    @classmethod
+    def from_pretrained_multilingual(cls, repo_id: str = REPO_ID, revision: str = "c819eeccdf99310da26bca3bc5ace120db93471a",
+                                     *args, **kwargs) -> "ChatterboxTTS":
+        """tts.py:192-206 — the 23-language checkpoint through the same class (variant="multilingual"); needs network.
+        (The reference also symlinks the weights into ./t3-model-multilingual for vLLM; nothing reads that here.)"""
+        from huggingface_hub import hf_hub_download
+        local_path = None
+        for fpath in ("t3_23lang.safetensors", "mtl_tokenizer.json", "conds.pt", "Cangjie5_TC.json"):
+            local_path = hf_hub_download(repo_id=repo_id, filename=fpath, revision=revision)
+        return cls.from_local(Path(local_path).parent, *args, variant="multilingual", **kwargs)
+
     def get_supported_languages(self) -> dict[str, str]:
         return SUPPORTED_LANGUAGES.copy() if self.variant == "multilingual" else {"en": "English"}
 
@@ -178,6 +196,13 @@ class ChatterboxTTS:
         reference's lru_cache(10)."""
         if wav_fpath in self._cond_cache:
             return self._cond_cache[wav_fpath]
+        if wav_fpath is None and self.default_cond_emb is None and self.default_conds is not None:
+            # tts.py:217-220,238-247: the built-in voice = conds.pt's speaker embedding + prompt speech tokens through
+            # T3CondEnc (on the device); its "gen" dict is the vocoder's reference
+            t3c = self.default_conds["t3"]
+            ref, emb = self.conditionals_from_features(t3c["speaker_emb"].reshape(-1), t3c["cond_prompt_speech_tokens"].reshape(-1),
+                                                       s3gen_ref=self.default_conds.get("gen", {}))
+            self.default_s3gen_ref, self.default_cond_emb = ref, emb
         if wav_fpath is None and self.default_cond_emb is not None:
             out = (self.default_s3gen_ref, self.default_cond_emb)
         elif self.conditioner is not None:
@@ -245,6 +270,16 @@ class ChatterboxTTS:
             out = [f"<{language_id.lower()}>{p}" for p in out]                      # tts.py:330-333
         return out
 
+    def _check_languages(self, language_id) -> None:                                # tts.py:316-322
+        if language_id and language_id.lower() not in self.get_supported_languages():
+            raise ValueError(f"Unsupported language_id '{language_id}'. Supported languages: "
+                             + ", ".join(self.get_supported_languages().keys()))
+
+    def _clamp_sampling(self, language_id) -> bool:                                 # tts.py:350-355
+        return bool(language_id)
+
+    PENALIZE_PROMPT_IDS = None          # None: by variant (the multilingual text ids reach vLLM's prompt-penalty mask)
+
     def generate_tokens(self, prompts: Union[str, list[str]], cond_emb: torch.Tensor,
                         language_id: Optional[str] = "en", temperature: float = 0.8, exaggeration: float = 0.5,
                         max_tokens=1000, top_p=1.0, repetition_penalty=2.0, raw: bool = False,
@@ -254,14 +289,12 @@ class ChatterboxTTS:
         stop token included, like ``output.token_ids``)."""
         if isinstance(prompts, str):
             prompts = [prompts]
-        if language_id and language_id.lower() not in self.get_supported_languages():
-            raise ValueError(f"Unsupported language_id '{language_id}'. Supported languages: "
-                             + ", ".join(self.get_supported_languages().keys()))
+        self._check_languages(language_id)
         cond_emb = self.update_exaggeration(cond_emb, exaggeration)
         wrapped = self.wrap_prompts(prompts, language_id)
         # sampling clamps (tts.py:350-362)
         temp_use, top_p_use = temperature, top_p
-        if language_id:
+        if self._clamp_sampling(language_id):
             temp_use, top_p_use = min(temperature, 0.5), min(top_p, 0.5)
         if _env_flag("CHATTERBOX_DETERMINISTIC"):
             temp_use, top_p_use = 0.0, 1.0
@@ -281,7 +314,8 @@ class ChatterboxTTS:
                 raise ValueError(f"prompt of {len(ids)} text tokens does not fit max_model_len={self.max_model_len}")
             sp = SamplingParams(temperature=temp_use, top_p=top_p_use, repetition_penalty=repetition_penalty,
                                 max_tokens=min(cap, budget), **sp_kw)
-            reqs.append(Request(ids, cond_emb, sp, penalize_prompt_ids=self.variant == "multilingual"))
+            pen = self.variant == "multilingual" if self.PENALIZE_PROMPT_IDS is None else self.PENALIZE_PROMPT_IDS
+            reqs.append(Request(ids, cond_emb, sp, penalize_prompt_ids=pen))
         crop = int(os.environ.get("CHATTERBOX_TAIL_CROP_TOKENS", "2"))
         t0 = time.time()
         with torch.inference_mode():

@@ -13,6 +13,7 @@ Fixtures and what pins them:
   t3_glue.npz          the REFERENCE'S OWN models/t3/t3.py glue (T3MultiModalProcessor.apply, split_prefill_decode,
                        get_input_embeddings, compute_logits, create_triangular_matrix) executed from /root/reference with
                        the vllm imports stubbed, on oracle.glue_cases inputs
+  mtl_tokenizer.json   the REFERENCE'S OWN MTLTokenizer (models/t3/mtl_tokenizer.py) on its packaged vocabulary
   cond_enc.npz         the REFERENCE'S OWN T3CondEnc / Perceiver modules (models/t3/modules/cond_enc.py,
                        perceiver.py) run on seeded weights and inputs (oracle.cond_ref.random_*)
 """
@@ -410,10 +411,45 @@ def t3_glue():
     print("t3_glue keys:", len(out), "bytes:", os.path.getsize(os.path.join(OUT, "t3_glue.npz")))
 
 
+def mtl_tokenizer():
+    """The reference's own MTLTokenizer (models/t3/mtl_tokenizer.py, executed from /root/reference on its packaged
+    mtl_tokenizer.json) on prompts in the languages whose normalisers need no third-party package here
+    -> tests/golden/mtl_tokenizer.json.  (HF_HUB_OFFLINE: its Cangjie download fails and it carries on, as it would
+    without network.)"""
+    import types
+    os.environ["HF_HUB_OFFLINE"] = "1"
+    base = f"{REF}/src/chatterbox_vllm"
+    saved = dict(sys.modules)
+    try:
+        pkg = types.ModuleType("chatterbox_vllm")
+        pkg.__path__ = [base]
+        sys.modules["chatterbox_vllm"] = pkg
+        spec = importlib.util.spec_from_file_location("chatterbox_vllm.text_utils", base + "/text_utils.py")
+        tu = importlib.util.module_from_spec(spec)
+        sys.modules["chatterbox_vllm.text_utils"] = tu
+        spec.loader.exec_module(tu)
+        spec = importlib.util.spec_from_file_location("ref_mtl_tokenizer", base + "/models/t3/mtl_tokenizer.py")
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        tok = mod.MTLTokenizer(vocab_file=base + "/models/t3/mtl_tokenizer.json")
+        cases = [("[START]Hello there, General Kenobi.[STOP]", None), ("[START]Hello there.[STOP]", "en"),
+                 ("[fr][START]Bonjour le monde, ça va ?[STOP]", None), ("[de][START]Über den Wolken.[STOP]", None),
+                 ("[ko][START]안녕하세요. 반갑습니다.[STOP]", None), ("[START]안녕하세요.[STOP]", "ko"),
+                 ("[es][START]¿Dónde está la biblioteca?[STOP]", None), ("[xx][START]Not a language tag.[STOP]", None),
+                 ("[START]ＦＵＬＬ width and ﬁ ligature[STOP]", "en"), ("[tr][START]İstanbul'da hava güzel.[STOP]", None)]
+        out = [dict(text=t, language_id=l, ids=[int(i) for i in tok.encode(t, language_id=l)]) for t, l in cases]
+        json.dump(dict(vocab_size=tok.get_vocab_size(), cases=out), open(f"{OUT}/mtl_tokenizer.json", "w"), ensure_ascii=False)
+    finally:
+        for k in list(sys.modules):
+            if k not in saved:
+                del sys.modules[k]
+        sys.modules.update(saved)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     only = sys.argv[1:]
-    for fn in (hf_backbone, rope, sampler, block_pool, prompt_lengths, cond_enc, t3_glue):
+    for fn in (hf_backbone, rope, sampler, block_pool, prompt_lengths, cond_enc, t3_glue, mtl_tokenizer):
         if only and fn.__name__ not in only:
             continue
         try:
