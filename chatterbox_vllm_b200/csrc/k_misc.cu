@@ -157,6 +157,8 @@ __global__ void __launch_bounds__(128) prefill_embed_kernel(
     o.y = pack_bf16(bf_lo(a.y) + bf_lo(b.y), bf_hi(a.y) + bf_hi(b.y));
     o.z = pack_bf16(bf_lo(a.z) + bf_lo(b.z), bf_hi(a.z) + bf_hi(b.z));
     o.w = pack_bf16(bf_lo(a.w) + bf_lo(b.w), bf_hi(a.w) + bf_hi(b.w));
+  } else if (d.x == 4) {                               // an already generated speech token: the decode embedding (t3.py:503-514)
+    o = speech_emb[(size_t)d.y * 128 + t];
   }
   x[(size_t)r * 128 + t] = o;
 }

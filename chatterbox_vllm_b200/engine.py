@@ -58,6 +58,8 @@ class Request:
     params: SamplingParams
     uid: int = 0
     penalize_prompt_ids: bool = False   # MTL quirk: prompt ids ≥1000 hit speech id−1000
+    history: list = field(default_factory=list)   # scheduler-internal: speech ids (no offset) this request had already
+                                                  # emitted when it was preempted; its KV is recomputed over them
 
 
 class T3Engine:
@@ -106,6 +108,8 @@ class T3Engine:
         elif self.weight_dtype != "bf16":
             raise ValueError(f"weight_dtype {self.weight_dtype!r}: expected 'bf16' or 'fp8_e4m3'")
         self.gpu_launches = 0
+        self._rows: dict[int, list[int]] = {}             # block-table row -> its blocks, in table order
+        self.preemptions = 0
 
     # ------------------------------------------------------------------ weights
     def _load_weights(self, sd: dict, rms_eps: float) -> None:
@@ -208,10 +212,14 @@ class T3Engine:
         self.buffer("slot", (2 * B,), torch.int64).fill_(-1)
         self.buffer("row_seq", (2 * B,), torch.int32).copy_(torch.arange(2 * B, dtype=torch.int32, device=self.device))
 
-    def _admit(self, reqs: list[Request], slots: list[int] | None = None) -> tuple[list[int], list[list[int]]]:
-        """Reserve KV blocks for prompt + max_tokens of both members of every pair (rows b and B+b of
-        the block table, B = slot count of this call) and upload those rows.  With slots=None the
-        requests take slots 0..n-1 of a fresh n-slot batch.  Returns prefix lengths and block lists."""
+    def _admit(self, reqs: list[Request], slots: list[int] | None = None,
+               lookahead: int | None = None) -> tuple[list[int], list[list[int]]]:
+        """Give both members of every pair (rows b and B+b of the block table, B = slot count of this call) their
+        first KV blocks and upload those rows.  lookahead=None reserves prompt + max_tokens up front (callers that
+        drive decode() themselves: bench, tests); lookahead=k allocates as vLLM does — cdiv(tokens, 16) blocks for
+        the tokens that can exist before the next top-up (prefix + first token + k), the rest arriving through
+        _grow() (vllm v1/core/single_type_kv_cache_manager.py:120).  With slots=None the requests take slots
+        0..n-1 of a fresh n-slot batch.  Returns prefix lengths and the rows' block lists (the lists grow in place)."""
         if slots is None:
             slots = list(range(len(reqs)))
             self._reset_slots(len(reqs))
@@ -221,22 +229,60 @@ class T3Engine:
             p = COND_LEN + len(r.text_ids) + 1
             if p + r.params.max_tokens > self.max_model_len:
                 raise ValueError(f"prompt ({p}) + max_tokens ({r.params.max_tokens}) exceeds max_model_len")
-            P.append(p)
+            P.append(p + len(r.history))                   # rows to prefill: the prefix + what was generated before a preemption
         for half in range(2):
             for j, r in enumerate(reqs):
-                blks = self.pool.alloc(-(-(P[j] + r.params.max_tokens) // BLOCK_SIZE))
+                n_tok = P[j] - len(r.history) + r.params.max_tokens
+                if lookahead is not None:
+                    n_tok = min(n_tok, P[j] + 1 + lookahead)
+                blks = self.pool.alloc(-(-n_tok // BLOCK_SIZE))
                 row = np.zeros(self.bt_stride, np.int32)
                 row[:len(blks)] = blks
                 rows.append(row)
                 ids.append(half * B + slots[j])
                 held.append(blks)
+                self._rows[half * B + slots[j]] = blks
         self.block_table.index_copy_(0, torch.tensor(ids, device=self.device),
                                      torch.from_numpy(np.stack(rows)).to(self.device))
         return P, held
 
+    def _grow(self, want: list[tuple[int, int]]) -> bool:
+        """Top block-table rows up so that row r can hold n tokens, for (r, n) in `want` — in that order, cdiv(n, 16)
+        blocks per row, new blocks popped from the pool's free queue exactly as vLLM's KV-cache manager does while a
+        request decodes.  All or nothing: returns False (and allocates nothing) when the pool cannot serve every row."""
+        need = [(r, -(-n // BLOCK_SIZE) - len(self._rows[r])) for r, n in want]
+        if sum(k for _, k in need if k > 0) > self.pool.num_free():
+            return False
+        rr, cc, bb = [], [], []
+        for r, k in need:
+            if k <= 0:
+                continue
+            blks = self.pool.alloc(k)
+            n0 = len(self._rows[r])
+            rr += [r] * k
+            cc += list(range(n0, n0 + k))
+            bb += blks
+            self._rows[r].extend(blks)
+        if rr:
+            dev = self.device
+            self.block_table.index_put_((torch.tensor(rr, device=dev), torch.tensor(cc, device=dev)),
+                                        torch.tensor(bb, dtype=torch.int32, device=dev))
+        return True
+
     def _release(self, held: list[list[int]]) -> None:
         for blks in held:                                  # vLLM frees a request's blocks in reverse order
             self.pool.free(list(reversed(blks)))
+            for r in [r for r, v in self._rows.items() if v is blks]:
+                del self._rows[r]
+
+    def _park_slot(self, b: int) -> None:
+        """Make pair slot b inert on the device (as _reset_slots leaves an empty slot): finished, nothing staged —
+        kv_len 0 so attention skips its rows, slot -1 so nothing is written to blocks it no longer owns."""
+        B = self._B
+        idx = torch.tensor([b, B + b], device=self.device)
+        self.sb.finished[b] = 1
+        self.buffer("kv_len", (2 * B,), torch.int32)[idx] = 0
+        self.buffer("slot", (2 * B,), torch.int64)[idx] = -1
 
     def _init_sampler_state(self, reqs: list[Request], P: list[int], slots: list[int] | None = None) -> None:
         sb, dev, B = self.sb, self.device, self._B
@@ -254,7 +300,10 @@ class T3Engine:
         seeds = [(p.seed if p.seed is not None else self.base_seed) & (2**63 - 1) for p in pr]
         sb.seed[idx] = up(seeds, torch.int64)
         sb.uid[idx] = up([r.uid for r in reqs], torch.int64)
-        sb.n_out[idx] = 0
+        sb.n_out[idx] = up([len(r.history) for r in reqs], torch.int32)
+        for j, r in enumerate(reqs):                       # a recomputed request keeps the tokens it had emitted
+            if r.history:
+                sb.out_tokens[slots[j], :len(r.history)] = up(r.history, torch.int32)
         sb.finished[idx] = 0
         # cache holds P tokens after prefill; the prefill-time sample call adds 1, so start at P-1
         lens = up([p - 1 for p in P], torch.int32)
@@ -267,6 +316,8 @@ class T3Engine:
                     if t >= SPEECH_TOKEN_OFFSET and t - SPEECH_TOKEN_OFFSET < SPEECH_VOCAB:
                         sp_id = t - SPEECH_TOKEN_OFFSET
                         seen[j, sp_id >> 5] |= np.uint32(1 << (sp_id & 31))
+            for sp_id in r.history:
+                seen[j, sp_id >> 5] |= np.uint32(1 << (sp_id & 31))
         sb.seen[idx] = torch.from_numpy(seen.view(np.int32)).to(dev)
 
     def prefill(self, reqs: list[Request], P: list[int], slots: list[int] | None = None) -> None:
@@ -308,7 +359,9 @@ class T3Engine:
                 text_c[:, 0], text_c[:, 1], text_c[:, 2] = 1, ids, np.arange(nt)
                 text_u = np.zeros((nt, 4), np.int32)
                 text_u[:, 0] = 2
-                desc_p += [cond_rows.copy(), text_c, sos_row, cond_rows.copy(), text_u, sos_row]
+                hist = np.zeros((len(reqs[j].history), 4), np.int32)      # generated tokens: decode embeddings, both members
+                hist[:, 0], hist[:, 1] = 4, np.asarray(reqs[j].history, np.int32)
+                desc_p += [cond_rows.copy(), text_c, sos_row, hist, cond_rows.copy(), text_u, sos_row, hist]
                 ar = np.arange(P[j], dtype=np.int32)
                 for half in range(2):
                     starts.append(T), plens.append(P[j]), btrows.append(half * B + slots[j])
@@ -356,9 +409,27 @@ class T3Engine:
         included, like vLLM's output.token_ids."""
         self.stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.stream):
-            out = self._generate(reqs, poll_every)
+            out: list = [None] * len(reqs)
+            for i, toks, _ in self._run(reqs, poll_every):
+                out[i] = toks
         torch.cuda.current_stream().wait_stream(self.stream)
         return out
+
+    def generate_stream(self, reqs: list[Request], every: int = 32):
+        """Streaming emission for the server caller (reference: openai_tts_server.py:392-528 consumes T3 tokens as
+        they appear): a generator of (request index, new token ids in vLLM id space, finished) — each request's
+        tokens since its last event, handed over every `every` decode steps from the device token ring.  The
+        concatenation of a request's events is exactly what generate() returns for it."""
+        self.stream.wait_stream(torch.cuda.current_stream())
+        it = self._run(reqs, every, stream=True)
+        while True:
+            with torch.cuda.stream(self.stream):
+                try:
+                    ev = next(it)
+                except StopIteration:
+                    break
+            yield ev
+        torch.cuda.current_stream().wait_stream(self.stream)
 
     def generate_device(self, reqs: list[Request], tail_crop: int = 2, guard_caps: list[int] | None = None,
                         poll_every: int = 32) -> tuple[torch.Tensor, torch.Tensor]:
@@ -372,62 +443,119 @@ class T3Engine:
         caps = None if guard_caps is None else torch.tensor(guard_caps, dtype=torch.int32, device=self.device)
         self.stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.stream):
-            self._generate(reqs, poll_every, handoff=(dst, dst_len, caps, tail_crop))
+            for _ in self._run(reqs, poll_every, handoff=(dst, dst_len, caps, tail_crop)):
+                pass
         torch.cuda.current_stream().wait_stream(self.stream)
         return dst[:n], dst_len[:n]
 
     def _generate(self, reqs: list[Request], poll_every: int, handoff=None) -> list[list[int]]:
+        out: list = [None] * len(reqs)
+        for i, toks, _ in self._run(reqs, poll_every, handoff=handoff):
+            out[i] = toks
+        return out
+
+    def _run(self, reqs: list[Request], poll_every: int, handoff=None, stream: bool = False):
+        """The scheduler loop (a generator).  KV blocks follow the sequences as in vLLM: a pair is admitted when the
+        pool holds the blocks for its prefix plus one poll window (on top of what the running pairs need for their
+        next window), every window tops each running row up to cdiv(tokens, 16) blocks, and when the pool runs dry
+        the most recently admitted pair is preempted — its blocks go back, it rejoins the queue's head and, once
+        re-admitted, its KV is recomputed over prefix + the tokens it had already emitted, after which it carries on
+        from there (vLLM v1's preemption = recompute; nothing already handed out is generated again)."""
         n = len(reqs)
         if n == 0:
-            return []
+            return
         for r in reqs:
             if r.uid == 0:
                 self._next_uid += 1
                 r.uid = self._next_uid
         B = min(self.max_pairs, n)
         self._reset_slots(B)
-        out: list = [None] * n
         slot_req: list = [None] * B                            # request index living in each slot
         slot_held: dict = {}
         slot_len = [0] * B                                     # host upper bound of each slot's context length
-        nxt = 0
+        slot_seq = [0] * B                                     # admission order (the newest is preempted first)
+        slot_emitted = [0] * B                                 # tokens of the slot's request already handed out (stream)
+        history: dict = {}                                     # request index -> speech ids emitted before its preemption
+        pending = list(range(n))
+        admissions = 0
+
+        def next_window_blocks() -> int:                       # blocks the running pairs take at their next top-up
+            tot = 0
+            for b in range(B):
+                if slot_req[b] is not None:
+                    cap = slot_held[b][2] + reqs[slot_req[b]].params.max_tokens
+                    tot += 2 * max(0, -(-min(cap, slot_len[b] + poll_every) // BLOCK_SIZE) - len(self._rows[b]))
+            return tot
         try:
             while True:
                 free = [b for b in range(B) if slot_req[b] is None]
                 new_slots, new_reqs = [], []
-                while nxt < n and free:
-                    r = reqs[nxt]
-                    need = 2 * -(-(COND_LEN + len(r.text_ids) + 1 + r.params.max_tokens) // BLOCK_SIZE)
-                    if need > self.pool.num_free():
-                        if not any(q is not None for q in slot_req) and not new_slots:
+                while pending and free:
+                    i = pending[0]
+                    r = reqs[i]
+                    if i in history:                           # recompute: same request, with what it had emitted
+                        r = Request(r.text_ids, r.cond_emb, r.params, r.uid, r.penalize_prompt_ids, history[i])
+                    p0 = COND_LEN + len(r.text_ids) + 1
+                    first = min(p0 + r.params.max_tokens, p0 + len(r.history) + 1 + poll_every)
+                    running = sum(q is not None for q in slot_req)
+                    if 2 * -(-first // BLOCK_SIZE) + next_window_blocks() > self.pool.num_free():
+                        if running == 0:
                             raise ValueError("KV pool too small for a single request")
                         break
                     b = free.pop(0)
-                    slot_req[b] = nxt
+                    slot_req[b] = pending.pop(0)
                     new_slots.append(b)
                     new_reqs.append(r)
-                    nxt += 1
+                    admissions += 1
+                    slot_seq[b] = admissions
                     # reserve now so the next fit check sees the pool shrink
-                    P1, held1 = self._admit([r], [b])
-                    slot_held[b] = (P1[0], held1)
+                    P1, held1 = self._admit([r], [b], lookahead=poll_every)
+                    slot_held[b] = (P1[0], held1, p0)          # rows prefilled, block lists, prefix length
+                    slot_len[b] = P1[0] + 1
+                    slot_emitted[b] = len(r.history)
                 if new_slots:
                     P = [slot_held[b][0] for b in new_slots]
                     self._init_sampler_state(new_reqs, P, new_slots)
                     self.prefill(new_reqs, P, new_slots)
-                    for b, p in zip(new_slots, P):
-                        slot_len[b] = p + 1
                 active = [b for b in range(B) if slot_req[b] is not None]
                 if not active:
                     break
-                remaining = max(reqs[slot_req[b]].params.max_tokens - (slot_len[b] - slot_held[b][0]) for b in active)
+                cap = lambda b: slot_held[b][2] + reqs[slot_req[b]].params.max_tokens      # noqa: E731
+                remaining = max(cap(b) - slot_len[b] for b in active)
                 if remaining > 0:
                     steps = min(poll_every, remaining)
+                    while True:                                # blocks for this window: cdiv(tokens, 16) per row, slot order
+                        want = []
+                        for b in active:
+                            tok = min(cap(b), slot_len[b] + steps)
+                            want += [(b, tok), (B + b, tok)]
+                        if self._grow(want):
+                            break
+                        if len(active) == 1:
+                            raise ValueError("KV pool too small for a single request")
+                        victim = max(active, key=lambda b: slot_seq[b])
+                        n_v = int(self.sb.n_out[victim].item())  # what it has emitted so far stays emitted
+                        history[slot_req[victim]] = self.sb.out_tokens[victim, :n_v].cpu().tolist()
+                        self._park_slot(victim)
+                        self._release(slot_held.pop(victim)[1])
+                        pending.insert(0, slot_req[victim])
+                        slot_req[victim] = None
+                        active.remove(victim)
+                        self.preemptions += 1
                     self.decode(B, steps, max(slot_len[b] for b in active) + steps)
                     for b in active:
                         slot_len[b] += steps
                 fin = self.sb.finished[:B].cpu().tolist()      # the only host sync: every poll_every steps
                 done = [b for b in active if fin[b]]
-                if done and handoff is not None:            # retire on the device: post-process straight into the result rows
+                if stream:
+                    n_out = self.sb.n_out[:B].cpu().tolist()
+                    for b in active:
+                        lo = slot_emitted[b]
+                        if n_out[b] > lo or fin[b]:
+                            toks = (self.sb.out_tokens[b, lo:n_out[b]].cpu() + SPEECH_TOKEN_OFFSET).tolist()
+                            slot_emitted[b] = n_out[b]
+                            yield slot_req[b], toks, bool(fin[b])
+                elif done and handoff is not None:          # retire on the device: post-process straight into the result rows
                     dst, dst_len, caps, crop = handoff
                     rows = torch.tensor([slot_req[b] for b in done], dtype=torch.int32, device=self.device)
                     ops.postprocess_tokens(self.sb, torch.tensor(done, dtype=torch.int32, device=self.device), dst, rows,
@@ -437,14 +565,13 @@ class T3Engine:
                     n_out = self.sb.n_out[:B].cpu().tolist()
                     toks = self.sb.out_tokens[:B].cpu().numpy()
                     for b in done:
-                        out[slot_req[b]] = (toks[b, :n_out[b]] + SPEECH_TOKEN_OFFSET).tolist()
+                        yield slot_req[b], (toks[b, :n_out[b]] + SPEECH_TOKEN_OFFSET).tolist(), True
                 for b in done:
                     self._release(slot_held.pop(b)[1])
                     slot_req[b] = None
         finally:
             for _, held in slot_held.values():
                 self._release(held)
-        return out
 
     def close(self) -> None:
         if getattr(self, "_h", None):

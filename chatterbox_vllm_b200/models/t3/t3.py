@@ -124,8 +124,15 @@ class T3VllmModel(torch.nn.Module):
             raise ValueError(f"{N} rows exceed the engine's row capacity {e.max_rows // 2}")
         pos_l = [int(p) for p in positions.tolist()]
         if seq_ids is None:
+            # Without request ids the rows can only be ONE request's consecutive positions in slot 0 (a prefix chunk
+            # or its next decode row).  Anything else is ambiguous — rows of different requests would be written into
+            # one KV sequence and the logits would be silently wrong — so it is refused, not guessed.
             consecutive = all(pos_l[i + 1] == pos_l[i] + 1 for i in range(N - 1))
-            seq_l = [0] * N if consecutive else list(range(N))
+            others = {r % self.max_num_seqs for r in self._blocks} - {0}
+            if not consecutive or others:
+                raise ValueError("T3VllmModel.forward: seq_ids (the request slot of every row) is required when more than "
+                                 "one request is live or the rows are not one request's consecutive positions")
+            seq_l = [0] * N
         else:
             seq_l = [int(s) for s in seq_ids.tolist()]
         if N and (max(pos_l) >= self.max_model_len or max(seq_l) >= self.max_num_seqs or min(seq_l) < 0):

@@ -267,7 +267,9 @@ int cbx_postprocess_tokens(const int32_t* out_tokens, const int32_t* n_out, int 
 /* t3.py:548-569 (full-block prefill embeds).  desc int32 [T,4] = {kind, a, b, c}:
  * kind 0: cond_emb row  (a = request, b = row 0..33) from cond_emb fp32 [n_req,34,1024];
  * kind 1: text row       text_emb[a] + text_pos[b]; kind 2: zero row (uncond text);
- * kind 3: start-of-speech speech_emb[a] + speech_pos[b]. */
+ * kind 3: start-of-speech speech_emb[a] + speech_pos[b];
+ * kind 4: speech_emb[a] alone — the decode embedding of an already generated token (t3.py:503-514), for a preempted
+ *         request whose KV is recomputed over prefix + generated tokens (vLLM v1 preemption = recompute). */
 int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, const void* text_emb,
                       const void* text_pos, const void* speech_emb, const void* speech_pos,
                       void* x, int T, void* stream);

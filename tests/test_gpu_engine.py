@@ -200,13 +200,16 @@ def _requests(n, n_steps, seed=2, **sp):
     return reqs
 
 
-def _oracle_stream(w, reqs, cfg_scale, n_steps, teacher=None, **sp):
-    """Free-running (or teacher-forced) oracle decode; returns tokens and merged logits per step."""
+def _oracle_stream(w, reqs, cfg_scale, n_steps, teacher=None, prompt_seen=None, **sp):
+    """Free-running (or teacher-forced) oracle decode; returns tokens and merged logits per step.
+    prompt_seen[r]: speech ids already in request r's repetition-penalty mask (the multilingual prompt quirk)."""
     o = T3Oracle(w, "bf16")
     toks, logs = [], []
     for ri, r in enumerate(reqs):
         pair = o.new_pair()
         seen = np.zeros(8194, bool)
+        if prompt_seen is not None:
+            seen[list(prompt_seen[ri])] = True
         lg = o.prefill_pair(pair, r.cond_emb, r.text_ids, cfg_scale).numpy()
         tr, lr = [], []
         for s in range(n_steps):
@@ -221,16 +224,18 @@ def _oracle_stream(w, reqs, cfg_scale, n_steps, teacher=None, **sp):
         logs.append(lr)
     return toks, logs
 
-def assert_stream_parity(got, w, reqs, cfg_scale, n_steps, *, first_exact=8, min_agree=0.9, ulps=4.0, **sp):
+def assert_stream_parity(got, w, reqs, cfg_scale, n_steps, *, first_exact=8, min_agree=0.9, ulps=4.0, prompt_seen=None, **sp):
     """Greedy parity under bf16 accumulation-order noise: the oracle is teacher-forced with the
     engine's tokens; at every step the engine's token must be the oracle's argmax or lie within
     `ulps` bf16 ulps (2^-7 relative) of the oracle's top penalised logit (within ONE ulp during the
     first `first_exact` steps, where little rounding noise has accumulated), and >= min_agree of all
     steps must agree exactly."""
-    want, logs = _oracle_stream(w, reqs, cfg_scale, n_steps, teacher=got, **sp)
+    want, logs = _oracle_stream(w, reqs, cfg_scale, n_steps, teacher=got, prompt_seen=prompt_seen, **sp)
     agree = total = 0
     for r in range(len(reqs)):
         seen = np.zeros(8194, bool)
+        if prompt_seen is not None:
+            seen[list(prompt_seen[r])] = True
         for s in range(n_steps):
             total += 1
             if got[r][s] == want[r][s]:
