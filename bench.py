@@ -41,7 +41,9 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms from the positioning steps (the same decode kernels, run
+    just before the timed ones) to the end of the timed region, so that even a --steps 20 run carries >= 5 samples
+    under load."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -50,7 +52,7 @@ class ClockSampler:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(index), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+                                          "-i", str(index), "-lms", "50"], stdout=subprocess.PIPE, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except Exception:
@@ -87,6 +89,95 @@ def cpu_baseline_sample(pairs=8, prefix=450, steps=4, warmup=1, model=None):
             "ms_per_step": 1e3 * r["decode_s"] / steps}
 
 
+KNOBS = ("CBX_SKIP", "CBX_MEGA", "CBX_GEMV_STREAM", "CBX_BLOCK_STOP", "CBX_BLOCK_NOACC", "CBX_BLOCK_FUSED", "CBX_PDL",
+         "CBX_ATTN_BALANCED", "CBX_ATTN_SMALL", "CBX_O_UNSPLIT", "CBX_SPLIT_MAX_ROWS", "CBX_L2_PREFETCH", "CBX_GEMM_MC",
+         "CBX_ATTN_PLAN_EACH", "CBX_PREFILL_ROWWISE", "CBX_BENCH_LAYERS", "CBX_GEMV_MAX_T")
+
+
+def refuse_knobs():
+    """The library honours profiling / experiment switches (CBX_SKIP drops kernels: results are garbage).  A bench line
+    measured under one of them is not a bench line: refuse, unless the caller says it is a tuning run."""
+    on = [k for k in KNOBS if os.environ.get(k) not in (None, "")]
+    if on and os.environ.get("CBX_BENCH_ALLOW_KNOBS") != "1":
+        sys.exit(f"bench.py: refusing to run with {on} set (experiment / profiling switches change what is computed); "
+                 "set CBX_BENCH_ALLOW_KNOBS=1 for a tuning run — its line is marked and is not a bench value")
+    return on
+
+
+def oracle_weights(sd: dict, n_layers: int):
+    """The engine's checkpoint as the oracle's weight object (CPU copies; q/k/v and gate/up stacked)."""
+    from oracle.t3_ref import T3ModelConfig, T3Weights
+    c = lambda k: sd[k].detach().to("cpu")  # noqa: E731
+    w = T3Weights(T3ModelConfig(n_layers=n_layers, text_vocab=sd["text_emb.weight"].shape[0]))
+    for i in range(n_layers):
+        p = f"tfmr.layers.{i}."
+        w.wqkv.append(torch_cat([c(p + f"self_attn.{n}_proj.weight") for n in "qkv"]))
+        w.wo.append(c(p + "self_attn.o_proj.weight"))
+        w.wgu.append(torch_cat([c(p + "mlp.gate_proj.weight"), c(p + "mlp.up_proj.weight")]))
+        w.wd.append(c(p + "mlp.down_proj.weight"))
+        w.ln1.append(c(p + "input_layernorm.weight"))
+        w.ln2.append(c(p + "post_attention_layernorm.weight"))
+    w.norm, w.speech_emb, w.speech_head = c("tfmr.norm.weight"), c("speech_emb.weight"), c("speech_head.weight")
+    w.text_emb, w.text_pos, w.speech_pos = c("text_emb.weight"), c("text_pos_emb.emb.weight"), c("speech_pos_emb.emb.weight")
+    return w
+
+
+def torch_cat(ts):
+    import torch
+    return torch.cat(ts, 0)
+
+
+def oracle_probe(sd, n_layers, req, tokens, cfg_scale, seed, n=8):
+    """The e2e arm's first pair against the CPU oracle: teacher-forced with the engine's first n tokens, every token
+    must lie in the oracle's kept set after penalty / temperature / top-p (or within 8 bf16 ulps of the top logit of its
+    boundary), and with the same Philox counters most must be the very token the oracle draws.  A bench run whose
+    kernels computed something else (a skipped kernel, a stale buffer) fails here instead of printing a fast number."""
+    import numpy as np
+    from oracle import sampler_ref
+    from oracle.t3_ref import T3Oracle
+    o = T3Oracle(oracle_weights(sd, n_layers), "bf16")
+    pair = o.new_pair()
+    seen = np.zeros(8194, bool)
+    p = req.params
+    lg = o.prefill_pair(pair, req.cond_emb.float().cpu(), req.text_ids, cfg_scale).numpy()
+    same = 0
+    for s_ in range(n):
+        tok = tokens[s_] - 1000
+        l = sampler_ref.apply_repetition_penalty(lg, seen, p.repetition_penalty)
+        keep, _ = sampler_ref.kept_set(l, p.temperature, p.min_p, p.top_p, p.top_k)
+        floor = l[keep].min() - 8 * 2.0 ** -7 * abs(float(l.max()))
+        assert l[tok] >= floor, f"bench: e2e token {s_} of the probed pair ({tok}) is outside the oracle's kept set"
+        want = sampler_ref.sample_row(lg, seen, repetition_penalty=p.repetition_penalty, temperature=p.temperature,
+                                      min_p=p.min_p, top_p=p.top_p, top_k=p.top_k, seed=p.seed if p.seed is not None else seed,
+                                      uid=req.uid, step=s_)
+        same += int(want == tok)
+        seen[tok] = True
+        lg = o.decode_pairs([pair], [tok], cfg_scale)[0].numpy()
+    assert same >= n - 3, f"bench: only {same}/{n} of the probed pair's tokens are the oracle's draws"
+    return {"pair": 0, "steps": n, "in_kept_set": n, "identical_draws": same}
+
+
+def gpu_standin(dev, pairs=128, prefix=418, steps=64, warmup=4):
+    """A reference-class number on the same GPU: the reference's own GPU path (vllm==0.10.0 +
+    torch 2.7.1) cannot be installed here, so this is the stock-library stand-in for it — HF transformers' LlamaModel
+    (bf16, SDPA attention, its own KV cache) driven as Chatterbox drives T3: batch rows [cond; uncond] for every pair,
+    per-step CFG merge and a torch sampler.  None of this repo's kernels are on that path.  Timed like tts.py:407-420
+    times LLM.generate: wall clock around the decode loop, at the workload's mean context (prefix 418 + 64 steps)."""
+    import torch
+    from oracle import hf_baseline
+    m, emb, head, pos = hf_baseline.build_model(30, torch.bfloat16)
+    m = m.to(dev)
+    model = (m, emb.to(dev), head.to(dev), pos.to(dev))
+    torch.cuda.synchronize()
+    r = hf_baseline.run(pairs, prefix, steps, dtype=torch.bfloat16, model=model, warmup=warmup, device=dev)
+    del model, m
+    torch.cuda.empty_cache()
+    return {"value": r["tokens"] / r["decode_s"], "unit": "speech_tokens/s", "ms_per_step": 1e3 * r["decode_s"] / steps,
+            "what": f"HF transformers LlamaModel bf16 + SDPA + HF KV cache on this GPU, eager, {pairs} CFG pairs "
+                    f"({2 * pairs} rows), context {prefix}..{prefix + steps}, torch sampler; stand-in for the reference's "
+                    "vLLM-0.10 path, which cannot be installed offline"}
+
+
 def run_reference(args, rank, world):
     """Reference arm: the reference's CPU implementation of the path (no GPU code involved)."""
     if rank != 0:
@@ -118,6 +209,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-b1", action="store_true")
+    ap.add_argument("--no-probe", action="store_true", help="skip the CPU-oracle check of the e2e arm's first pair")
+    ap.add_argument("--no-standin", action="store_true", help="skip the stock-library GPU stand-in leg")
     ap.add_argument("--no-fp8", action="store_true", help="skip the separately reported FP8-e4m3 weight leg")
     ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8_e4m3"],
                     help="profiling aid: run the WHOLE bench on FP8 weights (the line then says so; the default line is bf16)")
@@ -131,6 +224,7 @@ def main():
         return run_reference(args, rank, world)
     args.steps = args.steps or 480
     args.warmup = max(3, 20 if args.warmup is None else args.warmup)
+    knobs = refuse_knobs()
 
     import torch
     import torch.distributed as dist
@@ -162,7 +256,8 @@ def main():
     max_tokens = 1 + pre + K
     max_len = PREFIX + max_tokens + 8
     n_layers = int(os.environ.get("CBX_BENCH_LAYERS", "30"))    # tuning aid only: the bench line is for 30
-    eng = T3Engine(random_state_dict(n_layers, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
+    sd = random_state_dict(n_layers, device=dev, seed=0)
+    eng = T3Engine(sd, device=dev, max_pairs=B, max_model_len=max(max_len, PREFIX + GEN + 8),
                    max_rows=16384, base_seed=1234 + rank, weight_dtype=args.weights)
     w_bytes = W_BYTES if args.weights == "bf16" else eng.projection_weight_bytes()
     sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=max_tokens, ignore_eos=True)
@@ -190,13 +285,13 @@ def main():
         p1.record(eng.stream)
         torch.cuda.synchronize()
         prefill_ms = p0.elapsed_time(p1)
+        clocks = ClockSampler(local)                            # from the positioning steps on: the same kernels, same load
         done = 0
         while done < pre:
             n = min(32, pre - done)
             eng.decode(B, n, PREFIX + 1 + done + n)
             done += n
         barrier()
-        clocks = ClockSampler(local)
         l0 = eng.gpu_launches
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record(eng.stream)
@@ -244,7 +339,7 @@ def main():
     # ---- end-to-end arm: public engine API, host buffers in, host token lists out
     e2e = None
     if not args.no_e2e:
-        gen_e2e = min(GEN, 1 + pre + K)
+        gen_e2e = GEN                                           # the workload's 500 tokens per pair, whatever --steps says
         sp2 = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=gen_e2e, ignore_eos=True)
         for r in reqs:
             r.params = sp2
@@ -264,8 +359,11 @@ def main():
         d2h = B * eng.max_model_len * 4 + B * 4 + 4 * (gen_e2e // 32 + 1)
         e2e = {"value": world * B * gen_e2e / float(dt.item()), "unit": "speech_tokens/s",
                "h2d_bytes_per_step": h2d / gen_e2e, "d2h_bytes_per_step": d2h / gen_e2e,
+               "gen_tokens_per_pair": gen_e2e, "mean_context": PREFIX + gen_e2e // 2, "seconds": float(dt.item()),
                "what": f"T3Engine.generate: pinned-host prompts+cond_emb in, prefill + {gen_e2e} tokens/pair, token lists out"}
         assert all(len(o) == gen_e2e for o in out)
+        if rank == 0 and args.weights == "bf16" and not args.no_probe:
+            e2e["oracle_probe"] = oracle_probe(sd, n_layers, reqs[0], out[0], eng.cfg_scale, eng.base_seed)
 
     # ---- M2 leg: p50 decode-step latency at B = 1 pair (config 1 shape: P = 75, 500 tokens)
     def b1_leg(e, wb):
@@ -401,6 +499,12 @@ def main():
         line["b1"] = b1
     if fp8:
         line["fp8w"] = fp8
+    if knobs:
+        line["tuning_run_not_a_bench_value"] = knobs
+    if not args.no_standin and world == 1 and args.weights == "bf16":
+        st = gpu_standin(dev)
+        st["this_over_standin"] = value / st["value"]
+        line["gpu_standin"] = st
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline_sample()
     print(json.dumps(line), flush=True)

@@ -291,14 +291,22 @@ extern "C" int cbx_engine_set_fp8_weights(cbx_engine* e, const cbx_fp8_weights* 
 // Every projection that closes a residual branch adds into res in its epilogue, so a layer is
 //   T <= 4 (GEMV regime, 5 kernels): [norm+QKV+RoPE+KV-append] [attention] [O+res] [norm+gate_up+SiLU] [down+res]
 //   T  > 4 (tcgen05 regime, 7)     : [norm] [QKV+RoPE+KV-append] [attention] [O+res] [norm] [gate_up+SiLU] [down+res]
+// Rows at or below which the weight-streaming GEMV kernels run instead of the tcgen05 GEMM (they exist for 1, 2 and 4
+// padded rows).  env CBX_GEMV_MAX_T=0 forces the tcgen05 path everywhere: the switch-point sweep of tools/bench_bsweep.py.
+static int gemv_max_t() {
+  static const int v = getenv("CBX_GEMV_MAX_T") ? atoi(getenv("CBX_GEMV_MAX_T")) : 4;
+  return v < 0 ? 0 : (v > 4 ? 4 : v);
+}
+
 static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, bool final_norm) {
   const size_t layer_bytes = (size_t)e->cfg.num_blocks * CBX_PAGE_BYTES;
   const float eps = e->w.rms_eps;
   const int sk = e->skip;
+  const int G = gemv_max_t();                            // rows up to which the GEMV regime runs (4)
   // split-K for the two N = 1024 projections when their 16 column tiles would leave most SMs idle
   const int m_tiles = (T + 127) / 128;
   int splits = 1;
-  if (T > 4 && !e->trace && T <= e->split_max_rows) splits = m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1);
+  if (T > G && !e->trace && T <= e->split_max_rows) splits = m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1);
   bool pending = false;                                // down-proj partials not yet folded into res
   // decode attention cuts the step's pages into equal per-CTA ranges: one plan serves all layers
   static const bool plan_each = getenv("CBX_ATTN_PLAN_EACH") != nullptr;   // debugging aid: rebuild the plan per layer
@@ -308,7 +316,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
     uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;
     // T <= 4, bf16 weights, context within the fused block's page buffer: the attention half of the layer is ONE kernel
     // (k_block.cu): [norm+QKV+RoPE+append+attention+O+res] [norm+gate_up+SiLU] [down+res] = 3 launches per layer
-    const bool fused = T <= 4 && !e->fp8 && !sk && !pf && e->n_prefill_items == 0 && layer_attn_block_supported(T, max_kv_len);
+    const bool fused = T <= G && !e->fp8 && !sk && !pf && e->n_prefill_items == 0 && layer_attn_block_supported(T, max_kv_len);
     if (fused) {
       // the block leaves the O-proj output in block_acc; gate_up's norm prologue closes the residual branch from it
       // (bf16(bf16(o) + res), written by its CTA 0 to buffer h — NOT in place: the other CTAs still read res); the
@@ -323,7 +331,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                         cudaMemcpyDeviceToDevice, s);
       continue;
     }
-    if (T <= 4) {
+    if (T <= G) {
       // each kernel pulls a LATER kernel's weights into L2 (QKV -> Wo, attention -> Wgu, O -> Wd, gate_up -> next Wqkv)
       if (!(sk & 1) && gemv_qkv_rope(e->res, e->ln1[li], e->wqkv[li], e->w.cos_sin, e->pos, e->slot, e->qkv, kv, T, eps, s,
                                      pf ? e->wo[li] : nullptr, (size_t)1024 * 1024 * 2, e->sqkv[li])) return -1;
@@ -339,7 +347,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                                               e->attn, s)) return -1;
     } else if (!(sk & 2) && paged_attn_decode_ex(e->qkv, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, e->attn,
                                                  e->attn_scratch, e->attn_counters, T, max_kv_len, have_plan, s)) return -1;
-    if (T <= 4) {
+    if (T <= G) {
       const bool last = li + 1 == e->w.n_layers;
       if (!(sk & 4) && gemv_residual(e->attn, e->wo[li], e->res, T, 1024, s, pf ? e->wd[li] : nullptr, (size_t)1024 * 4096 * 2,
                                      e->so[li])) return -1;
@@ -374,7 +382,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                       cudaMemcpyDeviceToDevice, s);
   }
   if (pending) return cbx_rmsnorm_reduce(e->part, splits, e->res, e->w.norm, e->h, T, eps, s);
-  if (final_norm || T > 4) return cbx_rmsnorm(e->res, nullptr, e->w.norm, e->h, T, eps, s);
+  if (final_norm || T > G) return cbx_rmsnorm(e->res, nullptr, e->w.norm, e->h, T, eps, s);
   return 0;
 }
 
@@ -443,7 +451,7 @@ extern "C" int cbx_engine_sample_subset(cbx_engine* e, int B, int n_sub, const i
 // One decode step for pair slots [0,B): inputs were staged by the previous sampler launch.
 static int decode_step(cbx_engine* e, int B, int max_kv_len, cudaStream_t s) {
   const int T = 2 * B;
-  if (T <= 4 && e->mega && e->n_prefill_items == 0 && !e->skip) {
+  if (T <= gemv_max_t() && e->mega && e->n_prefill_items == 0 && !e->skip) {
     MegaArgs a = {};
     for (int li = 0; li < e->w.n_layers; ++li) {
       a.ln1[li] = (const bf16*)e->ln1[li]; a.wqkv[li] = (const bf16*)e->wqkv[li]; a.wo[li] = (const bf16*)e->wo[li];
@@ -463,7 +471,7 @@ static int decode_step(cbx_engine* e, int B, int max_kv_len, cudaStream_t s) {
     if (rc == 0) return launch_cfg_sample(e->logits, &e->st, B, next_step(e), s);
   }
   if (forward_layers(e, T, max_kv_len, s, false)) return -1;
-  if (T <= 4) {                                         // final norm fused into the head GEMV
+  if (T <= gemv_max_t()) {                              // final norm fused into the head GEMV
     if (gemv_norm_head(e->res, e->w.norm, e->head, e->logits, T, CBX_SPEECH_VOCAB, CBX_LOGITS_LD,
                        e->w.rms_eps, s, e->shead)) return -1;
   } else if (gemm_bf16_tc(e->h, e->head, e->logits, T, CBX_SPEECH_VOCAB, 1024, CBX_LOGITS_LD, 0, s, e->shead)) return -1;

@@ -17,10 +17,11 @@ def shard_indices(est_len: list[int], world: int, rank: int) -> list[int]:
 
 
 def gather_token_streams(local: list[list[int]], local_idx: list[int], n_total: int,
-                         device: torch.device | str = "cpu") -> list[list[int]] | None:
+                         device: torch.device | str = "cpu", all_ranks: bool = False) -> list[list[int]] | None:
     """All ranks call this with their own streams (`local[j]` belongs to global prompt
-    `local_idx[j]`); rank 0 gets the full list in global order, other ranks None.  One padded
-    all_gather of int32 [n_local_max, max_len + 2] per rank (≤ a few MB: latency-bound)."""
+    `local_idx[j]`); rank 0 (every rank with all_ranks=True) gets the full list in global order, the
+    others None.  One padded all_gather of int32 [n_local_max, max_len + 2] per rank (≤ a few MB:
+    latency-bound)."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     if world == 1:
         out: list = [None] * n_total
@@ -39,7 +40,7 @@ def gather_token_streams(local: list[list[int]], local_idx: list[int], n_total: 
             buf[j, 2:2 + len(t)] = torch.tensor(t, dtype=torch.int32, device=device)
     allb = [torch.empty_like(buf) for _ in range(world)]
     dist.all_gather(allb, buf)
-    if dist.get_rank() != 0:
+    if dist.get_rank() != 0 and not all_ranks:
         return None
     out = [None] * n_total
     for b in allb:
@@ -49,3 +50,24 @@ def gather_token_streams(local: list[list[int]], local_idx: list[int], n_total: 
             if i >= 0:
                 out[i] = row[2:2 + n].tolist()
     return out
+
+
+def generate_sharded(engine, reqs: list, est_len: list[int] | None = None, all_ranks: bool = False,
+                     poll_every: int = 32) -> list[list[int]] | None:
+    """`engine.generate` for one process per GPU (torchrun): every rank is given the SAME request list, runs its
+    share — longest-first round-robin on `est_len` (default: prefix + max_tokens) — on its own engine, and the token
+    streams are gathered over the default process group (NCCL on GPUs).  Requests without a uid get their global
+    index + 1, so the Philox streams do not depend on the number of ranks.  With no process group (or one rank) this
+    is engine.generate.  Returns the streams in request order on rank 0 (on every rank with all_ranks=True)."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    for i, r in enumerate(reqs):
+        if r.uid == 0:
+            r.uid = i + 1
+    if world == 1:
+        return engine.generate(reqs, poll_every)
+    if est_len is None:
+        est_len = [34 + len(r.text_ids) + 1 + r.params.max_tokens for r in reqs]
+    idx = shard_indices(est_len, world, dist.get_rank())
+    local = engine.generate([reqs[i] for i in idx], poll_every) if idx else []
+    dev = engine.device if dist.get_backend() == "nccl" else "cpu"
+    return gather_token_streams(local, idx, len(reqs), device=dev, all_ranks=all_ranks)

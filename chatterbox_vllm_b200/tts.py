@@ -319,6 +319,17 @@ class ChatterboxTTS:
         crop = int(os.environ.get("CHATTERBOX_TAIL_CROP_TOKENS", "2"))
         t0 = time.time()
         with torch.inference_mode():
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                # one process per GPU (torchrun): every rank holds the same prompts, runs its share on its own engine,
+                # and all ranks get every stream back (sharding.py); the vocoder hand-off then runs on the host lists
+                from .sharding import generate_sharded
+                outs = generate_sharded(self.t3, reqs, all_ranks=True)
+                if not raw:
+                    outs = [postprocess_tokens(o, crop)[:guard_cap_tokens(w)] for o, w in zip(outs, wrapped)]
+                self.last_t3_seconds = time.time() - t0
+                print(f"[T3] Speech Token Generation time: {self.last_t3_seconds:.2f}s")
+                return outs
             if raw or not hasattr(self.t3, "generate_device"):
                 outs = self.t3.generate(reqs)
             else:

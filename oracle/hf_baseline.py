@@ -52,7 +52,8 @@ def _sample(logits, seen, temperature, top_p, min_p, rep):
 @torch.no_grad()
 def run(pairs: int, prefix_len: int, n_steps: int, *, n_layers: int = 30, dtype=torch.float32,
         cfg_scale: float = 0.5, temperature: float = 0.5, top_p: float = 0.5, min_p: float = 0.0,
-        rep: float = 2.0, speech_pos: bool = False, threads: int | None = None, model=None, warmup: int = 0):
+        rep: float = 2.0, speech_pos: bool = False, threads: int | None = None, model=None, warmup: int = 0,
+        device=None):
     """Prefill `pairs` CFG pairs with random prefix embeddings of `prefix_len` rows, then time
     `n_steps` decode steps.  Returns dict(prefill_s, decode_s, steps, tokens, cores)."""
     threads = threads or os.cpu_count() or 1
@@ -60,24 +61,31 @@ def run(pairs: int, prefix_len: int, n_steps: int, *, n_layers: int = 30, dtype=
     m, emb, head, pos = model or build_model(n_layers, dtype)
     g = torch.Generator().manual_seed(1)
     x = (torch.randn(pairs, prefix_len, 1024, generator=g) * 0.02).to(dtype)
+    cuda = device is not None and torch.device(device).type == "cuda"   # bench.py's gpu_standin leg: same loop on the GPU
+    sync = torch.cuda.synchronize if cuda else (lambda: None)
+    if cuda:
+        x = x.to(device)
     xu = x.clone()
     xu[:, 34:-1] = 0                                         # uncond: text rows zeroed (t3.py:564)
     t0 = time.perf_counter()
     out = m(inputs_embeds=torch.cat((x, xu), 0), use_cache=True)
     past = out.past_key_values
     h = out.last_hidden_state[:, -1]
+    sync()
     t_prefill = time.perf_counter() - t0
-    seen = torch.zeros(pairs, 8194, dtype=torch.bool)
+    seen = torch.zeros(pairs, 8194, dtype=torch.bool, device=x.device)
     t_dec = 0.0
     for s in range(warmup + n_steps):
+        sync()
         t0 = time.perf_counter()
         lg = h @ head.T
         l = lg[:pairs] + cfg_scale * (lg[:pairs] - lg[pairs:])
         tok = _sample(l, seen, temperature, top_p, min_p, rep)
-        seen[torch.arange(pairs), tok] = True
+        seen[torch.arange(pairs, device=x.device), tok] = True
         e = emb[tok] + (pos[s + 1] if speech_pos else 0)
         out = m(inputs_embeds=torch.cat((e, e), 0)[:, None], past_key_values=past, use_cache=True)
         past, h = out.past_key_values, out.last_hidden_state[:, -1]
         if s >= warmup:
+            sync()
             t_dec += time.perf_counter() - t0
     return dict(prefill_s=t_prefill, decode_s=t_dec, steps=n_steps, tokens=pairs * n_steps, cores=threads)

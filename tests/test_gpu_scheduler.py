@@ -189,3 +189,40 @@ def test_cfg_scale_from_the_environment(weights, cfg, monkeypatch):
     one = eng.generate(reqs[:1])                                     # the GEMV path (T = 2 rows) merges with the same scale
     assert_stream_parity(one, weights, reqs[:1], float(cfg), n_steps, temperature=0.0, repetition_penalty=2.0)
     eng.close()
+
+
+@pytest.mark.parametrize("n_layers,seeds", [(4, range(8)), (30, range(2))], ids=["4layers", "30layers"])
+def test_free_running_greedy_stream_is_the_oracles_until_a_near_tie(n_layers, seeds):
+    """north_star: "identical greedy-decoded token sequences over the first N steps".  No unconditional N > 0 exists for
+    two correct bf16 implementations: tools/greedy_horizon.py (profiles/r02_greedy_horizon.json) finds seeds whose very
+    first step is a near-tie of the oracle's own logits.  What does hold, and is asserted here on FREE-RUNNING streams:
+    the engine emits exactly the oracle's tokens up to the first step at which the oracle's top two penalised logits lie
+    within 8 bf16 ulps of each other — i.e. N = the position of the first near-tie (measured: 0 .. 48+ steps)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from chatterbox_vllm_b200.engine import Request, SamplingParams, T3Engine
+    from oracle import sampler_ref
+    from oracle.t3_ref import T3Oracle
+    n_steps = 24
+    for seed in seeds:
+        w = T3Weights.random(T3ModelConfig(n_layers=n_layers), seed=seed, head_scale=16.0, norm_jitter=0.1)
+        eng = T3Engine(w.state_dict(), device="cuda:0", max_pairs=1, max_model_len=256)
+        g = torch.Generator().manual_seed(1000 + seed)
+        text = [255] + torch.randint(3, 600, (10 + seed % 30,), generator=g).tolist() + [0]
+        cond = torch.randn(34, 1024, generator=g) * 0.02
+        sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=n_steps, ignore_eos=True)
+        got = eng.generate([Request(text, cond, sp, uid=7)])[0]
+        eng.close()
+        o = T3Oracle(w, "bf16")
+        pair, seen = o.new_pair(), np.zeros(8194, bool)
+        lg = o.prefill_pair(pair, cond, text, 0.5).numpy()
+        for s in range(n_steps):
+            l = sampler_ref.apply_repetition_penalty(lg, seen, 2.0)
+            t = int(np.argmax(l))
+            if t + 1000 != got[s]:
+                gap = (l[t] - l[got[s] - 1000]) / (2.0 ** -7 * abs(l[t]))
+                assert gap <= 8.0, f"seed {seed}: streams differ at step {s} although the oracle's margin is {gap:.1f} ulps"
+                break
+            seen[t] = True
+            if s + 1 < n_steps:
+                lg = o.decode_pairs([pair], [t], 0.5)[0].numpy()
