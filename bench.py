@@ -199,6 +199,73 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_cfg3(args, rank, world, local):
+    """BASELINE config 3 through the PRODUCT's multi-GPU path (sharding.generate_sharded): 400 prompts whose text lengths
+    are drawn (seed 3, with replacement) from the reference chunker's 154 chunks of docs/benchmark-text-1.txt
+    (tests/golden/prompt_lengths.json: min 17, mean 152, max 484 text tokens), 390 speech tokens each (the README-derived
+    mean, ignore_eos), 256 pair slots per GPU, STRONG scaling: the same 400 prompts are split over the ranks
+    (longest-first round-robin), streams gathered to rank 0 over NCCL.  value = 400 x 390 tokens / wall time of the
+    whole job (prefill, admission, decode, gather), max over ranks."""
+    import random
+    import torch
+    import torch.distributed as dist
+    from chatterbox_vllm_b200.engine import Request, SamplingParams, T3Engine
+    from chatterbox_vllm_b200.sharding import generate_sharded
+    from chatterbox_vllm_b200.synthetic import random_cond_emb, random_prompt, random_state_dict
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
+    lens = json.load(open(os.path.join(ROOT, "tests", "golden", "prompt_lengths.json")))["n_text"]
+    rng = random.Random(3)
+    n_prompts, gen = 400, 390
+    n_text = [rng.choice(lens) for _ in range(n_prompts)]
+    eng = T3Engine(random_state_dict(30, device=dev, seed=0), device=dev, max_pairs=256, max_model_len=1000, max_rows=16384,
+                   base_seed=1234)
+    sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=gen, ignore_eos=True)
+    mk = lambda: [Request(random_prompt(n, seed=i), random_cond_emb(i, pinned=True), sp, uid=1 + i)   # noqa: E731
+                  for i, n in enumerate(n_text)]
+    warm = mk()[:2 * world]
+    for r in warm:
+        r.params = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=40, ignore_eos=True)
+    generate_sharded(eng, warm)                                   # warm-up: graphs, tensor maps, NCCL
+    times = []
+    for _ in range(max(1, min(args.steps or 2, 3))):
+        reqs = mk()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        out = generate_sharded(eng, reqs)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        times.append(float(dt.item()))
+        if rank == 0:
+            assert len(out) == n_prompts and all(len(t) == gen for t in out), "cfg3: wrong token counts"
+    if rank == 0:
+        best = min(times)
+        print(json.dumps({"metric": "t3_speech_tokens_per_sec_cfg3_400_prompts", "value": n_prompts * gen / best,
+                          "unit": "speech_tokens/s", "n_gpus": world, "scaling": "strong", "seconds": best, "runs": times,
+                          "higher_is_better": True, "dtype": "bf16", "data": "synthetic", "preemptions": eng.preemptions,
+                          "config": {"workload": f"cfg3: {n_prompts} prompts (benchmark-text-1 chunk lengths, mean text "
+                                                 f"{sum(n_text) / n_prompts:.0f} tokens) x {gen} speech tokens, 256 pair slots "
+                                                 f"per GPU, split over {world} rank(s) by sharding.generate_sharded; prefill, "
+                                                 "admission, decode and the NCCL gather inside the timed region"}}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -214,6 +281,9 @@ def main():
     ap.add_argument("--no-fp8", action="store_true", help="skip the separately reported FP8-e4m3 weight leg")
     ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8_e4m3"],
                     help="profiling aid: run the WHOLE bench on FP8 weights (the line then says so; the default line is bf16)")
+    ap.add_argument("--config", default="m1", choices=["m1", "cfg3"],
+                    help="m1 (default): the BASELINE metric's workload, weak scaling; cfg3: 400 benchmark-text prompts, strong "
+                         "scaling through the product's sharded generate (its own JSON line, not the driver's metric)")
     ap.add_argument("--ctx0", type=int, default=None,
                     help="profiling aid: context length at the first timed step (default: centred on the workload mean)")
     args = ap.parse_args()
@@ -222,6 +292,9 @@ def main():
     if args.impl == "reference":
         args.steps, args.warmup = args.steps or 4, 1 if args.warmup is None else args.warmup
         return run_reference(args, rank, world)
+    if args.config == "cfg3":
+        refuse_knobs()
+        return run_cfg3(args, rank, world, local)
     args.steps = args.steps or 480
     args.warmup = max(3, 20 if args.warmup is None else args.warmup)
     knobs = refuse_knobs()
