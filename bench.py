@@ -553,7 +553,9 @@ def main():
             "roofline": {"kernel": "paged_attn_decode_bal_kernel", "bound": "hbm",
                          "achieved": attn_bytes / (attn_ms / 1e3) / 1e9, "peak": hbm, "unit": "GB/s",
                          "frac": attn_bytes / (attn_ms / 1e3) / 1e9 / hbm, "traffic": traffic, "peak_source": which,
-                         "us_per_launch": attn_ms * 1e3, "algorithmic_bytes_per_launch": attn_bytes},
+                         "us_per_launch": attn_ms * 1e3, "algorithmic_bytes_per_launch": attn_bytes, "context": mean_ctx,
+                         "traffic_source": "profiles/attn_traffic.json: dram__bytes of one ncu --set full capture of this "
+                                           "kernel, scaled by algorithmic bytes to this launch"},
             "step_roofline": {"bytes_per_step": step_bytes, "achieved_gbs": step_bytes / (ms / K / 1e3) / 1e9,
                               "frac": step_bytes / (ms / K / 1e3) / 1e9 / hbm}}
     # prefill: 2·ΣP rows through 30 layers (2·503 378 944 FLOP per row + causal attention) + one head row per sequence

@@ -41,6 +41,7 @@ class EngineCfg(C.Structure):
 _PROTOS = {
     "cbx_last_error": (C.c_char_p, []),
     "cbx_abi_version": (C.c_int, []),
+    "cbx_has_experiments": (C.c_int, []),
     "cbx_slot_mapping": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, vp]),
     "cbx_pool_create": (vp, [C.c_int]),
     "cbx_pool_destroy": (None, [vp]),

@@ -55,10 +55,25 @@ struct MegaArgs {
   const int32_t* bt; uint8_t* kv_cache; size_t layer_bytes;
   int bt_stride, T, n_layers, vocab, ldl; float eps; int flags;
 };
+#ifdef CBX_EXPERIMENTS   // `make EXPERIMENTS=1` links k_mega.cu (the persistent b = 1 step kernel: parity-green, slower)
 size_t mega_ws_bytes();
 int init_mega();
 int launch_decode_mega(const MegaArgs&, cudaStream_t);
+#else
+inline size_t mega_ws_bytes() { return 1024; }
+inline int init_mega() { return 0; }
+inline int launch_decode_mega(const MegaArgs&, cudaStream_t) { return 1; }      // "not applicable": the kernel chain runs
+#endif
 }  // namespace cbx
+
+// 1 when the library was built with the measured-slower experiment kernels (CBX_MEGA / CBX_GEMV_STREAM act only then)
+extern "C" int cbx_has_experiments(void) {
+#ifdef CBX_EXPERIMENTS
+  return 1;
+#else
+  return 0;
+#endif
+}
 using namespace cbx;
 
 namespace {
@@ -159,7 +174,9 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   cudaMemset(e->mega_sync, 0, 256);
   cudaMemset(e->block_acc, 0, 4 * 1024 * 8);
   cudaMemset(e->mega_ws, 0, mega_ws_bytes());
+#ifdef CBX_EXPERIMENTS
   if (const char* v = getenv("CBX_MEGA")) e->mega = v[0] != '0';
+#endif
   if (const char* v = getenv("CBX_SKIP")) e->skip = atoi(v);
   if (const char* v = getenv("CBX_L2_PREFETCH")) e->l2_prefetch = v[0] != '0';
   if (const char* v = getenv("CBX_SPLIT_MAX_ROWS")) { e->split_max_rows = atoi(v); if (e->split_max_rows > 512) e->split_max_rows = 512; }

@@ -443,6 +443,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
   }
 }
 
+#ifdef CBX_EXPERIMENTS   // `make EXPERIMENTS=1`: measured-slower variants kept for their write-ups, not shipped
 // ---- stream-ahead form (experiment, off by default: see stream_mode()) ------------------------------
 // The register form above holds a CTA's weights in ~100 registers x 384-512 threads, so two consecutive
 // kernels of the PDL chain never share an SM: kernel n+1 starts its weight loads only when kernel n's
@@ -610,6 +611,8 @@ int launch_stream(const GemvArgs& a, cudaStream_t s) {
   return 0;
 }
 
+#endif  // CBX_EXPERIMENTS
+
 template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
 int launch_w(const GemvArgs& a, int grid, cudaStream_t s) {
   constexpr int smem = TT * KSEG * 1024 * 2 + (KSEG > 1 ? NW * 2 * TT * 4 : 0);
@@ -622,11 +625,13 @@ int launch_w(const GemvArgs& a, int grid, cudaStream_t s) {
 
 template <int TT, int KSEG, int PRO, int EPI, int NW>
 int launch(const GemvArgs& a, int grid, cudaStream_t s) {
+#ifdef CBX_EXPERIMENTS
   if (stream_mode()) {
     // stream-ahead form: 8 warps (4 for the two N = 1024 projections, whose CTAs own 4 items)
     constexpr int SW = (EPI == EPI_RES) ? 4 : 8;
     return a.wscale ? launch_stream<TT, KSEG, PRO, EPI, SW, true>(a, s) : launch_stream<TT, KSEG, PRO, EPI, SW, false>(a, s);
   }
+#endif
   return a.wscale ? launch_w<TT, KSEG, PRO, EPI, NW, true>(a, grid, s) : launch_w<TT, KSEG, PRO, EPI, NW, false>(a, grid, s);
 }
 

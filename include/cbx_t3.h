@@ -40,6 +40,10 @@ extern "C" {
 
 const char* cbx_last_error(void);
 int cbx_abi_version(void);
+/* 1 when the library carries the experiment kernels (`make EXPERIMENTS=1`: the persistent b = 1 step kernel selected by
+ * CBX_MEGA=1, the stream-ahead GEMV selected by CBX_GEMV_STREAM=1 — both parity-green and measured slower);
+ * the default build returns 0 and ignores those switches.  No counterpart in the reference. */
+int cbx_has_experiments(void);
 
 /* ---- integer bookkeeping (bit-exact) ------------------------------------------ */
 

@@ -25,19 +25,22 @@ for f in sorted(os.listdir(go)):
                 for i in idx:
                     o.write(f"{hdr[i]:70s} {r[i][:90]} {units[i]}\n")
                 o.write("\n")
-        if name == "paged_attn_decode":
+        if name.startswith("paged_attn_decode"):
             ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
             vals = [float(r[ir]) * SCALE.get(units[ir], 1) + float(r[iw]) * SCALE.get(units[iw], 1) for r in rows[2:]]
             meta = {}
             try:
-                meta = json.loads([l for l in open(os.path.join(go, "plain.log")) if l.startswith("{")][-1])["roofline"]
+                meta = json.loads([l for l in open(os.path.join(go, f"plain_{name}.log") if os.path.exists(os.path.join(go, f"plain_{name}.log")) else os.path.join(go, "plain.log")) if l.startswith("{")][-1])["roofline"]
             except Exception:
                 pass
             json.dump({"dram_bytes_per_launch": sum(vals) / len(vals),
                        "algorithmic_bytes_same_launch": meta.get("algorithmic_bytes_per_launch"),
-                       "source": f"profiles/{tag}_ncu_full_paged_attn_decode.txt"},
+                       "us_per_launch": sum(float(r[hdr.index("gpu__time_duration.sum")]) for r in rows[2:]) / len(rows[2:]) /
+                                        (1e3 if units[hdr.index("gpu__time_duration.sum")].startswith("ns") else 1),
+                       "context": meta.get("context"), "source": f"profiles/{tag}_ncu_full_{name}.txt"},
                       open(os.path.join(pr, "attn_traffic.json"), "w"))
 for f, out in (("launches.csv", f"{tag}_launches_B128.txt"), ("launches_B1.csv", f"{tag}_launches_B1.txt"),
+               ("launches_B1_chain.csv", f"{tag}_launches_B1_five_kernel_chain.txt"),
                ("launches_fp8.csv", f"{tag}_launches_B128_fp8w.txt")):
     p = os.path.join(go, f)
     if os.path.exists(p):
