@@ -284,6 +284,7 @@ def main():
     ap.add_argument("--config", default="m1", choices=["m1", "cfg3"],
                     help="m1 (default): the BASELINE metric's workload, weak scaling; cfg3: 400 benchmark-text prompts, strong "
                          "scaling through the product's sharded generate (its own JSON line, not the driver's metric)")
+    ap.add_argument("--max-rows", type=int, default=16384, help="row capacity of the engine's step buffers (prefill chunk size)")
     ap.add_argument("--ctx0", type=int, default=None,
                     help="profiling aid: context length at the first timed step (default: centred on the workload mean)")
     args = ap.parse_args()
@@ -331,7 +332,7 @@ def main():
     n_layers = int(os.environ.get("CBX_BENCH_LAYERS", "30"))    # tuning aid only: the bench line is for 30
     sd = random_state_dict(n_layers, device=dev, seed=0)
     eng = T3Engine(sd, device=dev, max_pairs=B, max_model_len=max(max_len, PREFIX + GEN + 8),
-                   max_rows=16384, base_seed=1234 + rank, weight_dtype=args.weights)
+                   max_rows=args.max_rows, base_seed=1234 + rank, weight_dtype=args.weights)
     w_bytes = W_BYTES if args.weights == "bf16" else eng.projection_weight_bytes()
     sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=max_tokens, ignore_eos=True)
     # global prompt index keeps the Philox streams independent of how requests are sharded
