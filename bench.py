@@ -89,7 +89,7 @@ def cpu_baseline_sample(pairs=8, prefix=450, steps=4, warmup=1, model=None):
             "ms_per_step": 1e3 * r["decode_s"] / steps}
 
 
-KNOBS = ("CBX_SKIP", "CBX_MEGA", "CBX_GEMV_STREAM", "CBX_BLOCK_STOP", "CBX_BLOCK_NOACC", "CBX_BLOCK_FUSED", "CBX_PDL",
+KNOBS = ("CBX_SKIP", "CBX_MEGA", "CBX_GEMV_STREAM", "CBX_BLOCK_STOP", "CBX_BLOCK_NOACC", "CBX_BLOCK_FUSED", "CBX_MLP_FUSED", "CBX_DUAL_MIN_ROWS", "CBX_DUAL_ATTN_CTAS", "CBX_DUAL_CHAIN", "CBX_PDL",
          "CBX_ATTN_BALANCED", "CBX_ATTN_SMALL", "CBX_O_UNSPLIT", "CBX_SPLIT_MAX_ROWS", "CBX_L2_PREFETCH", "CBX_GEMM_MC",
          "CBX_ATTN_PLAN_EACH", "CBX_PREFILL_ROWWISE", "CBX_BENCH_LAYERS", "CBX_GEMV_MAX_T")
 
@@ -285,6 +285,9 @@ def main():
                     help="m1 (default): the BASELINE metric's workload, weak scaling; cfg3: 400 benchmark-text prompts, strong "
                          "scaling through the product's sharded generate (its own JSON line, not the driver's metric)")
     ap.add_argument("--max-rows", type=int, default=16384, help="row capacity of the engine's step buffers (prefill chunk size)")
+    ap.add_argument("--prefix", type=int, default=None,
+                    help="profiling aid: prompt rows per sequence (default 200, the M1 workload); with --ctx0 it puts the first "
+                         "timed step at that context after the warm-up steps alone, so a profiler has few launches to skip")
     ap.add_argument("--ctx0", type=int, default=None,
                     help="profiling aid: context length at the first timed step (default: centred on the workload mean)")
     args = ap.parse_args()
@@ -299,6 +302,10 @@ def main():
     args.steps = args.steps or 480
     args.warmup = max(3, 20 if args.warmup is None else args.warmup)
     knobs = refuse_knobs()
+    if args.prefix is not None:
+        global PREFIX
+        PREFIX = args.prefix
+        knobs = knobs + [f"--prefix {args.prefix}"]        # not the M1 workload: the line is marked as a tuning run
 
     import torch
     import torch.distributed as dist

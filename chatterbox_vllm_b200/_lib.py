@@ -73,6 +73,9 @@ _PROTOS = {
     "cbx_engine_set_prefill_items": (C.c_int, [vp, vp, C.c_int]),
     "cbx_layer_qkv": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
     "cbx_linear_residual": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, vp]),
+    "cbx_layer_mlp_block": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]),
+    "cbx_layer_mlp_block_scratch_bytes": (C.c_int64, []),
+    "cbx_engine_set_down_t": (C.c_int, [vp, vp, C.c_int]),
     "cbx_layer_attn_block_scratch_bytes": (C.c_int64, []),
     "cbx_layer_attn_block_supported": (C.c_int, [C.c_int, C.c_int]),
     "cbx_layer_attn_block": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]),

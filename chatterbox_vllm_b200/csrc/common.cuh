@@ -20,6 +20,11 @@ int  count_launch();                       // ++ global launch counter; returns 
 // SMs of the current device (queried once), capped at kMaxSms: the persistent kernels launch one CTA per SM and the
 // attention page-range plan is laid out for at most kMaxSms ranges (B200: 148)
 constexpr int kMaxSms = 148;
+// Copies of the fused MLP block's down-proj accumulator (k_mlp.cu: CTA b adds into copy b % kMlpAccCopies; k_block.cu's
+// FOLD prologue and acc_finalize add the copies).  L2 serialises reductions per address: with one copy the 148 CTAs' bulk
+// reductions cost ~0.5 us per launch at b = 1 (measured with unread copies: step 0.512 -> 0.498 ms) — but READING four
+// copies in the next kernel's prologue (70 KB per CTA through one SM's L2 port) costs more than that: 0.542 ms.  So: 1.
+constexpr int kMlpAccCopies = 1;
 int  sm_count();
 #define CBX_CHECK_LAUNCH(name)                                                   \
   do {                                                                           \

@@ -29,9 +29,9 @@ int gemv_norm_gate_up(const void*, const void*, const void*, void*, int, float, 
                       size_t next_bytes = 0, const float* wscale = nullptr, const void* acc = nullptr, void* res_out = nullptr);
 void attn_set_prefetch(const void*, size_t);
 int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
-              const int32_t* row_seq);
+              const int32_t* row_seq, int n_ctas = 0);
 int paged_attn_decode_ex(const void*, const void*, const int32_t*, int, const int32_t*, const int32_t*, void*, void*, int32_t*,
-                         int, int, bool, void*);
+                         int, int, bool, void*, int n_ctas = 0);
 int gemv_norm_head(const void*, const void*, const void*, void*, int, int, int, float, cudaStream_t, const float* wscale = nullptr);
 int gemm_bf16_tc(const void*, const void*, void*, int, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
 int gemm_qkv_rope(const void*, const void*, void*, const void*, const int32_t*, const int64_t*, void*, int, cudaStream_t,
@@ -46,6 +46,13 @@ bool layer_attn_block_supported(int T, int max_kv_len);
 int layer_attn_block(const void* res, const void* ln_w, const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos,
                      const int64_t* slot, void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq,
                      const int32_t* kv_len, void* acc, void* q_out, int T, float eps, cudaStream_t s);
+bool layer_mlp_block_on();
+int layer_attn_block_fold(const void* res, const void* acc_in, void* res_wb, void* zero_ptr, int zero_bytes, const void* ln_w,
+                          const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos, const int64_t* slot,
+                          void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
+                          void* acc, int T, float eps, cudaStream_t s);
+int layer_mlp_block(const void* x, const void* acc_in, void* res_wb, const void* ln_w, const void* Wgu, const void* WdT,
+                    void* acc_out, void* zero_ptr, int zero_bytes, int T, float eps, cudaStream_t s);
 struct MegaArgs {
   const bf16* ln1[32]; const bf16* wqkv[32]; const bf16* wo[32];
   const bf16* ln2[32]; const bf16* wgu[32]; const bf16* wd[32];
@@ -85,12 +92,15 @@ __global__ void __launch_bounds__(128) gather_rows_kernel(const uint4* src,
   dst[(size_t)blockIdx.x * 128 + threadIdx.x] = src[(size_t)rows[blockIdx.x] * 128 + threadIdx.x];
 }
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr int kAccBytes = 4 * 1024 * 8;                // one fixed-point accumulator: [4][1024] u64
+constexpr int kAccSlots = 2 + 2 * kMlpAccCopies;       // O-proj: even / odd layers; down-proj: even / odd layers x copies
 }  // namespace
 
 struct cbx_engine {
   cbx_engine_cfg cfg;
   cbx_weights w;
   std::vector<const void*> wqkv, wo, wgu, wd, ln1, ln2;
+  std::vector<const void*> wd_t;   // transposed bf16 down-proj weights [4096,1024] per layer (cbx_engine_set_down_t), or empty
   // FP8-e4m3 weight path (cbx_engine_set_fp8_weights): the four projections above and the head then point at
   // e4m3 bytes and these hold their per-output-feature scales; NULL entries = bf16 weights
   std::vector<const float*> sqkv, so, sgu, sd;
@@ -103,9 +113,16 @@ struct cbx_engine {
   // workspace carve-up
   bf16 *res, *h, *qkv, *attn, *act, *hs, *logits;
   int32_t *pos, *kv_len, *row_seq, *head_rows, *attn_counters;
-  unsigned long long* block_acc;   // [4][1024] fixed-point O-proj accumulator of the fused attention block (zero between layers)
+  // 64-bit fixed-point accumulators of the fused T <= 4 kernels, [4][1024] each, all zero between steps: slots 0, 1 the
+  // O-proj output of even / odd layers (k_block.cu), then the down-proj output of even / odd layers (k_mlp.cu; each in
+  // kMlpAccCopies copies, common.cuh)
+  unsigned long long* block_acc;
   int64_t* slot;
   void* attn_scratch;
+  void* attn_scratch2;         // second plan + partial slots: the uncond half of a two-stream step (forward_dual)
+  cudaStream_t s2 = nullptr;   // its stream, and the fork / join events
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_att[2][32] = {};   // "attention of layer l done" per half: the two halves' attention launches alternate
   float* part;                 // split-K partials [4][split_max_rows][1024] fp32 
   unsigned* mega_sync;         // exit counter + epoch of the persistent decode kernel
   uint8_t* mega_ws;            // its tagged exchange buffers
@@ -139,9 +156,12 @@ static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
   p = take(R * 8); if (e) e->slot = (int64_t*)p;
   p = take(R * 4); if (e) e->attn_counters = (int32_t*)p;
   p = take((R + 1024) * (CBX_HIDDEN * 4 + CBX_HEADS * 8) + 256); if (e) e->attn_scratch = p;
+#ifdef CBX_EXPERIMENTS
+  p = take((size_t)4 << 20); if (e) e->attn_scratch2 = p;       // >= the balanced kernel's scratch (1.3 MB)
+#endif
   p = take((size_t)4 * 512 * 1024 * 4); if (e) e->part = (float*)p;
   p = take(256); if (e) e->mega_sync = (unsigned*)p;
-  p = take(4 * 1024 * 8); if (e) e->block_acc = (unsigned long long*)p;
+  p = take(kAccBytes * kAccSlots); if (e) e->block_acc = (unsigned long long*)p;
   p = take(mega_ws_bytes()); if (e) e->mega_ws = (uint8_t*)p;
   return off;
 }
@@ -172,7 +192,19 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   // split-K attention tickets start at zero and reset themselves
   cudaMemset(e->attn_counters, 0, (size_t)cfg->max_rows * 4);
   cudaMemset(e->mega_sync, 0, 256);
-  cudaMemset(e->block_acc, 0, 4 * 1024 * 8);
+  cudaMemset(e->block_acc, 0, kAccBytes * kAccSlots);
+#ifdef CBX_EXPERIMENTS
+  // second stream of the two-stream decode step (forward_dual); without it the step runs on one stream
+  if (cudaStreamCreateWithFlags(&e->s2, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    cudaGetLastError();
+    e->s2 = nullptr;
+  }
+  for (int hf = 0; hf < 2 && e->s2; ++hf)
+    for (int i = 0; i < 32; ++i)
+      if (cudaEventCreateWithFlags(&e->ev_att[hf][i], cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); e->s2 = nullptr; break; }
+#endif
   cudaMemset(e->mega_ws, 0, mega_ws_bytes());
 #ifdef CBX_EXPERIMENTS
   if (const char* v = getenv("CBX_MEGA")) e->mega = v[0] != '0';
@@ -186,6 +218,10 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
 extern "C" void cbx_engine_destroy(cbx_engine* e) {
   if (!e) return;
   for (auto& g : e->graphs) cudaGraphExecDestroy(g.second.first);
+  if (e->s2) cudaStreamDestroy(e->s2);
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
+  for (auto& hf : e->ev_att) for (cudaEvent_t ev : hf) if (ev) cudaEventDestroy(ev);
   delete e;
 }
 
@@ -193,7 +229,7 @@ extern "C" void* cbx_engine_buffer(cbx_engine* e, const char* name) {
   struct { const char* n; void* p; } tab[] = {
       {"x", e->res}, {"res", e->res}, {"h", e->h}, {"qkv", e->qkv}, {"attn", e->attn}, {"act", e->act},
       {"hs", e->hs}, {"logits", e->logits}, {"pos", e->pos}, {"slot", e->slot}, {"kv_len", e->kv_len},
-      {"row_seq", e->row_seq}, {"head_rows", e->head_rows}};
+      {"row_seq", e->row_seq}, {"head_rows", e->head_rows}, {"block_acc", e->block_acc}};
   for (auto& t : tab) if (!strcmp(t.n, name)) return t.p;
   return nullptr;
 }
@@ -282,6 +318,18 @@ extern "C" int cbx_head_logits_fp8w(const void* res, const void* norm_w, const v
   return head_logits(res, norm_w, Whead8, wscale, logits, h_scratch, T, eps, stream);
 }
 static void drop_graphs(cbx_engine* e);
+// Transposed bf16 down-proj weights (WdT[l] = Wd[l]^T, [4096,1024] row-major) for the fused MLP block of the T <= 4 path
+// (k_mlp.cu): a CTA that owns a slice of MLP features reads its rows of WdT contiguously.  Without them (or with
+// CBX_MLP_FUSED=0) the gate_up and down-proj kernels run.  NULL / 0 layers removes them again.
+extern "C" int cbx_engine_set_down_t(cbx_engine* e, const void* const* wd_t, int n_layers) {
+  CBX_REQUIRE(e != nullptr, "cbx_engine_set_down_t: NULL engine");
+  CBX_REQUIRE(wd_t == nullptr || n_layers == e->w.n_layers, "cbx_engine_set_down_t: %d layers, engine has %d", n_layers, e->w.n_layers);
+  if (wd_t)
+    for (int i = 0; i < n_layers; ++i) CBX_REQUIRE(wd_t[i] != nullptr, "cbx_engine_set_down_t: NULL pointer in layer %d", i);
+  if (wd_t) e->wd_t.assign(wd_t, wd_t + n_layers); else e->wd_t.clear();
+  drop_graphs(e);
+  return 0;
+}
 // Switch a created engine to FP8-e4m3 projection weights (cbx_quantize_fp8_rows output).  Embeddings, norms,
 // KV cache, activations and the sampler are unchanged (bf16 / fp32).  Graphs captured before the switch are dropped.
 extern "C" int cbx_engine_set_fp8_weights(cbx_engine* e, const cbx_fp8_weights* f) {
@@ -315,7 +363,129 @@ static int gemv_max_t() {
   return v < 0 ? 0 : (v > 4 ? 4 : v);
 }
 
+#ifdef CBX_EXPERIMENTS   // `make EXPERIMENTS=1` + env CBX_DUAL_MIN_ROWS=128: measured SLOWER (M1 3.46 -> 3.60-3.82 ms/step), see below
+// ---- two-stream decode step (tcgen05 regime) -----------------------------------------------------------------------
+// The cond rows [0, B) and the uncond rows [B, 2B) of a decode step do not meet before the sampler's CFG merge
+// (t3.py:732), and the step is two very different kinds of work: paged attention (HBM-bound: 67 % of the M1 step at
+// 95 % of the copy roofline) and a chain of six short GEMM / norm kernels per layer (latency-bound: 6 us each for
+// 0.7 us of tensor work, ~12 % of the SMs' warps active).  Run as ONE stream they alternate, and the HBM idles
+// through a third of the step.  Here each half runs its own layer loop on its own stream, and the attention launches
+// take `dual_attn_ctas` CTAs (one per SM: the kernel's page ring fills an SM's shared memory) instead of one per SM of
+// the whole GPU, so the other half's GEMM CTAs find free SMs while a half streams its KV pages.  The halves fall out of
+// phase only if forced to (forward_dual chains the attention launches by events).  Weights are read twice per step
+// (1 GB more, against 14 GB of KV at M1).  Same kernels, same per-row arithmetic (the parity tests pass on it).
+// MEASURED on B200, M1, ms per step: one stream 3.46; two streams unchained 3.68 (104 CTAs) / 3.50 (120) / 3.53 (148);
+// chained 3.82 (88 CTAs) / 3.73 (96) / 3.65 (112) / 3.63 (120) / 3.60 (132) / 3.69 (148).  The premise was wrong: the
+// attention kernel's throughput is per SM (41 GB/s each: the QK / PV arithmetic on the CUDA cores keeps pace with an
+// SM's 1/148 share of the HBM stream and no more), so it needs every SM to reach 95 % of the roofline and there are no
+// SMs to lend.  Default off (CBX_DUAL_MIN_ROWS=0).
+static int dual_attn_ctas() {
+  static const int v = getenv("CBX_DUAL_ATTN_CTAS") ? atoi(getenv("CBX_DUAL_ATTN_CTAS")) : 104;
+  return v;
+}
+static bool dual_on(const cbx_engine* e, int T) {
+  static const int min_rows = getenv("CBX_DUAL_MIN_ROWS") ? atoi(getenv("CBX_DUAL_MIN_ROWS")) : 0;   // 0 = off (default)
+  return e->s2 != nullptr && min_rows > 0 && T >= min_rows && T % 2 == 0 && T / 2 <= 512 && !e->trace && !e->skip && e->n_prefill_items == 0 &&
+         !e->fp8 && dual_attn_ctas() > 0;
+}
+// One half's rows and buffers.
+struct HalfCtx {
+  int off, H, splits;
+  cudaStream_t s;
+  void* scratch;
+  bf16 *res, *h, *qkv, *attn, *act;
+  float* part;
+  const int32_t *pos, *kv_len, *row_seq;
+  const int64_t* slot;
+  int32_t* counters;
+  bool have_plan, pending;
+};
+static HalfCtx half_ctx(cbx_engine* e, int off, int H, cudaStream_t s, void* scratch) {
+  HalfCtx c = {};
+  const int m_tiles = (H + 127) / 128;
+  c.off = off; c.H = H; c.s = s; c.scratch = scratch;
+  c.splits = H <= e->split_max_rows ? (m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1)) : 1;
+  c.res = e->res + (size_t)off * 1024; c.h = e->h + (size_t)off * 1024; c.qkv = e->qkv + (size_t)off * 3072;
+  c.attn = e->attn + (size_t)off * 1024; c.act = e->act + (size_t)off * 4096;
+  c.part = e->part + (off ? (size_t)4 * 256 * 1024 : 0);             // [splits][H][1024] per half: 4 x 256 or 2 x 512 rows
+  c.pos = e->pos + off; c.kv_len = e->kv_len + off; c.row_seq = e->row_seq + off; c.slot = e->slot + off;
+  c.counters = e->attn_counters + off;
+  return c;
+}
+// [add+norm] [QKV+RoPE+append] of layer li: everything of the layer in front of its attention
+static int half_pre(cbx_engine* e, HalfCtx& c, int li, uint8_t* kv) {
+  const float eps = e->w.rms_eps;
+  if (c.pending ? cbx_rmsnorm_reduce(c.part, c.splits, c.res, e->ln1[li], c.h, c.H, eps, c.s)
+                : cbx_rmsnorm(c.res, nullptr, e->ln1[li], c.h, c.H, eps, c.s)) return -1;
+  c.pending = false;
+  return gemm_qkv_rope(c.h, e->wqkv[li], c.qkv, e->w.cos_sin, c.pos, c.slot, kv, c.H, c.s, nullptr);
+}
+static int half_attn(cbx_engine* e, HalfCtx& c, uint8_t* kv, int max_kv_len) {
+  return paged_attn_decode_ex(c.qkv, kv, e->block_table, e->bt_stride, c.row_seq, c.kv_len, c.attn, c.scratch, c.counters, c.H,
+                              max_kv_len, c.have_plan, c.s, dual_attn_ctas());
+}
+// [O] [add+norm] [gate_up+SiLU] [down]: everything of the layer behind its attention
+static int half_post(cbx_engine* e, HalfCtx& c, int li) {
+  const float eps = e->w.rms_eps;
+  if (c.splits > 1) {
+    if (gemm_partials(c.attn, e->wo[li], c.part, c.H, 1024, 1024, c.splits, c.s, nullptr)) return -1;
+    if (cbx_rmsnorm_reduce(c.part, c.splits, c.res, e->ln2[li], c.h, c.H, eps, c.s)) return -1;
+    if (gemm_bf16_tc(c.h, e->wgu[li], c.act, c.H, 8192, 1024, 4096, 1, c.s, nullptr)) return -1;
+    if (gemm_partials(c.act, e->wd[li], c.part, c.H, 1024, 4096, c.splits, c.s, nullptr)) return -1;
+    c.pending = true;
+    return 0;
+  }
+  if (gemm_residual(c.attn, e->wo[li], c.res, c.H, 1024, 1024, c.s, nullptr)) return -1;
+  if (cbx_rmsnorm(c.res, nullptr, e->ln2[li], c.h, c.H, eps, c.s)) return -1;
+  if (gemm_bf16_tc(c.h, e->wgu[li], c.act, c.H, 8192, 1024, 4096, 1, c.s, nullptr)) return -1;
+  return gemm_residual(c.act, e->wd[li], c.res, c.H, 1024, 4096, c.s, nullptr);
+}
+// The two attention launches of a layer are chained by events — cond after the uncond of the layer before, uncond after
+// the cond of the same layer — so the HBM-bound kernels run back to back, never against each other, and each half's GEMM
+// chain falls into the other half's attention window.  (Left to themselves the halves stay in phase: both GEMM chains
+// run together, then both attention launches share the HBM, and nothing is gained — measured.)
+static int forward_dual(cbx_engine* e, int T, int max_kv_len, cudaStream_t s) {
+  const size_t layer_bytes = (size_t)e->cfg.num_blocks * CBX_PAGE_BYTES;
+  const int H = T / 2, L = e->w.n_layers;
+  static const bool chain = !(getenv("CBX_DUAL_CHAIN") && getenv("CBX_DUAL_CHAIN")[0] == '0');
+  HalfCtx a = half_ctx(e, 0, H, s, e->attn_scratch), b = half_ctx(e, H, H, e->s2, e->attn_scratch2);
+  int rc = 0;
+  auto ok = [&](cudaError_t ce) { if (ce != cudaSuccess && rc == 0) { set_error("forward_dual: %s", cudaGetErrorString(ce)); rc = -1; } };
+  ok(cudaEventRecord(e->ev_fork, s));
+  ok(cudaStreamWaitEvent(e->s2, e->ev_fork, 0));
+  a.have_plan = attn_plan(a.kv_len, H, a.scratch, a.s, e->block_table, e->bt_stride, a.row_seq, dual_attn_ctas()) == 0;
+  b.have_plan = attn_plan(b.kv_len, H, b.scratch, b.s, e->block_table, e->bt_stride, b.row_seq, dual_attn_ctas()) == 0;
+  for (int li = 0; li < L && rc == 0; ++li) {
+    uint8_t* kv = e->kv_cache + (size_t)li * layer_bytes;
+    if (half_pre(e, a, li, kv)) rc = -1;
+    if (chain && li > 0) ok(cudaStreamWaitEvent(a.s, e->ev_att[1][li - 1], 0));
+    if (half_attn(e, a, kv, max_kv_len)) rc = -1;
+    if (chain) ok(cudaEventRecord(e->ev_att[0][li], a.s));
+    if (half_post(e, a, li)) rc = -1;
+    if (half_pre(e, b, li, kv)) rc = -1;
+    if (chain) ok(cudaStreamWaitEvent(b.s, e->ev_att[0][li], 0));
+    if (half_attn(e, b, kv, max_kv_len)) rc = -1;
+    if (chain) ok(cudaEventRecord(e->ev_att[1][li], b.s));
+    if (half_post(e, b, li)) rc = -1;
+  }
+  // final norm into h (the head GEMM / the sampler's row gather read it)
+  for (HalfCtx* c : {&a, &b}) {
+    if (rc) break;
+    if (c->pending ? cbx_rmsnorm_reduce(c->part, c->splits, c->res, e->w.norm, c->h, H, e->w.rms_eps, c->s)
+                   : cbx_rmsnorm(c->res, nullptr, e->w.norm, c->h, H, e->w.rms_eps, c->s)) rc = -1;
+  }
+  // always join: a capture must not end with the second stream still forked
+  const bool joined = cudaEventRecord(e->ev_join, e->s2) == cudaSuccess && cudaStreamWaitEvent(s, e->ev_join, 0) == cudaSuccess;
+  CBX_REQUIRE(joined, "forward_dual: join failed: %s", cudaGetErrorString(cudaGetLastError()));
+  return rc;
+}
+
+#endif  // CBX_EXPERIMENTS
+
 static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, bool final_norm) {
+#ifdef CBX_EXPERIMENTS
+  if (T > gemv_max_t() && dual_on(e, T)) return forward_dual(e, T, max_kv_len, s);
+#endif
   const size_t layer_bytes = (size_t)e->cfg.num_blocks * CBX_PAGE_BYTES;
   const float eps = e->w.rms_eps;
   const int sk = e->skip;
@@ -334,6 +504,30 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
     // T <= 4, bf16 weights, context within the fused block's page buffer: the attention half of the layer is ONE kernel
     // (k_block.cu): [norm+QKV+RoPE+append+attention+O+res] [norm+gate_up+SiLU] [down+res] = 3 launches per layer
     const bool fused = T <= G && !e->fp8 && !sk && !pf && e->n_prefill_items == 0 && layer_attn_block_supported(T, max_kv_len);
+    if (fused && !e->trace && !e->wd_t.empty() && layer_mlp_block_on()) {
+      // (env CBX_MLP_FUSED=1; measured equal to the three-launch layer below, which stays the default)
+      // TWO launches per layer: [attention block] [MLP block], each closing the OTHER one's residual branch in its norm
+      // prologue from a fixed-point accumulator.  Rows alternate between res (entering a layer) and h (between the two
+      // blocks): the kernel that closes a branch writes the rows to the buffer its sibling CTAs are not reading.
+      // Accumulators alternate with the layer's parity; each kernel clears, after its wait, the one that the NEXT
+      // kernel of its kind will add into (its last reader finished two launches ago).  The last layer ends with the
+      // gate_up / down kernels, which leave the residual closed in res and all four accumulators zero.
+      unsigned long long* a_o = e->block_acc + (size_t)(li & 1) * (kAccBytes / 8);
+      unsigned long long* a_d = e->block_acc + (size_t)(2 + (li & 1) * kMlpAccCopies) * (kAccBytes / 8);
+      const unsigned long long* a_d_prev = li > 0 ? e->block_acc + (size_t)(2 + ((li - 1) & 1) * kMlpAccCopies) * (kAccBytes / 8) : nullptr;
+      unsigned long long* a_o_next = e->block_acc + (size_t)((li + 1) & 1) * (kAccBytes / 8);
+      // (each kernel pulling the other one's weights into L2 behind its own stream was tried: 0.517 -> 0.533 ms at b = 1)
+      const bool last = li + 1 == e->w.n_layers;
+      if (layer_attn_block_fold(e->res, a_d_prev, e->h, a_d, kAccBytes * kMlpAccCopies, e->ln1[li], e->wqkv[li], e->wo[li], e->w.cos_sin, e->pos,
+                                e->slot, kv, e->block_table, e->bt_stride, e->row_seq, e->kv_len, a_o, T, eps, s)) return -1;
+      if (!last) {
+        if (layer_mlp_block(e->h, a_o, e->res, e->ln2[li], e->wgu[li], e->wd_t[li], a_d, a_o_next, kAccBytes, T, eps, s)) return -1;
+      } else {
+        if (gemv_norm_gate_up(e->h, e->ln2[li], e->wgu[li], e->act, T, eps, s, nullptr, 0, nullptr, a_o, e->res)) return -1;
+        if (gemv_residual(e->act, e->wd[li], e->res, T, 4096, s, nullptr, 0, nullptr, e->block_acc, kAccBytes * kAccSlots, nullptr)) return -1;
+      }
+      continue;
+    }
     if (fused) {
       // the block leaves the O-proj output in block_acc; gate_up's norm prologue closes the residual branch from it
       // (bf16(bf16(o) + res), written by its CTA 0 to buffer h — NOT in place: the other CTAs still read res); the
@@ -342,7 +536,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                            e->bt_stride, e->row_seq, e->kv_len, e->block_acc, nullptr, T, eps, s)) return -1;
       static const bool noacc = getenv("CBX_BLOCK_NOACC") != nullptr;   // profiling aid: gate_up ignores the accumulator (garbage)
       if (gemv_norm_gate_up(e->res, e->ln2[li], e->wgu[li], e->act, T, eps, s, nullptr, 0, e->sgu[li], noacc ? nullptr : e->block_acc, e->h)) return -1;
-      if (gemv_residual(e->act, e->wd[li], e->res, T, 4096, s, nullptr, 0, e->sd[li], e->block_acc, 4 * 1024 * 8, noacc ? nullptr : e->h)) return -1;
+      if (gemv_residual(e->act, e->wd[li], e->res, T, 4096, s, nullptr, 0, e->sd[li], e->block_acc, kAccBytes, noacc ? nullptr : e->h)) return -1;
       if (e->trace)
         cudaMemcpyAsync(e->trace + (size_t)li * T * CBX_HIDDEN, e->res, (size_t)T * CBX_HIDDEN * 2,
                         cudaMemcpyDeviceToDevice, s);
@@ -503,7 +697,13 @@ extern "C" int cbx_engine_decode(cbx_engine* e, int B, int n_steps, int max_kv_l
   if (!use_graph) {
     for (int i = 0; i < n_steps; ++i) if (decode_step(e, B, max_kv_len, s)) return -1;
   } else {
-    const int bucket = (max_kv_len + 63) / 64 * 64;
+    // What a captured step bakes in of max_kv_len: for T <= 4 whether the fused block's / the small attention kernel's
+    // page buffers hold the context (so: buckets of 64 tokens); for more rows only the unbalanced attention plan — the
+    // balanced kernel cuts its page ranges on the device from kv_len, so ONE graph serves every context length and a
+    // long generation does not re-capture every 64 steps.
+    static const bool balanced = !(getenv("CBX_ATTN_BALANCED") && getenv("CBX_ATTN_BALANCED")[0] == '0');
+    const bool any_len = balanced && 2 * B > 4 && 2 * B <= 4095;
+    const int bucket = any_len ? e->cfg.max_model_len : (max_kv_len + 63) / 64 * 64;
     auto key = std::make_pair(B, bucket);
     auto itr = e->graphs.find(key);
     if (itr == e->graphs.end()) {

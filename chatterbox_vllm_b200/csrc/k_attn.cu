@@ -946,9 +946,9 @@ static size_t g_next_bytes = 0;
 void attn_set_prefetch(const void* w, size_t bytes) { g_next_w = w; g_next_bytes = bytes; }
 int paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                          const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch, int32_t* counters,
-                         int T, int max_kv_len, bool have_plan, void* stream);
+                         int T, int max_kv_len, bool have_plan, void* stream, int n_ctas = 0);
 int attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
-              const int32_t* row_seq);
+              const int32_t* row_seq, int n_ctas = 0);
 static bool balanced_on() {
   static const bool on = !(getenv("CBX_ATTN_BALANCED") && getenv("CBX_ATTN_BALANCED")[0] == '0');
   return on;
@@ -960,11 +960,14 @@ static int32_t* plan_of(void* scratch) {
 // Page-range plan shared by every layer of a decode step (kv_len is the same for all 30 launches).
 // Returns 1 when the balanced variant does not apply to T rows.
 // block_table / row_seq (may be NULL): when given, each range's first pages are resolved here, once for all layers.
+// n_ctas (0 = one per SM): CTAs of the attention launches that will use the plan — fewer than the SM count when the
+// engine runs the two CFG halves of a step on two streams and leaves SMs to the other half's GEMMs.
 int cbx::attn_plan(const int32_t* kv_len, int T, void* scratch, void* stream, const int32_t* block_table, int bt_stride,
-                   const int32_t* row_seq) {
+                   const int32_t* row_seq, int n_ctas) {
   if (T <= 4 || T > kPlanMaxRows || !balanced_on() || scratch == nullptr) return 1;
   if (row_seq == nullptr) block_table = nullptr;
-  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, sm_count(), plan_of(scratch),
+  const int G = n_ctas > 0 && n_ctas < sm_count() ? n_ctas : sm_count();
+  cudaError_t e = launch_pdl(attn_plan_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, kv_len, T, G, plan_of(scratch),
                              block_table, bt_stride, row_seq);
   CBX_REQUIRE(e == cudaSuccess, "attn_plan launch failed: %s", cudaGetErrorString(e));
   count_launch();
@@ -995,8 +998,8 @@ extern "C" int cbx_paged_attn_decode_planned(const void* qkv, const void* kv_lay
 // have_plan: cbx::attn_plan already ran on this stream for the same kv_len (the engine builds it once per step).
 int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32_t* block_table, int bt_stride,
                               const int32_t* row_seq, const int32_t* kv_len, void* out, void* scratch,
-                              int32_t* counters, int T, int max_kv_len, bool have_plan, void* stream) {
-  const int max_ctas = sm_count();
+                              int32_t* counters, int T, int max_kv_len, bool have_plan, void* stream, int n_ctas) {
+  const int max_ctas = n_ctas > 0 && n_ctas < sm_count() ? n_ctas : sm_count();
   if (T <= 0) return 0;
   if (cbx::init_attn()) return -1;
   {
@@ -1021,7 +1024,7 @@ int cbx::paged_attn_decode_ex(const void* qkv, const void* kv_layer, const int32
   }
   if (T > 4 && T <= kPlanMaxRows && balanced_on()) {
     CBX_REQUIRE(scratch != nullptr && counters != nullptr, "cbx_paged_attn_decode: scratch / counters is NULL");
-    if (!have_plan && attn_plan(kv_len, T, scratch, stream, block_table, bt_stride, row_seq)) return -1;
+    if (!have_plan && attn_plan(kv_len, T, scratch, stream, block_table, bt_stride, row_seq, n_ctas)) return -1;
     float* o_part = reinterpret_cast<float*>(scratch);
     float2* ml_part = reinterpret_cast<float2*>(o_part + (size_t)2 * kMaxSms * CBX_HIDDEN);
     cudaError_t e = launch_pdl(paged_attn_decode_bal_kernel, dim3(max_ctas), dim3(kThreads), kSmemBytes, (cudaStream_t)stream,

@@ -75,6 +75,12 @@ struct BlockArgs {
   unsigned long long* acc;   // [4][1024] 64-bit fixed-point (2^-32) accumulator of the 16 heads' O-proj partials:
                              // integer adds commute, so the sum does not depend on arrival order (bit-reproducible)
   bf16* q_out;               // optional [T,3072]: rotated q (tests); may be NULL
+  // FOLD form (after the fused MLP block, k_mlp.cu): the previous layer's down-proj output waits in acc_in; the norm
+  // prologue closes that residual branch, x = bf16(bf16(acc_in * 2^-32) + res), CTA (0,0) writing the rows to res_wb
+  // (NOT the buffer res points at: the other CTAs are still reading that one).  acc_in == NULL: the rows are copied.
+  const unsigned long long* acc_in;   // [kMlpAccCopies][4][1024]: the MLP block's CTAs add into copy b % kMlpAccCopies
+  bf16* res_wb;
+  void* zero_ptr; int zero_bytes;   // cleared after the wait (the accumulator the MLP block of THIS layer will add into)
   int T; float eps;
   int prof_id;               // CBX_BLOCK_PROF builds only
   int stop;                  // profiling aid (env CBX_BLOCK_STOP=k): every CTA returns after phase k; results are garbage
@@ -118,7 +124,7 @@ struct Smem {
 // Wo feature groups (4 features each, 256 in all) owned by cluster rank r: 43, 43, 43, 43, 42, 42
 __host__ __device__ constexpr int wo_group0(int r) { return r * 43 - (r > 4 ? r - 4 : 0); }
 
-template <int TT>
+template <int TT, bool FOLD>
 __global__ void __launch_bounds__(kNW * 32, 1) layer_attn_block_kernel(const BlockArgs a) {
   using S = Smem<TT>;
   constexpr int kLocal = S::kLocal;
@@ -161,11 +167,15 @@ __global__ void __launch_bounds__(kNW * 32, 1) layer_attn_block_kernel(const Blo
     if (g < g_hi) wo[j] = ld_stream(reinterpret_cast<const uint4*>(a.Wo + (size_t)(g * 4 + (lane >> 3)) * 1024 + h * 64) + (lane & 7));
   }
   uint4 lnw[4] = {};
-  if (warp < TT) {
+  if (!FOLD && warp < TT) {
     const uint4* wr = reinterpret_cast<const uint4*>(a.ln_w);
 #pragma unroll
     for (int i = 0; i < 4; ++i) lnw[i] = ld_stream(wr + lane + 32 * i);
   }
+  // FOLD: all warps share the rows (thread -> 16-byte chunk ci = tid of the TT x 128 chunks), norm weights in that mapping
+  const int ci = threadIdx.x;
+  uint4 lnc = make_uint4(0, 0, 0, 0);
+  if (FOLD && ci < TT * 128) lnc = ld_stream(reinterpret_cast<const uint4*>(a.ln_w) + (ci & 127));
   // page ids of this CTA's page-slices, one lane of warps 12..15 per slice: the block table is written at admission
   // and row_seq is re-staged with the same value every step — neither depends on the awaited kernels (kv_len does)
   const int sl = (warp - 12) * 32 + lane;              // slice owned by this lane (warps 12..15), else < 0 or >= kSlices
@@ -209,7 +219,60 @@ __global__ void __launch_bounds__(kNW * 32, 1) layer_attn_block_kernel(const Blo
     if (which < 2) my_pos = a.pos[lane];
     if (which > 0) my_slot = a.slot[lane];
   }
-  if (warp < TT) {                                     // RMSNorm of row `warp` -> xs
+  if (FOLD) {
+    if (a.zero_ptr != nullptr) {
+      uint4* z = reinterpret_cast<uint4*>(a.zero_ptr);
+      const int cta = blockIdx.y * kCl + blockIdx.x;
+      for (int i = cta * (kNW * 32) + threadIdx.x; i < a.zero_bytes / 16; i += kCl * kHeads * (kNW * 32)) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    const bool mine = ci < TT * 128 && (ci >> 7) < T;
+    float f[8];
+    float ss = 0.f;
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (mine) {
+      const uint4 xv = reinterpret_cast<const uint4*>(a.res)[ci];
+      unpack8(xv, f);
+      if (a.acc_in != nullptr) {
+        uint4 av[kMlpAccCopies][4];                    // [copy][16-byte piece of the chunk's 8 u64]: all loads in flight
+#pragma unroll
+        for (int c = 0; c < kMlpAccCopies; ++c)
+#pragma unroll
+          for (int q = 0; q < 4; ++q) av[c][q] = reinterpret_cast<const uint4*>(a.acc_in + (size_t)c * 4096)[ci * 4 + q];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          unsigned long long slo = 0ull, shi = 0ull;
+#pragma unroll
+          for (int c = 0; c < kMlpAccCopies; ++c) {
+            slo += ((unsigned long long)av[c][q].y << 32) | av[c][q].x;
+            shi += ((unsigned long long)av[c][q].w << 32) | av[c][q].z;
+          }
+          const long long lo = (long long)slo, hi = (long long)shi;
+          f[2 * q] = round_bf16(round_bf16((float)lo * (1.f / kAccScale)) + f[2 * q]);
+          f[2 * q + 1] = round_bf16(round_bf16((float)hi * (1.f / kAccScale)) + f[2 * q + 1]);
+        }
+      }
+      o = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+      if (blockIdx.x == 0 && blockIdx.y == 0 && a.res_wb != nullptr) reinterpret_cast<uint4*>(a.res_wb)[ci] = o;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss += f[e] * f[e];
+    }
+    ss = warp_sum(ss);                                 // 32 consecutive chunks lie in one row: warps 4t .. 4t+3 hold row t
+    if (lane == 0 && ci < TT * 128) red[warp] = ss;    // `red` is free until the attention phase
+    __syncthreads();
+    if (ci < TT * 128) {
+      if (mine) {
+        const int t = ci >> 7;
+        const float tot = red[4 * t] + red[4 * t + 1] + red[4 * t + 2] + red[4 * t + 3];   // fixed order: same bits in every CTA
+        const float rstd = rsqrtf(tot * (1.0f / 1024.f) + a.eps);
+        float w[8];
+        unpack8(lnc, w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = round_bf16(f[e] * rstd) * w[e];
+        o = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+      }
+      xs[ci] = o;
+    }
+  } else if (warp < TT) {                              // RMSNorm of row `warp` -> xs
     uint4 o[4] = {};
     if (warp < T) {
       const uint4* xr = reinterpret_cast<const uint4*>(a.res + (size_t)warp * 1024);
@@ -481,16 +544,16 @@ bool block_on() {
   return on;
 }
 
-template <int TT>
+template <int TT, bool FOLD>
 int launch_block(const BlockArgs& a, cudaStream_t s) {
-  static bool attr = false;
+  static bool attr = false;                            // per instantiation
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(layer_attn_block_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(layer_attn_block_kernel<TT, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Smem<TT>::total);
     if (e != cudaSuccess) { set_error("layer_attn_block smem attribute: %s", cudaGetErrorString(e)); return -2; }
     attr = true;
   }
-  cudaError_t e = launch_pdl_cluster(layer_attn_block_kernel<TT>, dim3(kCl, kHeads), dim3(kNW * 32), Smem<TT>::total, s, kCl, a);
+  cudaError_t e = launch_pdl_cluster(layer_attn_block_kernel<TT, FOLD>, dim3(kCl, kHeads), dim3(kNW * 32), Smem<TT>::total, s, kCl, a);
   if (e != cudaSuccess) { set_error("layer_attn_block launch failed: %s", cudaGetErrorString(e)); return -2; }
   count_launch();
   return 0;
@@ -531,9 +594,28 @@ int layer_attn_block(const void* res, const void* ln_w, const void* Wqkv, const 
 #ifdef CBX_BLOCK_PROF
   a.prof_id = g_bprof_next++;
 #endif
-  if (T == 1) return launch_block<1>(a, s);
-  if (T == 2) return launch_block<2>(a, s);
-  return launch_block<4>(a, s);
+  if (T == 1) return launch_block<1, false>(a, s);
+  if (T == 2) return launch_block<2, false>(a, s);
+  return launch_block<4, false>(a, s);
+}
+// FOLD form: the rows enter as res (+ acc_in, the previous layer's down-proj output in 2^-32 fixed point, or NULL); the
+// closed rows are written to res_wb (!= res); zero_ptr / zero_bytes: an accumulator to clear after the wait
+int layer_attn_block_fold(const void* res, const void* acc_in, void* res_wb, void* zero_ptr, int zero_bytes, const void* ln_w,
+                          const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos, const int64_t* slot,
+                          void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq, const int32_t* kv_len,
+                          void* acc, int T, float eps, cudaStream_t s) {
+  BlockArgs a = {};
+  a.res = (bf16*)res; a.ln_w = (const bf16*)ln_w; a.Wqkv = (const bf16*)Wqkv; a.Wo = (const bf16*)Wo;
+  a.cos_sin = (const bf16*)cos_sin; a.pos = pos; a.slot = slot; a.kv_layer = (uint8_t*)kv_layer; a.bt = bt;
+  a.bt_stride = bt_stride; a.row_seq = row_seq; a.kv_len = kv_len; a.acc = (unsigned long long*)acc;
+  a.acc_in = (const unsigned long long*)acc_in; a.res_wb = (bf16*)res_wb; a.zero_ptr = zero_ptr; a.zero_bytes = zero_bytes;
+  a.T = T; a.eps = eps;
+#ifdef CBX_BLOCK_PROF
+  a.prof_id = g_bprof_next++;
+#endif
+  if (T == 1) return launch_block<1, true>(a, s);
+  if (T == 2) return launch_block<2, true>(a, s);
+  return launch_block<4, true>(a, s);
 }
 }  // namespace cbx
 
@@ -577,9 +659,9 @@ extern "C" int cbx_debug_block_max_clusters(int TT, int cluster) {
   cfg.attrs = at; cfg.numAttrs = 1;
   int n = -1;
   cudaError_t e;
-  if (TT == 1) { cfg.dynamicSmemBytes = Smem<1>::total; cudaFuncSetAttribute(layer_attn_block_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<1>::total); e = cudaOccupancyMaxActiveClusters(&n, layer_attn_block_kernel<1>, &cfg); }
-  else if (TT == 2) { cfg.dynamicSmemBytes = Smem<2>::total; cudaFuncSetAttribute(layer_attn_block_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<2>::total); e = cudaOccupancyMaxActiveClusters(&n, layer_attn_block_kernel<2>, &cfg); }
-  else { cfg.dynamicSmemBytes = Smem<4>::total; cudaFuncSetAttribute(layer_attn_block_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<4>::total); e = cudaOccupancyMaxActiveClusters(&n, layer_attn_block_kernel<4>, &cfg); }
+  if (TT == 1) { cfg.dynamicSmemBytes = Smem<1>::total; cudaFuncSetAttribute(layer_attn_block_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<1>::total); e = cudaOccupancyMaxActiveClusters(&n, layer_attn_block_kernel<1, false>, &cfg); }
+  else if (TT == 2) { cfg.dynamicSmemBytes = Smem<2>::total; cudaFuncSetAttribute(layer_attn_block_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<2>::total); e = cudaOccupancyMaxActiveClusters(&n, layer_attn_block_kernel<2, false>, &cfg); }
+  else { cfg.dynamicSmemBytes = Smem<4>::total; cudaFuncSetAttribute(layer_attn_block_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<4>::total); e = cudaOccupancyMaxActiveClusters(&n, layer_attn_block_kernel<4, false>, &cfg); }
   if (e != cudaSuccess) { set_error("cudaOccupancyMaxActiveClusters: %s", cudaGetErrorString(e)); return -1; }
   return n;
 }

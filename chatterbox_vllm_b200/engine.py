@@ -107,6 +107,14 @@ class T3Engine:
             self._quantize_weights()
         elif self.weight_dtype != "bf16":
             raise ValueError(f"weight_dtype {self.weight_dtype!r}: expected 'bf16' or 'fp8_e4m3'")
+        elif os.environ.get("CBX_MLP_FUSED") == "1":
+            # opt-in two-launch layer of the T <= 4 decode path (measured equal to the default three launches): its fused
+            # MLP block reads the down-proj weights by MLP feature, so a transposed copy (+8 MB per layer) keeps a CTA's
+            # slice contiguous (csrc/k_mlp.cu)
+            self.wd_t = [w.t().contiguous() for w in self.wd]
+            self._arr_wd_t = (C.c_void_p * self.n_layers)(*[t.data_ptr() for t in self.wd_t])
+            torch.cuda.synchronize()
+            check(load().cbx_engine_set_down_t(self._h, self._arr_wd_t, self.n_layers), "set_down_t")
         self.gpu_launches = 0
         self._rows: dict[int, list[int]] = {}             # block-table row -> its blocks, in table order
         self.preemptions = 0

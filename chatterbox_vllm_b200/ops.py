@@ -202,6 +202,7 @@ def layer_qkv(res, ln_w, wqkv, cos_sin, pos, slot, kv_layer, eps: float = 1e-5, 
 
 
 _block_ws: dict = {}
+_mlp_ws: dict = {}
 
 
 def layer_attn_block(res, ln_w, wqkv, wo, cos_sin, pos, slot, kv_layer, block_table, row_seq, kv_len, max_kv_len: int,
@@ -217,6 +218,20 @@ def layer_attn_block(res, ln_w, wqkv, wo, cos_sin, pos, slot, kv_layer, block_ta
                                       _p(pos, torch.int32), _p(slot, torch.int64), _p(kv_layer), _p(block_table, torch.int32),
                                       block_table.stride(0), _p(row_seq, torch.int32), _p(kv_len, torch.int32), _p(ws),
                                       _p(q_out, BF16), T, max_kv_len, eps, _stream()), "layer_attn_block")
+    return res
+
+
+def layer_mlp_block(res, ln_w, wgu_packed, wd_t, eps: float = 1e-5):
+    """cbx_layer_mlp_block: norm + gate_up + SiLU·mul + down-proj + residual in one launch (T <= 4 rows, bf16 weights).
+    wd_t = Wd.t().contiguous() ([4096, 1024]).  Updates `res` in place."""
+    T = res.shape[0]
+    assert tuple(wd_t.shape) == (4096, HIDDEN) and tuple(wgu_packed.shape) == (8192, HIDDEN)
+    ws = _mlp_ws.get(res.device)
+    if ws is None:
+        ws = torch.zeros(load().cbx_layer_mlp_block_scratch_bytes(), dtype=torch.uint8, device=res.device)
+        _mlp_ws[res.device] = ws
+    check(load().cbx_layer_mlp_block(_p(res, BF16), _p(ln_w, BF16), _p(wgu_packed, BF16), _p(wd_t, BF16), _p(ws), T, eps,
+                                     _stream()), "layer_mlp_block")
     return res
 
 

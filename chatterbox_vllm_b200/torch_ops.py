@@ -120,5 +120,16 @@ def _(res, ln_w, wqkv, wo, cos_sin, pos, slot, kv_layer, block_table, row_seq, k
     return None
 
 
+@_lib.custom_op("cbx::layer_mlp_block", mutates_args=("res",), device_types="cuda")
+def layer_mlp_block(res: Tensor, ln_w: Tensor, wgu_packed: Tensor, wd_t: Tensor, eps: float = 1e-5) -> None:
+    """cbx_layer_mlp_block: the MLP half of a layer in one launch (T <= 4 rows); wd_t = Wd.t().contiguous()."""
+    ops.layer_mlp_block(res, ln_w, wgu_packed, wd_t, eps)
+
+
+@layer_mlp_block.register_fake
+def _(res, ln_w, wgu_packed, wd_t, eps=1e-5):
+    return None
+
+
 OPS = ("slot_mapping", "rmsnorm", "linear", "layer_qkv", "paged_attn_decode", "linear_residual", "layer_gate_up",
-       "head_logits", "layer_attn_block")
+       "head_logits", "layer_attn_block", "layer_mlp_block")

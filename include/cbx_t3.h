@@ -196,6 +196,16 @@ int cbx_layer_attn_block(void* res, const void* ln_w, const void* Wqkv, const vo
                          const int32_t* pos, const int64_t* slot, void* kv_layer, const int32_t* block_table,
                          int bt_stride, const int32_t* row_seq, const int32_t* kv_len, void* scratch, void* q_out,
                          int T, int max_kv_len, float eps, void* stream);
+/* The MLP half of a layer as ONE launch for T <= 4 rows (llama.py:117-120,323-326): res += Wd · (SiLU(g)·u) of
+ * RMSNorm(res)·ln_w · Wgu^T.  One CTA per SM owns 27-28 of the 4096 MLP features, computes their activations and
+ * multiplies them by ITS rows of WdT = Wd^T ([4096,1024] row-major bf16: the transposed down-proj weights), adding the
+ * fp32 partial [T,1024] into `scratch` as 64-bit fixed point with one bulk reduction (order-independent sum; four
+ * copies of the accumulator, CTA b into copy b % 4, so that L2 does not serialise 148 reductions per address).  bf16
+ * weights only; Wgu packed by cbx_pack_gate_up.  scratch: cbx_layer_mlp_block_scratch_bytes() bytes, zero before
+ * first use (left zero).  Inside the engine the accumulator is folded by the next layer's attention block instead. */
+int64_t cbx_layer_mlp_block_scratch_bytes(void);
+int cbx_layer_mlp_block(void* res, const void* ln_w, const void* Wgu, const void* WdT, void* scratch, int T, float eps,
+                        void* stream);
 /* logits[T, CBX_LOGITS_LD] = RMSNorm(res)·norm_w · Whead[8194,1024]^T (llama.py:430 + t3.py:729-730). */
 int cbx_head_logits(const void* res, const void* norm_w, const void* Whead, void* logits, void* h_scratch,
                     int T, float eps, void* stream);
@@ -329,6 +339,11 @@ typedef struct cbx_fp8_weights {
 } cbx_fp8_weights;
 /* Switch a created engine's projections + speech head to FP8 weights (pointers must outlive it). */
 int cbx_engine_set_fp8_weights(cbx_engine*, const cbx_fp8_weights*);
+/* Transposed bf16 down-proj weights per layer (wd_t[l] = Wd[l]^T, [4096,1024]) for the engine's two-launch layer of the
+ * T <= 4 decode path (cbx_layer_attn_block's kernel + cbx_layer_mlp_block's kernel, each folding the other's
+ * accumulator).  Without them the T <= 4 layer runs three launches.  NULL removes them.  No reference counterpart
+ * (vLLM keeps one layout per weight); a layout choice of this implementation. */
+int cbx_engine_set_down_t(cbx_engine*, const void* const* wd_t, int n_layers);
 
 /* Device pointer of an internal buffer by name ("x","h","qkv","attn","act","logits","pos",
  * "slot","kv_len","row_seq","head_rows") for tests / the Python façade; NULL if unknown. */

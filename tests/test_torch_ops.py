@@ -17,6 +17,7 @@ def test_ops_are_registered_with_schemas_and_mutation_annotations():
     s = str(torch.ops.cbx.layer_attn_block.default._schema)
     assert "Tensor(a0!) res" in s and "Tensor(a7!) kv_layer" in s
     assert "Tensor(a6!) kv_layer" in str(torch.ops.cbx.layer_qkv.default._schema)
+    assert "Tensor(a0!) res" in str(torch.ops.cbx.layer_mlp_block.default._schema)
 
 
 def test_fake_tensor_propagation_needs_no_gpu():
@@ -83,3 +84,11 @@ def test_torch_ops_give_the_ctypes_paths_bits():
     torch.ops.cbx.layer_attn_block(r4, ln, wqkv, wo, cs, pos[:2], slot[:2], kv4, bt, rows[:2], kv_len[:2], 6)
     ops.layer_attn_block(r4b, ln, wqkv, wo, cs, pos[:2], slot[:2], kv4b, bt, rows[:2], kv_len[:2], 6)
     assert torch.equal(r4, r4b) and torch.equal(kv4, kv4b) and not torch.equal(r4, res[:2])
+    # ... and the fused MLP block
+    g = torch.Generator().manual_seed(9)
+    wgu = ops.pack_gate_up((torch.randn(8192, 1024, generator=g) * 0.03).to(BF16).cuda())
+    wd_t = (torch.randn(4096, 1024, generator=g) * 0.02).to(BF16).cuda()
+    m_a, m_b = res[:2].clone(), res[:2].clone()
+    assert torch.ops.cbx.layer_mlp_block(m_a, ln, wgu, wd_t) is None
+    ops.layer_mlp_block(m_b, ln, wgu, wd_t)
+    assert torch.equal(m_a, m_b) and not torch.equal(m_a, res[:2])
