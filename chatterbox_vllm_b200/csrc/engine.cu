@@ -42,6 +42,8 @@ int launch_decode_prepare(const void*, const int32_t*, const int32_t*, const int
 int launch_cfg_sample(const void*, const cbx_sampler_state*, int, const NextStep&, cudaStream_t, const int32_t* pair_map = nullptr,
                       int n_sub = 0);
 int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
+int gemm_partials_fold(const void* x, const void* W, void* part, int M, int K, int splits, cudaStream_t s, void* res,
+                       const void* ln_w, void* h_out, float eps, void* counters);
 bool layer_attn_block_supported(int T, int max_kv_len);
 int layer_attn_block(const void* res, const void* ln_w, const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos,
                      const int64_t* slot, void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq,
@@ -124,6 +126,7 @@ struct cbx_engine {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   cudaEvent_t ev_att[2][32] = {};   // "attention of layer l done" per half: the two halves' attention launches alternate
   float* part;                 // split-K partials [4][split_max_rows][1024] fp32 
+  unsigned* fold_cnt;          // arrival counters of the split-K GEMMs that fold their own partials (zero between launches)
   unsigned* mega_sync;         // exit counter + epoch of the persistent decode kernel
   uint8_t* mega_ws;            // its tagged exchange buffers
   bool mega = false;           // env CBX_MEGA=1: T <= 4 decode steps run as ONE persistent kernel (k_mega.cu).  Parity-tested,
@@ -161,6 +164,7 @@ static size_t carve(const cbx_engine_cfg* c, cbx_engine* e, uint8_t* base) {
 #endif
   p = take((size_t)4 * 512 * 1024 * 4); if (e) e->part = (float*)p;
   p = take(256); if (e) e->mega_sync = (unsigned*)p;
+  p = take(256); if (e) e->fold_cnt = (unsigned*)p;
   p = take(kAccBytes * kAccSlots); if (e) e->block_acc = (unsigned long long*)p;
   p = take(mega_ws_bytes()); if (e) e->mega_ws = (uint8_t*)p;
   return off;
@@ -192,6 +196,7 @@ extern "C" cbx_engine* cbx_engine_create(const cbx_engine_cfg* cfg, const cbx_we
   // split-K attention tickets start at zero and reset themselves
   cudaMemset(e->attn_counters, 0, (size_t)cfg->max_rows * 4);
   cudaMemset(e->mega_sync, 0, 256);
+  cudaMemset(e->fold_cnt, 0, 256);
   cudaMemset(e->block_acc, 0, kAccBytes * kAccSlots);
 #ifdef CBX_EXPERIMENTS
   // second stream of the two-stream decode step (forward_dual); without it the step runs on one stream
@@ -495,6 +500,11 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
   int splits = 1;
   if (T > G && !e->trace && T <= e->split_max_rows) splits = m_tiles <= 2 ? 4 : (m_tiles <= 4 ? 2 : 1);
   bool pending = false;                                // down-proj partials not yet folded into res
+  bool normed = false;                                 // ... or folded already, with h = the NEXT norm's output
+  // env CBX_GEMM_FOLD=1 (`make EXPERIMENTS=1` builds only): the split-K GEMMs fold their own partials instead of leaving
+  // them to a separate add+RMSNorm launch — bit-identical, measured slower (k_gemm.cu).  Read per call: the test compares
+  // the two forms in one process (a captured graph keeps what it was captured with).
+  const bool fold_on = getenv("CBX_GEMM_FOLD") && getenv("CBX_GEMM_FOLD")[0] == '1';
   // decode attention cuts the step's pages into equal per-CTA ranges: one plan serves all layers
   static const bool plan_each = getenv("CBX_ATTN_PLAN_EACH") != nullptr;   // debugging aid: rebuild the plan per layer
   const bool have_plan = !plan_each && e->n_prefill_items == 0 && !(sk & 2) && attn_plan(e->kv_len, T, e->attn_scratch, s, e->block_table, e->bt_stride, e->row_seq) == 0;
@@ -548,9 +558,10 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
                                      pf ? e->wo[li] : nullptr, (size_t)1024 * 1024 * 2, e->sqkv[li])) return -1;
       if (pf) attn_set_prefetch(e->wgu[li], (size_t)8192 * 1024 * 2);
     } else {
-      if (pending ? cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln1[li], e->h, T, eps, s)
-                  : cbx_rmsnorm(e->res, nullptr, e->ln1[li], e->h, T, eps, s)) return -1;
-      pending = false;
+      if (normed) {}                                   // the previous layer's down-proj GEMM folded AND normalised (ln1 of this layer)
+      else if (pending ? cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln1[li], e->h, T, eps, s)
+                       : cbx_rmsnorm(e->res, nullptr, e->ln1[li], e->h, T, eps, s)) return -1;
+      pending = false; normed = false;
       if (!(sk & 1) && gemm_qkv_rope(e->h, e->wqkv[li], e->qkv, e->w.cos_sin, e->pos, e->slot, kv, T, s, e->sqkv[li])) return -1;
     }
     if (e->n_prefill_items > 0) {
@@ -576,12 +587,28 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
         if (!(sk & 4) && gemm_residual(e->attn, e->wo[li], e->res, T, 1024, 1024, s, e->so[li])) return -1;
         if (cbx_rmsnorm(e->res, nullptr, e->ln2[li], e->h, T, eps, s)) return -1;
       } else {
-        if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s, e->so[li])) return -1;
-        if (cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
+        // the split-K GEMM folds its own partials (add + RMSNorm by the producing CTAs behind an arrival counter) when
+        // its grid is co-resident; rc 1 = not applicable: the two-kernel form
+        int rc = fold_on && !e->fp8 && !sk ? gemm_partials_fold(e->attn, e->wo[li], e->part, T, 1024, splits, s, e->res, e->ln2[li],
+                                                                 e->h, eps, e->fold_cnt) : 1;
+        if (rc < 0) return -1;
+        if (rc == 1) {
+          if (!(sk & 4) && gemm_partials(e->attn, e->wo[li], e->part, T, 1024, 1024, splits, s, e->so[li])) return -1;
+          if (cbx_rmsnorm_reduce(e->part, splits, e->res, e->ln2[li], e->h, T, eps, s)) return -1;
+        }
       }
       if (!(sk & 8) && gemm_bf16_tc(e->h, e->wgu[li], e->act, T, 8192, 1024, 4096, 1, s, e->sgu[li])) return -1;
-      if (!(sk & 16) && gemm_partials(e->act, e->wd[li], e->part, T, 1024, 4096, splits, s, e->sd[li])) return -1;
-      pending = true;
+      {
+        const void* ln_next = li + 1 < e->w.n_layers ? e->ln1[li + 1] : e->w.norm;   // what the fold normalises with
+        int rc = fold_on && !e->fp8 && !sk ? gemm_partials_fold(e->act, e->wd[li], e->part, T, 4096, splits, s, e->res, ln_next,
+                                                                 e->h, eps, e->fold_cnt) : 1;
+        if (rc < 0) return -1;
+        if (rc == 0) normed = true;
+        else {
+          if (!(sk & 16) && gemm_partials(e->act, e->wd[li], e->part, T, 1024, 4096, splits, s, e->sd[li])) return -1;
+          pending = true;
+        }
+      }
     } else {
       if (!(sk & 4) && gemm_residual(e->attn, e->wo[li], e->res, T, 1024, 1024, s, e->so[li])) return -1;
       if (cbx_rmsnorm(e->res, nullptr, e->ln2[li], e->h, T, eps, s)) return -1;
@@ -592,6 +619,7 @@ static int forward_layers(cbx_engine* e, int T, int max_kv_len, cudaStream_t s, 
       cudaMemcpyAsync(e->trace + (size_t)li * T * CBX_HIDDEN, e->res, (size_t)T * CBX_HIDDEN * 2,
                       cudaMemcpyDeviceToDevice, s);
   }
+  if (normed) return 0;                                // the last down-proj GEMM folded and applied the final norm
   if (pending) return cbx_rmsnorm_reduce(e->part, splits, e->res, e->w.norm, e->h, T, eps, s);
   if (final_norm || T > G) return cbx_rmsnorm(e->res, nullptr, e->w.norm, e->h, T, eps, s);
   return 0;

@@ -81,7 +81,62 @@ struct Cfg {
 struct EpiArgs {               // EPI 2 only
   const bf16* cos_sin; const int32_t* pos; const int64_t* slot; uint8_t* kv_layer;
   int prof_id;                 // CBX_GEMM_PROF builds only
+  // EPI 5 only (split-K partials folded by the CTAs that produced them): residual stream [M,1024] (updated in place),
+  // norm weights [1024], normalised rows out [M,1024], two counters per row tile (arrived, done; zero between launches)
+  bf16* f_res; const bf16* f_ln; bf16* f_out; unsigned* f_cnt; float f_eps;
 };
+
+// EPI 5 tail: rows [ra, ra + 2) of the residual stream (N = 1024): res = bf16(bf16(sum of the S K-slices) + res),
+// out = bf16(bf16(res * rstd) * w) — thread t owns columns 4t .. 4t+3; the adds, the warp sums and the 8-warp tree are
+// rmsnorm_reduce4_kernel's (k_misc.cu), so the rows carry the same bits as the two-kernel form's.
+template <int S>
+__device__ __forceinline__ void fold_two_rows(const float4* part, int M, int ra, const EpiArgs& ea, float (*sums)[8]) {
+  const int t = threadIdx.x;
+  const uint2 wv = __ldg(reinterpret_cast<const uint2*>(ea.f_ln) + t);
+  uint2* res = reinterpret_cast<uint2*>(ea.f_res);
+  float4 a[2][S];
+  uint2 q[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    if (ra + k < M) {
+      q[k] = __ldcg(res + (size_t)(ra + k) * 256 + t);
+#pragma unroll
+      for (int z = 0; z < S; ++z) a[k][z] = __ldcg(part + ((size_t)z * M + ra + k) * 256 + t);
+    }
+  }
+  float f[2][4];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    float ss = 0.f;
+    if (ra + k < M) {
+      float4 sum = a[k][0];
+#pragma unroll
+      for (int z = 1; z < S; ++z) { sum.x += a[k][z].x; sum.y += a[k][z].y; sum.z += a[k][z].z; sum.w += a[k][z].w; }
+      f[k][0] = round_bf16(sum.x); f[k][1] = round_bf16(sum.y); f[k][2] = round_bf16(sum.z); f[k][3] = round_bf16(sum.w);
+      const float g[4] = {bf_lo(q[k].x), bf_hi(q[k].x), bf_lo(q[k].y), bf_hi(q[k].y)};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) f[k][i] = round_bf16(f[k][i] + g[i]);
+      res[(size_t)(ra + k) * 256 + t] = make_uint2(pack_bf16(f[k][0], f[k][1]), pack_bf16(f[k][2], f[k][3]));
+      ss = (f[k][0] * f[k][0] + f[k][1] * f[k][1]) + (f[k][2] * f[k][2] + f[k][3] * f[k][3]);
+    }
+    ss = warp_sum(ss);
+    if ((t & 31) == 0) sums[k][t >> 5] = ss;
+  }
+  __syncthreads();
+  const float wf[4] = {bf_lo(wv.x), bf_hi(wv.x), bf_lo(wv.y), bf_hi(wv.y)};
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    if (ra + k < M) {
+      const float* sm = sums[k];
+      const float tot = ((sm[0] + sm[1]) + (sm[2] + sm[3])) + ((sm[4] + sm[5]) + (sm[6] + sm[7]));
+      const float rstd = rsqrtf(tot * (1.0f / CBX_HIDDEN) + ea.f_eps);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) f[k][i] = round_bf16(f[k][i] * rstd) * wf[i];
+      reinterpret_cast<uint2*>(ea.f_out)[(size_t)(ra + k) * 256 + t] = make_uint2(pack_bf16(f[k][0], f[k][1]), pack_bf16(f[k][2], f[k][3]));
+    }
+  }
+  __syncthreads();                                     // sums are reused by the next pair of rows
+}
 
 // CN = 2: CTA pair along M (grid.x = row tiles, cluster dims (2, 1, 1), rank 0 = leader).  The decode GEMMs are bound by the
 // bytes entering the SMs (activation re-reads are most of them); a pair computes a
@@ -378,7 +433,7 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
             dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
             dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
           }
-        } else if (EPI == 4) {
+        } else if (EPI == 4 || EPI == 5) {
           // split-K partial: fp32 [gridDim.z][M][N] behind y (N % 32 == 0); summed by cbx_rmsnorm_reduce
           float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(y) + ((size_t)blockIdx.z * M + row) * N + col);
 #pragma unroll
@@ -419,7 +474,35 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
     }
     tc_fence_before();
   }
+  if (EPI == 5) __threadfence();                       // this thread's partial stores, before the CTA announces them
   __syncthreads();
+  if (EPI == 5) {
+    // ---- the split-K fold, by the CTAs that produced the slices.  Every CTA of a 128-row tile (column tiles x K
+    // slices: 64 or 32 CTAs) announces its partials, waits until all of them have, and then adds + normalises its share
+    // of the tile's rows — what a separate add+RMSNorm launch did (60 per M1 step, each a wait release + a row fetch
+    // + a tail behind the GEMM's).  The host launches this form only when the whole grid is co-resident (<= one CTA
+    // per SM), so the wait cannot deadlock; CTAs of the NEXT kernel cannot be ahead of ours on an SM either (they are
+    // launched once every CTA of this grid has executed griddepcontrol.launch_dependents, i.e. runs).
+    __shared__ float f_sums[2][8];
+    const int n_cta = gridDim.x * gridDim.z, ci = blockIdx.x + gridDim.x * blockIdx.z;
+    unsigned* arrive = ea.f_cnt + 2 * blockIdx.y;
+    unsigned* done = arrive + 1;
+    if (threadIdx.x == 0) {
+      atomicAdd(arrive, 1u);
+      unsigned v;
+      do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(arrive) : "memory"); } while (v < (unsigned)n_cta);
+    }
+    __syncthreads();
+    const float4* part = reinterpret_cast<const float4*>(y);
+    for (int base = 2 * ci; base < BM; base += 2 * n_cta) {
+      if (gridDim.z == 4) fold_two_rows<4>(part, M, m0 + base, ea, f_sums);
+      else fold_two_rows<2>(part, M, m0 + base, ea, f_sums);
+    }
+    if (threadIdx.x == 0) {                            // the last CTA of the tile to finish hands the counters back empty
+      const unsigned d = atomicAdd(done, 1u);
+      if (d == (unsigned)n_cta - 1) { *arrive = 0u; *done = 0u; }
+    }
+  }
   if (threadIdx.x == 0) PROF(6);
   if (CN > 1)      // nobody leaves while the leader's MMAs may still read this CTA's shared memory / TMEM
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -519,6 +602,9 @@ int init_gemm() {
   if (done) return 0;
   if (set_attr<64, 0, 1>() || set_attr<64, 1, 1>() || set_attr<128, 0, 1>() || set_attr<128, 1, 1>() || set_attr<64, 2, 1>() ||
       set_attr<64, 3, 1>() || set_attr<128, 3, 1>() || set_attr<64, 4, 1>() || set_attr<128, 2, 1>()) return -1;
+#ifdef CBX_EXPERIMENTS
+  if (set_attr<64, 5, 1>()) return -1;
+#endif
   if (set_attr_pairs<0>() || set_attr_pairs<1>() || set_attr_pairs<2>() || set_attr_pairs<3>() || set_attr_pairs<4>()) return -1;
   if (set_attr8<64, 0>() || set_attr8<64, 1>() || set_attr8<64, 2>() || set_attr8<64, 3>() || set_attr8<64, 4>() ||
       set_attr8<128, 0>() || set_attr8<128, 1>() || set_attr8<128, 2>() || set_attr8<128, 3>()) return -1;
@@ -667,6 +753,26 @@ int gemm_partials(const void* x, const void* W, void* part, int M, int N, int K,
   if (const int w = pair_width(M, 4096)) return launch_pair_w<4>(w, x, W, part, M, N, K, N, s, EpiArgs(), splits);
   return launch<64, 4>(x, W, part, M, N, K, N, s, EpiArgs(), splits);
 }
+#ifdef CBX_EXPERIMENTS   // `make EXPERIMENTS=1` + env CBX_GEMM_FOLD=1.  Bit-identical to the two-kernel form (GPU test) and
+// SLOWER: M1 3.462 -> 3.526 ms per step (154 launches instead of 214).  A programmatic-dependent-launch boundary costs
+// less than the arrival counter + spin + fold serialised behind the GEMM's epilogue: the separate kernel's launch, wait
+// and weight fetch overlap the GEMM's tail, the in-kernel fold cannot start before the slowest CTA of the tile.
+// EPI 5: gemm_partials + the add+RMSNorm that folds them, in one launch: res[M,1024] = bf16(bf16(x·W^T) + res) summed
+// over `splits` K-slices in slice order, h_out = RMSNorm(res)·ln_w (the bits of gemm_partials + cbx_rmsnorm_reduce).
+// counters: 2 x (row tiles) uint32, zero on entry (left zero).  Returns 1 without launching when the form does not
+// apply (the caller then runs the two kernels): N != 1024, splits not 2 or 4, or a grid that is not co-resident.
+int gemm_partials_fold(const void* x, const void* W, void* part, int M, int K, int splits, cudaStream_t s, void* res,
+                       const void* ln_w, void* h_out, float eps, void* counters) {
+  const int m_tiles = (M + BM - 1) / BM;
+  if ((splits != 2 && splits != 4) || K % (BK * splits) != 0 || pair_width(M, 4096) != 0) return 1;
+  if (16 * m_tiles * splits > sm_count() || counters == nullptr) return 1;
+  EpiArgs ea = {};
+  ea.f_res = (bf16*)res; ea.f_ln = (const bf16*)ln_w; ea.f_out = (bf16*)h_out; ea.f_cnt = (unsigned*)counters; ea.f_eps = eps;
+  return launch<64, 5>(x, W, part, M, 1024, K, 1024, s, ea, splits);
+}
+#else
+int gemm_partials_fold(const void*, const void*, void*, int, int, int, cudaStream_t, void*, const void*, void*, float, void*) { return 1; }
+#endif
 int gemv_bf16(const void*, const void*, void*, int, int, int, int, int, cudaStream_t, const float* wscale = nullptr);
 }  // namespace cbx
 

@@ -643,3 +643,32 @@ def test_engine_prefill_and_decode_are_deterministic_at_scale(ops):
     for _ in range(3):
         assert eng.generate(reqs) == first
     eng.close()
+
+
+@pytest.mark.parametrize("n_pairs", [32, 96])
+def test_split_k_fold_inside_the_gemm_equals_the_separate_reduce_kernel(ops, n_pairs, monkeypatch):
+    """T = 64 / 192 rows (1 / 2 row tiles), experiment builds: with CBX_GEMM_FOLD=1 the split-K o_proj / down_proj GEMMs
+    fold their own partials (add + RMSNorm by the producing CTAs behind an arrival counter, k_gemm.cu EPI 5) instead of
+    leaving them to rmsnorm_reduce4_kernel.  Same adds in the same order: tokens AND the last step's logits must be
+    bit-identical, graph replay and eager, and the arrival counters must come back to zero (a second run gives the
+    same bits).  (Measured slower than the default two-kernel form, so it is not in the default library.)"""
+    if not ops._lib.load().cbx_has_experiments():
+        pytest.skip("default build: the experiment kernels are behind `make EXPERIMENTS=1`")
+    n_steps = 8
+    out = {}
+    for fold in ("1", "0"):
+        monkeypatch.setenv("CBX_GEMM_FOLD", fold)
+        for use_graph in (True, False):
+            cfg, w, eng = _mk_engine(3, n_pairs, use_graph=use_graph)
+            reqs = _requests(n_pairs, n_steps, temperature=0.0, repetition_penalty=2.0)
+            l0 = eng.gpu_launches
+            toks = eng.generate(reqs, poll_every=7)
+            assert eng.generate(reqs, poll_every=7) == toks
+            lg = eng.buffer("logits", (2 * n_pairs, 8256), BF16)[:, :8194].clone()
+            out[(fold, use_graph)] = (toks, lg, eng.gpu_launches - l0)
+            eng.close()
+    ref_t, ref_l, ref_n = out[("0", False)]
+    for key, (t, l, n) in out.items():
+        assert t == ref_t, f"fold={key[0]} graph={key[1]}: tokens differ from the two-kernel form"
+        assert torch.equal(l, ref_l), f"fold={key[0]} graph={key[1]}: logits differ from the two-kernel form"
+    assert out[("1", False)][2] < ref_n, "the folding form did not launch fewer kernels"
