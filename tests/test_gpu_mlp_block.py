@@ -77,7 +77,8 @@ def test_engine_two_launch_layer_streams_and_accumulators(ops, n_layers, monkeyp
             reqs = _requests(n_pairs, n_steps, temperature=0.0, repetition_penalty=2.0)
             got = eng.generate(reqs, poll_every=5)
             l0 = eng.gpu_launches                         # one more step over the (finished, inert) slots: count its launches
-            eng.decode(n_pairs, 1, 64)
+            with torch.cuda.stream(eng.stream):           # graph capture needs a real stream, not the legacy default one
+                eng.decode(n_pairs, 1, 64)
             torch.cuda.synchronize()
             assert eng.gpu_launches - l0 == 2 * (n_layers - 1) + 3 + 2, "the two-launch layer did not run"
             acc = eng.buffer("block_acc", (4 * 4 * 1024,), torch.int64)
