@@ -722,6 +722,7 @@ extern "C" int cbx_engine_decode(cbx_engine* e, int B, int n_steps, int max_kv_l
   cudaStream_t s = (cudaStream_t)stream;
   const int64_t l0 = launches();
   int64_t extra = 0;
+  if (s == nullptr || s == cudaStreamLegacy) use_graph = 0;   // the legacy default stream cannot be captured: eager launches
   if (!use_graph) {
     for (int i = 0; i < n_steps; ++i) if (decode_step(e, B, max_kv_len, s)) return -1;
   } else {
