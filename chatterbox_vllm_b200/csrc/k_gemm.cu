@@ -332,8 +332,9 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
   // Epilogue.  A warp may only read the TMEM lane quarter (warp % 4); with one warp per quarter the
   // epilogue is a single warp per SM sub-partition issuing dependent math (measured: SiLU epilogue
   // +3.5 us at T = 256).  For the column-chunked epilogues the four role warps, idle by now, take every
-  // other 32-column chunk of their quarter.
-  constexpr bool kAllWarps = EPI != 2;
+  // other 32-column chunk of their quarter; for the RoPE / KV-append epilogue (one 64-column head at a time) every
+  // other head, when the tile holds more than one (the prefill shapes: BN = 128 / 256).
+  constexpr bool kAllWarps = EPI != 2 || BN > 64;
   if (warp < 8 && (warp >= 4 || kAllWarps)) {
     __syncwarp();
     const int ew = warp & 3;                           // TMEM lane quarter
@@ -354,7 +355,7 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
     if (EPI == 2) {
       // ---- RoPE + q store + KV append: each 64-wide half of the tile is head (col/64) % 16 of q (0), k (1) or v (2)
 #pragma unroll 1
-      for (int hh = 0; hh < BN / 64; ++hh) {
+      for (int hh = (BN > 64 && warp < 4) ? 1 : 0; hh < BN / 64; hh += (BN > 64 ? 2 : 1)) {
       uint32_t r0[32], r1[32];
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + hh * 64, r0);
       tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + hh * 64 + 32, r1);
