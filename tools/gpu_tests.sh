@@ -20,3 +20,10 @@ run sampler tests/test_gpu_engine.py -k "sampler or prefill_embed"
 run engine  tests/test_gpu_engine.py -k "engine"
 run facade  tests/test_gpu_facade.py
 run fp8     tests/test_gpu_fp8.py
+run block   tests/test_gpu_block.py tests/test_gpu_mlp_block.py
+run sched   tests/test_gpu_scheduler.py
+run configs tests/test_gpu_configs.py
+run torchop tests/test_torch_ops.py
+run mtl     tests/test_mtl_surface.py
+run shard   tests/test_gpu_sharding_nccl.py
+run noalloc tests/test_zz_no_alloc.py
