@@ -178,6 +178,23 @@ def gpu_standin(dev, pairs=128, prefix=418, steps=64, warmup=4):
                     "vLLM-0.10 path, which cannot be installed offline"}
 
 
+def vllm_standin(e2e_value):
+    """The serving stack the reference sits on, stock, on this GPU: tools/vllm_standin.py in its own process (vLLM starts
+    an engine-core subprocess and wants half the GPU's memory: this process has released its engines by now).  Compared
+    with the E2E value — both include the prefill and are wall-clock around a generate call."""
+    import subprocess
+    here = os.path.dirname(os.path.abspath(__file__))
+    try:
+        r = subprocess.run([sys.executable, os.path.join(here, "tools", "vllm_standin.py")], capture_output=True, text=True,
+                           timeout=1200)
+        out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": f"{type(e).__name__}: {str(e)[:200]}"}
+    if "value" in out and e2e_value:
+        out["this_e2e_over_standin"] = e2e_value / out["value"]
+    return out
+
+
 def run_reference(args, rank, world):
     """Reference arm: the reference's CPU implementation of the path (no GPU code involved)."""
     if rank != 0:
@@ -278,6 +295,9 @@ def main():
     ap.add_argument("--no-b1", action="store_true")
     ap.add_argument("--no-probe", action="store_true", help="skip the CPU-oracle check of the e2e arm's first pair")
     ap.add_argument("--no-standin", action="store_true", help="skip the stock-library GPU stand-in leg")
+    ap.add_argument("--vllm-standin", action="store_true",
+                    help="also run stock vLLM (this image's 0.22) on a stock Llama of the T3 backbone's dimensions in a "
+                         "subprocess (tools/vllm_standin.py; its engine takes ~2.5 min to start, so it is not in the default run)")
     ap.add_argument("--no-fp8", action="store_true", help="skip the separately reported FP8-e4m3 weight leg")
     ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8_e4m3"],
                     help="profiling aid: run the WHOLE bench on FP8 weights (the line then says so; the default line is bf16)")
@@ -590,6 +610,8 @@ def main():
         line["gpu_standin"] = st
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline_sample()
+    if args.vllm_standin and world == 1:
+        line["gpu_standin_vllm"] = vllm_standin(line.get("e2e", {}).get("value"))
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
