@@ -41,6 +41,7 @@ for f in sorted(os.listdir(go)):
                       open(os.path.join(pr, "attn_traffic.json"), "w"))
 for f, out in (("launches.csv", f"{tag}_launches_B128.txt"), ("launches_B1.csv", f"{tag}_launches_B1.txt"),
                ("launches_B1_chain.csv", f"{tag}_launches_B1_five_kernel_chain.txt"),
+               ("launches_B1_two_launch.csv", f"{tag}_launches_B1_two_launch_layer.txt"),
                ("launches_fp8.csv", f"{tag}_launches_B128_fp8w.txt")):
     p = os.path.join(go, f)
     if os.path.exists(p):
