@@ -361,11 +361,13 @@ extern "C" int cbx_engine_set_fp8_weights(cbx_engine* e, const cbx_fp8_weights* 
 // Every projection that closes a residual branch adds into res in its epilogue, so a layer is
 //   T <= 4 (GEMV regime, 5 kernels): [norm+QKV+RoPE+KV-append] [attention] [O+res] [norm+gate_up+SiLU] [down+res]
 //   T  > 4 (tcgen05 regime, 7)     : [norm] [QKV+RoPE+KV-append] [attention] [O+res] [norm] [gate_up+SiLU] [down+res]
-// Rows at or below which the weight-streaming GEMV kernels run instead of the tcgen05 GEMM (they exist for 1, 2 and 4
-// padded rows).  env CBX_GEMV_MAX_T=0 forces the tcgen05 path everywhere: the switch-point sweep of tools/bench_bsweep.py.
+// Rows at or below which the weight-streaming GEMV kernels run instead of the tcgen05 GEMM (they exist for 1, 2, 4 and 8
+// padded rows; the fused attention block only up to 4).  Measured (tools/bench_bsweep.py, p50 step): 3 pairs 1.157 ms on
+// the GEMV kernels against 1.244 ms on the tcgen05 GEMMs, 4 pairs 1.216 against 1.244 — so the switch is at 8 rows.
+// env CBX_GEMV_MAX_T=0 forces the tcgen05 path everywhere, =4 the round-1 switch point.
 static int gemv_max_t() {
-  static const int v = getenv("CBX_GEMV_MAX_T") ? atoi(getenv("CBX_GEMV_MAX_T")) : 4;
-  return v < 0 ? 0 : (v > 4 ? 4 : v);
+  static const int v = getenv("CBX_GEMV_MAX_T") ? atoi(getenv("CBX_GEMV_MAX_T")) : 8;
+  return v < 0 ? 0 : (v > 8 ? 8 : v);
 }
 
 #ifdef CBX_EXPERIMENTS   // `make EXPERIMENTS=1` + env CBX_DUAL_MIN_ROWS=128: measured SLOWER (M1 3.46 -> 3.60-3.82 ms/step), see below

@@ -1,4 +1,4 @@
-// k_gemv.cu — fused weight-streaming GEMV family for T <= 4 rows (the b=1 / b=2 CFG-pair decode
+// k_gemv.cu — fused weight-streaming GEMV family for T <= 8 rows (1-4 CFG pairs: the latency / small-server decode
 // regime), one kernel per projection of a Llama layer:
 //
 //   QKV   : RMSNorm(res)·ln1 -> x·Wqkv^T -> RoPE -> q to the qkv buffer, k/v into the KV page
@@ -167,7 +167,7 @@ __device__ __forceinline__ void gemv_epilogue(const GemvArgs& a, int item, int r
   }
 }
 
-// TT = padded row count (1,2,4); KSEG = K / 1024 (1 or 4); NW = warps per CTA.
+// TT = padded row count (1,2,4,8); KSEG = K / 1024 (1 or 4); NW = warps per CTA.
 template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
 __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a) {
   constexpr int K = KSEG * 1024;
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gemv_fused_kernel(const GemvArgs a
     // After the fused attention block: the rows' O-proj output waits in the 64-bit fixed-point accumulator.  Close the
     // residual branch, x = bf16(bf16(acc * 2^-32) + x) (CTA 0 writes the rows back), then normalise.  Spread over all
     // warps: done by warps < TT alone, the 1024 64-bit conversions per lane-row cost 0.9 us per layer at b = 1.
-    __shared__ float s_ss[4][16];
+    __shared__ float s_ss[TT > 4 ? TT : 4][16];
     float ssl[TT];
 #pragma unroll
     for (int t = 0; t < TT; ++t) ssl[t] = 0.f;
@@ -616,7 +616,14 @@ int launch_stream(const GemvArgs& a, cudaStream_t s) {
 template <int TT, int KSEG, int PRO, int EPI, int NW, bool W8>
 int launch_w(const GemvArgs& a, int grid, cudaStream_t s) {
   constexpr int smem = TT * KSEG * 1024 * 2 + (KSEG > 1 ? NW * 2 * TT * 4 : 0);
-  static_assert(smem <= 48 * 1024, "x tile must fit the default dynamic smem limit");
+  if (smem > 48 * 1024) {                              // 8 rows x K = 4096: 65 KB, above the default dynamic limit
+    static bool attr = false;                          // per instantiation
+    if (!attr) {
+      cudaError_t e = cudaFuncSetAttribute(gemv_fused_kernel<TT, KSEG, PRO, EPI, NW, W8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) { set_error("gemv smem attribute (%d B): %s", smem, cudaGetErrorString(e)); return -2; }
+      attr = true;
+    }
+  }
   cudaError_t e = launch_pdl(gemv_fused_kernel<TT, KSEG, PRO, EPI, NW, W8>, dim3(grid), dim3(NW * 32), smem, s, a);
   if (e != cudaSuccess) { set_error("gemv launch failed: %s", cudaGetErrorString(e)); return -2; }
   count_launch();
@@ -639,7 +646,8 @@ template <int KSEG, int PRO, int EPI, int NW>
 int dispatch_t(const GemvArgs& a, int grid, cudaStream_t s) {
   if (a.T == 1) return launch<1, KSEG, PRO, EPI, NW>(a, grid, s);
   if (a.T == 2) return launch<2, KSEG, PRO, EPI, NW>(a, grid, s);
-  return launch<4, KSEG, PRO, EPI, NW>(a, grid, s);
+  if (a.T <= 4) return launch<4, KSEG, PRO, EPI, NW>(a, grid, s);
+  return launch<8, KSEG, PRO, EPI, NW>(a, grid, s);      // 5..8 rows: 3-4 CFG pairs (engine only, CBX_GEMV_MAX_T=8)
 }
 
 // one warp per item when that needs <= one CTA per SM, else 148 CTAs looping

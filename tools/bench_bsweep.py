@@ -30,4 +30,4 @@ for B in [int(x) for x in os.environ.get("PAIRS", "1,2,3,4,8,16,32").split(",")]
     d = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(100))
     out[B] = round(d[50], 4)
     eng.close()
-print(json.dumps({"gemv_max_t": os.environ.get("CBX_GEMV_MAX_T", "4"), "p50_step_ms_by_pairs": out}))
+print(json.dumps({"gemv_max_t": os.environ.get("CBX_GEMV_MAX_T", "8 (default)"), "p50_step_ms_by_pairs": out}))
