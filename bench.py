@@ -89,7 +89,7 @@ def cpu_baseline_sample(pairs=8, prefix=450, steps=4, warmup=1, model=None):
             "ms_per_step": 1e3 * r["decode_s"] / steps}
 
 
-KNOBS = ("CBX_SKIP", "CBX_MEGA", "CBX_GEMV_STREAM", "CBX_BLOCK_STOP", "CBX_BLOCK_NOACC", "CBX_BLOCK_FUSED", "CBX_MLP_FUSED", "CBX_GEMM_FOLD", "CBX_GEMM_SHALLOW", "CBX_DUAL_MIN_ROWS", "CBX_DUAL_ATTN_CTAS", "CBX_DUAL_CHAIN", "CBX_PDL",
+KNOBS = ("CBX_SKIP", "CBX_MEGA", "CBX_GEMV_STREAM", "CBX_BLOCK_STOP", "CBX_BLOCK_NOACC", "CBX_BLOCK_FUSED", "CBX_MLP_FUSED", "CBX_GEMM_FOLD", "CBX_GRAPH_BUCKETS", "CBX_GEMM_SHALLOW", "CBX_DUAL_MIN_ROWS", "CBX_DUAL_ATTN_CTAS", "CBX_DUAL_CHAIN", "CBX_PDL",
          "CBX_ATTN_BALANCED", "CBX_ATTN_SMALL", "CBX_O_UNSPLIT", "CBX_SPLIT_MAX_ROWS", "CBX_L2_PREFETCH", "CBX_GEMM_MC",
          "CBX_ATTN_PLAN_EACH", "CBX_PREFILL_ROWWISE", "CBX_BENCH_LAYERS", "CBX_GEMV_MAX_T")
 

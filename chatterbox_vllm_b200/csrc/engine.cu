@@ -45,6 +45,7 @@ int gemm_partials(const void*, const void*, void*, int, int, int, int, cudaStrea
 int gemm_partials_fold(const void* x, const void* W, void* part, int M, int K, int splits, cudaStream_t s, void* res,
                        const void* ln_w, void* h_out, float eps, void* counters);
 bool layer_attn_block_supported(int T, int max_kv_len);
+int layer_attn_block_max_len(int T);
 int layer_attn_block(const void* res, const void* ln_w, const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos,
                      const int64_t* slot, void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq,
                      const int32_t* kv_len, void* acc, void* q_out, int T, float eps, cudaStream_t s);
@@ -732,9 +733,16 @@ extern "C" int cbx_engine_decode(cbx_engine* e, int B, int n_steps, int max_kv_l
     // page buffers hold the context (so: buckets of 64 tokens); for more rows only the unbalanced attention plan — the
     // balanced kernel cuts its page ranges on the device from kv_len, so ONE graph serves every context length and a
     // long generation does not re-capture every 64 steps.
+    // At T <= 4 the same holds while the fused attention block takes the step (its page buffer holds up to 1921 tokens at
+    // one pair): the graph is captured for the block's longest context and serves every shorter one — a single request
+    // no longer pays a capture every 64 tokens.
     static const bool balanced = !(getenv("CBX_ATTN_BALANCED") && getenv("CBX_ATTN_BALANCED")[0] == '0');
-    const bool any_len = balanced && 2 * B > 4 && 2 * B <= 4095;
-    const int bucket = any_len ? e->cfg.max_model_len : (max_kv_len + 63) / 64 * 64;
+    const int T2 = 2 * B;
+    const bool any_len = balanced && T2 > 4 && T2 <= 4095;
+    static const bool buckets_only = getenv("CBX_GRAPH_BUCKETS") && getenv("CBX_GRAPH_BUCKETS")[0] == '1';   // A/B aid: round-1 keys
+    const bool block_len = !buckets_only && T2 <= 4 && T2 <= gemv_max_t() && !e->fp8 && !e->skip && !e->l2_prefetch && !e->mega &&
+                           layer_attn_block_supported(T2, max_kv_len);
+    const int bucket = any_len ? e->cfg.max_model_len : block_len ? layer_attn_block_max_len(T2) : (max_kv_len + 63) / 64 * 64;
     auto key = std::make_pair(B, bucket);
     auto itr = e->graphs.find(key);
     if (itr == e->graphs.end()) {

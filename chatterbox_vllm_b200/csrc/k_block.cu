@@ -580,6 +580,12 @@ bool layer_attn_block_supported(int T, int max_kv_len) {
   const int TT = T == 1 ? 1 : (T == 2 ? 2 : 4);
   return max_kv_len - 1 <= (kSlices / TT) * kCl * CBX_BLOCK_SIZE;
 }
+// longest context (incl. the new token) the block takes for T rows; 0 when it is switched off or T is out of range
+int layer_attn_block_max_len(int T) {
+  if (T < 1 || T > 4 || !block_on()) return 0;
+  const int TT = T == 1 ? 1 : (T == 2 ? 2 : 4);
+  return (kSlices / TT) * kCl * CBX_BLOCK_SIZE + 1;
+}
 // acc: [4][1024] u64, zero on entry; on return (stream order) it holds the O-proj output of the T rows in 2^-32 fixed point
 int layer_attn_block(const void* res, const void* ln_w, const void* Wqkv, const void* Wo, const void* cos_sin, const int32_t* pos,
                      const int64_t* slot, void* kv_layer, const int32_t* bt, int bt_stride, const int32_t* row_seq,
