@@ -85,6 +85,7 @@ _PROTOS = {
     "cbx_debug_sampler_radix_pivot": (C.c_int, [C.c_int]),
     "cbx_decode_prepare": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
     "cbx_prefill_embed": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]),
+    "cbx_prefill_rows": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp]),
     "cbx_cond_workspace_bytes": (C.c_int64, [C.c_int]),
     "cbx_cond_encode": (C.c_int, [vp, vp, vp, C.c_int, C.c_float, vp, vp, vp]),
     "cbx_cond_emotion_row": (C.c_int, [vp, C.c_float, vp, vp]),

@@ -173,6 +173,46 @@ extern "C" int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, con
   return 0;
 }
 
+// ---------------------------------------------------------------- prefill row descriptors
+// What T3Engine.prefill built row by row with numpy (51 200 rows at M1): the descriptor, position, block-table row and
+// context length of every prefill row, from one record per SEQUENCE (a pair contributes two: cond and uncond).
+// seq[s] = {first row, rows P, text tokens nt, index into cond_emb, uncond (0/1), block-table row, offset of its text ids,
+// offset of its history}; a sequence's rows are [34 conditioning rows] [nt text rows] [start-of-speech] [P-35-nt history
+// rows] (t3.py:229-262 layout; the uncond member's text rows are zeros, t3.py:548-569; history rows carry tokens
+// generated before a preemption).  One thread per row, binary search over the sequences' first rows.
+__global__ void __launch_bounds__(256) prefill_rows_kernel(const int32_t* __restrict__ seq, int n_seq,
+                                                           const int32_t* __restrict__ text_ids,
+                                                           const int32_t* __restrict__ hist, int T, int4* __restrict__ desc,
+                                                           int32_t* __restrict__ pos, int32_t* __restrict__ row_seq,
+                                                           int32_t* __restrict__ kv_len) {
+  const int r = blockIdx.x * 256 + threadIdx.x;
+  if (r >= T) return;
+  int lo = 0, hi = n_seq - 1;
+  while (lo < hi) {                                    // last sequence whose first row is <= r
+    const int mid = (lo + hi + 1) >> 1;
+    if (seq[mid * 8] <= r) lo = mid; else hi = mid - 1;
+  }
+  const int32_t* q = seq + lo * 8;
+  const int i = r - q[0], nt = q[2];
+  int4 d;
+  if (i < 34) d = make_int4(0, q[3], i, 0);
+  else if (i < 34 + nt) d = q[4] ? make_int4(2, 0, 0, 0) : make_int4(1, text_ids[q[6] + i - 34], i - 34, 0);
+  else if (i == 34 + nt) d = make_int4(3, 6561, 0, 0);
+  else d = make_int4(4, hist[q[7] + i - 35 - nt], 0, 0);
+  desc[r] = d;
+  pos[r] = i;
+  row_seq[r] = q[5];
+  kv_len[r] = i + 1;
+}
+extern "C" int cbx_prefill_rows(const int32_t* seq, int n_seq, const int32_t* text_ids, const int32_t* hist, int T,
+                                int32_t* desc, int32_t* pos, int32_t* row_seq, int32_t* kv_len, void* stream) {
+  if (T <= 0 || n_seq <= 0) return 0;
+  CBX_REQUIRE(seq && text_ids && desc && pos && row_seq && kv_len, "cbx_prefill_rows: NULL argument");
+  prefill_rows_kernel<<<(T + 255) / 256, 256, 0, (cudaStream_t)stream>>>(seq, n_seq, text_ids, hist, T, (int4*)desc, pos, row_seq, kv_len);
+  CBX_CHECK_LAUNCH("prefill_rows");
+  return 0;
+}
+
 // ---------------------------------------------------------------- (add +) RMSNorm -----
 // One CTA of 128 threads per row; each thread owns 8 contiguous elements (one 16-byte
 // load).  Rounding points follow vLLM: z = bf16(x + res); out = bf16(bf16(z·rstd)·w).

@@ -352,37 +352,27 @@ class T3Engine:
                 j1 += 1
             if j1 == j0:
                 raise ValueError("max_rows too small for one pair's prefix")
-            # per-row descriptors, positions and block-table rows, built with numpy (51 200 rows at M1)
-            desc_p, pos_p, rseq_p, last = [], [], [], {}
+            # one record per SEQUENCE goes to the device; the per-row descriptors, positions, block-table rows and context
+            # lengths (51 200 rows at M1) are written there, straight into the step buffers (cbx_prefill_rows)
+            seq, text_flat, hist_flat, last = [], [], [], {}
             starts, plens, btrows = [], [], []
-            cond_rows = np.zeros((COND_LEN, 4), np.int32)
-            cond_rows[:, 2] = np.arange(COND_LEN)
-            sos_row = np.array([[3, START_SPEECH, 0, 0]], np.int32)
-            T = 0
+            T = t_off = h_off = 0
             for j in range(j0, j1):
-                ids = np.asarray(reqs[j].text_ids, np.int32)
-                nt = len(ids)
-                cond_rows[:, 1] = j
-                text_c = np.zeros((nt, 4), np.int32)
-                text_c[:, 0], text_c[:, 1], text_c[:, 2] = 1, ids, np.arange(nt)
-                text_u = np.zeros((nt, 4), np.int32)
-                text_u[:, 0] = 2
-                hist = np.zeros((len(reqs[j].history), 4), np.int32)      # generated tokens: decode embeddings, both members
-                hist[:, 0], hist[:, 1] = 4, np.asarray(reqs[j].history, np.int32)
-                desc_p += [cond_rows.copy(), text_c, sos_row, hist, cond_rows.copy(), text_u, sos_row, hist]
-                ar = np.arange(P[j], dtype=np.int32)
+                nt, nh = len(reqs[j].text_ids), len(reqs[j].history)
+                text_flat.extend(int(t) for t in reqs[j].text_ids)
+                hist_flat.extend(int(t) for t in reqs[j].history)   # generated tokens: decode embeddings, both members
                 for half in range(2):
-                    starts.append(T), plens.append(P[j]), btrows.append(half * B + slots[j])
-                    pos_p.append(ar)
-                    rseq_p.append(np.full(P[j], half * B + slots[j], np.int32))
+                    row = half * B + slots[j]
+                    seq.append((T, P[j], nt, j, half, row, t_off, h_off))
+                    starts.append(T), plens.append(P[j]), btrows.append(row)
                     T += P[j]
                     last[half * n + j] = T - 1
-            d_desc = torch.from_numpy(np.concatenate(desc_p)).to(dev)
-            d_pos = torch.from_numpy(np.concatenate(pos_p)).to(dev)
-            d_rseq = torch.from_numpy(np.concatenate(rseq_p)).to(dev)
-            self.buffer("pos", (T,), torch.int32).copy_(d_pos)
-            self.buffer("row_seq", (T,), torch.int32).copy_(d_rseq)
-            self.buffer("kv_len", (T,), torch.int32).copy_(d_pos + 1)
+                t_off += nt
+                h_off += nh
+            i32 = lambda v: torch.tensor(v if len(v) else [0], dtype=torch.int32).to(dev)  # noqa: E731
+            d_pos, d_rseq = self.buffer("pos", (T,), torch.int32), self.buffer("row_seq", (T,), torch.int32)
+            d_desc, _, _, _ = ops.prefill_rows(i32(seq).view(-1, 8), i32(text_flat), i32(hist_flat), T, pos=d_pos, row_seq=d_rseq,
+                                               kv_len=self.buffer("kv_len", (T,), torch.int32))
             self.buffer("slot", (T,), torch.int64).copy_(ops.slot_mapping(self.block_table, d_rseq, d_pos))
             ops.prefill_embed(d_desc, cond, self.text_emb, self.text_pos, self.speech_emb, self.speech_pos, out=x[:T])
             items = ops.prefill_items(starts, plens, btrows).to(dev)       # causal attention: 16 query rows per item

@@ -353,6 +353,20 @@ def prefill_embed(desc, cond_emb, text_emb, text_pos, speech_emb, speech_pos, ou
     return out
 
 
+def prefill_rows(seq, text_ids, hist, T: int, desc=None, pos=None, row_seq=None, kv_len=None):
+    """cbx_prefill_rows: per-row descriptors / positions / block-table rows / context lengths of a prefill step from one
+    int32 [n_seq, 8] record per sequence (see include/cbx_t3.h).  Returns (desc [T,4], pos, row_seq, kv_len)."""
+    dev = seq.device
+    new = lambda *shape: torch.empty(*shape, dtype=torch.int32, device=dev)  # noqa: E731
+    desc = new(T, 4) if desc is None else desc
+    pos = new(T) if pos is None else pos
+    row_seq = new(T) if row_seq is None else row_seq
+    kv_len = new(T) if kv_len is None else kv_len
+    check(load().cbx_prefill_rows(_p(seq, torch.int32), seq.shape[0], _p(text_ids, torch.int32), _p(hist, torch.int32), T,
+                                  _p(desc), _p(pos), _p(row_seq), _p(kv_len), _stream()), "prefill_rows")
+    return desc, pos, row_seq, kv_len
+
+
 def postprocess_tokens(sb: "SamplerBuffers", slots: torch.Tensor, dst: torch.Tensor, dst_rows: torch.Tensor,
                        dst_len: torch.Tensor, tail_crop: int = 2, guard_cap: torch.Tensor | None = None,
                        sos: int = 6561, eos: int = 6562) -> None:

@@ -288,6 +288,15 @@ int cbx_prefill_embed(const int32_t* desc, const float* cond_emb, const void* te
                       const void* text_pos, const void* speech_emb, const void* speech_pos,
                       void* x, int T, void* stream);
 
+/* The rows of a prefill step from one record per sequence (T3MultiModalProcessor.apply's layout, t3.py:229-262, for both
+ * members of every CFG pair): seq int32 [n_seq,8] = {first row, rows P, text tokens nt, request index into cond_emb,
+ * uncond member (0/1), block-table row, offset of the sequence's ids in text_ids, offset of its history in hist}, sorted
+ * by first row; rows of a sequence = 34 conditioning rows, nt text rows (zero rows for the uncond member), start-of-speech,
+ * P-35-nt history rows (tokens generated before a preemption).  Writes desc [T,4] (cbx_prefill_embed's), pos, row_seq and
+ * kv_len = pos + 1.  Replaces the per-row Python the reference runs in apply / get_input_embeddings for every request. */
+int cbx_prefill_rows(const int32_t* seq, int n_seq, const int32_t* text_ids, const int32_t* hist, int T,
+                     int32_t* desc, int32_t* pos, int32_t* row_seq, int32_t* kv_len, void* stream);
+
 /* ---- engine: the whole T3 step behind one handle -------------------------------- */
 
 typedef struct cbx_weights {

@@ -508,3 +508,45 @@ def test_paged_attention_prefill_is_deterministic(ops):
         if ref is None:
             ref = cur
         assert torch.equal(cur, ref), "prefill attention: same inputs, different bits"
+
+
+def test_prefill_rows_equal_the_row_by_row_builder(ops):
+    """cbx_prefill_rows against the numpy builder T3Engine.prefill used before it (the reference's per-request Python of
+    T3MultiModalProcessor.apply / get_input_embeddings, t3.py:229-262,548-569, for both members of every pair): ragged
+    text lengths, histories of preempted requests, scattered block-table rows.  Integer work: bit-exact."""
+    rng = np.random.default_rng(5)
+    B = 37
+    seq, text_flat, hist_flat, want_desc, want_pos, want_rseq = [], [], [], [], [], []
+    T = t_off = h_off = 0
+    for j in range(9):
+        nt = int(rng.integers(1, 60))
+        nh = int(rng.integers(0, 40)) if j % 3 == 0 else 0
+        ids = rng.integers(0, 700, nt).astype(np.int32)
+        hist = rng.integers(0, 6561, nh).astype(np.int32)
+        P = 34 + nt + 1 + nh
+        slot = int(rng.integers(0, B))
+        text_flat += ids.tolist()
+        hist_flat += hist.tolist()
+        cond_rows = np.zeros((34, 4), np.int32)
+        cond_rows[:, 1], cond_rows[:, 2] = j, np.arange(34)
+        text_c = np.zeros((nt, 4), np.int32)
+        text_c[:, 0], text_c[:, 1], text_c[:, 2] = 1, ids, np.arange(nt)
+        text_u = np.zeros((nt, 4), np.int32)
+        text_u[:, 0] = 2
+        hrows = np.zeros((nh, 4), np.int32)
+        hrows[:, 0], hrows[:, 1] = 4, hist
+        sos = np.array([[3, 6561, 0, 0]], np.int32)
+        for half, text in ((0, text_c), (1, text_u)):
+            seq.append((T, P, nt, j, half, half * B + slot, t_off, h_off))
+            want_desc += [cond_rows, text, sos, hrows]
+            want_pos.append(np.arange(P, dtype=np.int32))
+            want_rseq.append(np.full(P, half * B + slot, np.int32))
+            T += P
+        t_off += nt
+        h_off += nh
+    i32 = lambda v: torch.tensor(v if len(v) else [0], dtype=torch.int32).cuda()  # noqa: E731
+    desc, pos, rseq, kvl = ops.prefill_rows(i32(seq).view(-1, 8), i32(text_flat), i32(hist_flat), T)
+    assert np.array_equal(desc.cpu().numpy(), np.concatenate(want_desc))
+    assert np.array_equal(pos.cpu().numpy(), np.concatenate(want_pos))
+    assert np.array_equal(rseq.cpu().numpy(), np.concatenate(want_rseq))
+    assert np.array_equal(kvl.cpu().numpy(), np.concatenate(want_pos) + 1)
