@@ -81,6 +81,7 @@ class T3Engine:
         self.use_graph, self.base_seed, self._next_uid = use_graph, base_seed, 0
         # a dedicated non-default stream: CUDA graphs cannot be captured on the legacy stream
         self.stream = torch.cuda.Stream(device=self.device)
+        self._copy_stream = torch.cuda.Stream(device=self.device)   # host->device copies of prefill metadata (prefill())
         self._load_weights(state_dict, rms_eps)
         self.bt_stride = -(-max_model_len // BLOCK_SIZE)
         if num_blocks is None:
@@ -340,16 +341,39 @@ class T3Engine:
             names = (("res", (2 * B, HIDDEN), BF16), ("pos", (2 * B,), torch.int32), ("slot", (2 * B,), torch.int64),
                      ("kv_len", (2 * B,), torch.int32), ("row_seq", (2 * B,), torch.int32))
             staged = [(self.buffer(*nm), self.buffer(*nm).clone()) for nm in names]
-        cond = torch.stack([r.cond_emb.to(torch.float32) for r in reqs]).to(dev).contiguous()
+        # the conditioning rows go up request by request (pinned host tensors copy asynchronously; a torch.stack on the host
+        # would make one pageable 18 MB tensor at M1 and a blocking copy)
+        cond = torch.empty(n, COND_LEN, HIDDEN, dtype=torch.float32, device=dev)
+        for i, r in enumerate(reqs):
+            cond[i].copy_(r.cond_emb, non_blocking=True)
         h_last = torch.empty(2 * n, HIDDEN, dtype=BF16, device=dev)
         x = self.buffer("x", (self.max_rows, HIDDEN), BF16)
         h = self.buffer("h", (self.max_rows, HIDDEN), BF16)
-        j0 = 0
+        # ---- per chunk: host work, host->device copies on a COPY stream, then the chunk's kernels on the engine's stream.
+        # (With the copies on the engine's stream each pageable copy waited, in stream order, for the previous chunk's
+        # 16 ms of GPU work, and the host work of the next chunk — ~2 ms — then sat exposed between chunks: 8 ms of a 74 ms
+        # M1 prefill.  Now the host plans chunk k+1 while the GPU runs chunk k.)
+        # Chunks of at most max_rows rows, of EQUAL size: a short last chunk (M1: 40 + 40 + 40 + 8 pairs) runs the small-M
+        # GEMM configurations at a fraction of the big chunks' rate.  A pair joins chunk k while its midpoint lies in front
+        # of the k-th equal cut of the row total.
+        main = torch.cuda.current_stream()
+        def up(v, dtype=torch.int32):                         # noqa: E306  host list -> device tensor, on the copy stream
+            with torch.cuda.stream(self._copy_stream):
+                t = torch.tensor(v if len(v) else [0], dtype=dtype).to(dev)
+            t.record_stream(main)
+            return t
+        i32 = up
+        total_rows = 2 * sum(P)
+        target = total_rows / max(1, -(-total_rows // self.max_rows))
+        plan = []
+        j0 = rows_done = k_chunk = 0
         while j0 < n:
             j1, rows = j0, 0
-            while j1 < n and rows + 2 * P[j1] <= self.max_rows:
+            k_chunk += 1
+            while j1 < n and rows + 2 * P[j1] <= self.max_rows and (rows == 0 or rows_done + rows + P[j1] <= k_chunk * target):
                 rows += 2 * P[j1]
                 j1 += 1
+            rows_done += rows
             if j1 == j0:
                 raise ValueError("max_rows too small for one pair's prefix")
             # one record per SEQUENCE goes to the device; the per-row descriptors, positions, block-table rows and context
@@ -369,24 +393,31 @@ class T3Engine:
                     last[half * n + j] = T - 1
                 t_off += nt
                 h_off += nh
-            i32 = lambda v: torch.tensor(v if len(v) else [0], dtype=torch.int32).to(dev)  # noqa: E731
+            items_h = ops.prefill_items(starts, plens, btrows)             # causal attention: 16 query rows per item
+            if os.environ.get("CBX_PREFILL_ROWWISE") == "1":      # debugging aid: causal prefill row by row through the decode kernel
+                items_h = items_h[:0]
+            with torch.cuda.stream(self._copy_stream):
+                items = items_h.to(dev)
+            items.record_stream(main)
+            seqs = sorted(last)
+            max_p, d_seq, d_text, d_hist = max(P[j0:j1]), i32(seq).view(-1, 8), i32(text_flat), i32(hist_flat)
+            dst_rows, src_rows = up(seqs, torch.int64), up([last[q] for q in seqs], torch.int64)
+            main.wait_stream(self._copy_stream)
+            plan.append((d_seq, d_text, d_hist, items, dst_rows, src_rows))   # alive until the chunks have been enqueued
+            j0 = j1
+            # ---- the chunk's kernels
             d_pos, d_rseq = self.buffer("pos", (T,), torch.int32), self.buffer("row_seq", (T,), torch.int32)
-            d_desc, _, _, _ = ops.prefill_rows(i32(seq).view(-1, 8), i32(text_flat), i32(hist_flat), T, pos=d_pos, row_seq=d_rseq,
+            d_desc, _, _, _ = ops.prefill_rows(d_seq, d_text, d_hist, T, pos=d_pos, row_seq=d_rseq,
                                                kv_len=self.buffer("kv_len", (T,), torch.int32))
             self.buffer("slot", (T,), torch.int64).copy_(ops.slot_mapping(self.block_table, d_rseq, d_pos))
             ops.prefill_embed(d_desc, cond, self.text_emb, self.text_pos, self.speech_emb, self.speech_pos, out=x[:T])
-            items = ops.prefill_items(starts, plens, btrows).to(dev)       # causal attention: 16 query rows per item
-            if os.environ.get("CBX_PREFILL_ROWWISE") == "1":      # debugging aid: causal prefill row by row through the decode kernel
-                items = items[:0]
             check(load().cbx_engine_set_prefill_items(self._h, items.data_ptr() if items.shape[0] else None, items.shape[0]),
                   "set_prefill_items")
             try:
-                self.forward(T, max(P[j0:j1]))
+                self.forward(T, max_p)
             finally:
                 check(load().cbx_engine_set_prefill_items(self._h, None, 0), "set_prefill_items")
-            seqs = sorted(last)
-            h_last[torch.tensor(seqs, device=dev)] = h[torch.tensor([last[q] for q in seqs], device=dev)]
-            j0 = j1
+            h_last[dst_rows] = h[src_rows]
         h[:2 * n].copy_(h_last)
         self.buffer("head_rows", (2 * n,), torch.int32).copy_(torch.arange(2 * n, dtype=torch.int32, device=dev))
         if whole:
