@@ -246,7 +246,7 @@ def run_cfg3(args, rank, world, local):
     rng = random.Random(3)
     n_prompts, gen = 400, 390
     n_text = [rng.choice(lens) for _ in range(n_prompts)]
-    eng = T3Engine(random_state_dict(30, device=dev, seed=0), device=dev, max_pairs=256, max_model_len=1000, max_rows=16384,
+    eng = T3Engine(random_state_dict(30, device=dev, seed=0), device=dev, max_pairs=256, max_model_len=1000, max_rows=17408,
                    base_seed=1234)
     sp = SamplingParams(temperature=0.5, top_p=0.5, repetition_penalty=2.0, max_tokens=gen, ignore_eos=True)
     mk = lambda: [Request(random_prompt(n, seed=i), random_cond_emb(i, pinned=True), sp, uid=1 + i)   # noqa: E731
@@ -304,7 +304,7 @@ def main():
     ap.add_argument("--config", default="m1", choices=["m1", "cfg3"],
                     help="m1 (default): the BASELINE metric's workload, weak scaling; cfg3: 400 benchmark-text prompts, strong "
                          "scaling through the product's sharded generate (its own JSON line, not the driver's metric)")
-    ap.add_argument("--max-rows", type=int, default=16384, help="row capacity of the engine's step buffers (prefill chunk size)")
+    ap.add_argument("--max-rows", type=int, default=17408, help="row capacity of the engine's step buffers (prefill chunk size)")
     ap.add_argument("--prefix", type=int, default=None,
                     help="profiling aid: prompt rows per sequence (default 200, the M1 workload); with --ctx0 it puts the first "
                          "timed step at that context after the warm-up steps alone, so a profiler has few launches to skip")
@@ -503,7 +503,7 @@ def main():
         del eng
         torch.cuda.empty_cache()
         e8 = T3Engine(random_state_dict(n_layers, device=dev, seed=0), device=dev, max_pairs=B, max_model_len=max_len,
-                      max_rows=16384, base_seed=1234 + rank, weight_dtype="fp8_e4m3")
+                      max_rows=17408, base_seed=1234 + rank, weight_dtype="fp8_e4m3")
         K8 = min(K, 128)
         L8 = max(PREFIX + 1 + W, PREFIX + GEN // 2 - K8 // 2)
         pre8 = L8 - PREFIX - 1

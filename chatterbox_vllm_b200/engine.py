@@ -87,7 +87,9 @@ class T3Engine:
         if num_blocks is None:
             num_blocks = 2 * max_pairs * self.bt_stride + 1
         self.num_blocks = num_blocks
-        self.max_rows = max_rows or max(2 * max_pairs, 8192)
+        # step-buffer rows = the largest prefill chunk.  17 408 rows = 136 row tiles: the prefill GEMM grids then come to whole
+        # numbers of waves on 148 SMs x 2 CTAs (measured at M1: three chunks of 17 067 rows 65.6 ms, four of 12 800 67.9 ms)
+        self.max_rows = max_rows or max(2 * max_pairs, 17408)
         self.kv_cache = torch.zeros(self.n_layers * num_blocks * PAGE_BYTES, dtype=torch.uint8, device=self.device)
         self.block_table = torch.zeros(2 * max_pairs, self.bt_stride, dtype=torch.int32, device=self.device)
         self.pool = ops.BlockPool(num_blocks)
