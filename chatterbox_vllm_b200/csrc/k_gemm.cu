@@ -505,8 +505,12 @@ __global__ void __launch_bounds__(W8 ? kThreads8 : kThreads, W8 ? 1 : 2) gemm_tc
     }
   }
   if (threadIdx.x == 0) PROF(6);
-  if (CN > 1)      // nobody leaves while the leader's MMAs may still read this CTA's shared memory / TMEM
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  // nobody leaves while the leader's MMAs may still read this CTA's shared memory / TMEM.  An EXECUTION barrier only: no data
+  // passes between the CTAs here, so the arrive is .relaxed — the default .release is a MEMBAR.ALL.GPU that made every CTA
+  // wait for its epilogue's global stores to be acknowledged before it could leave (20 % of the QKV prefill GEMM's stall
+  // samples, profiles/r02_ncu_prefill_qkv_stalls.txt)
+  if (CN > 1)
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
   if (warp == 2) {
     tc_fence_after();
     if (CN == 1) tmem_dealloc(tmem_base, BN);
