@@ -310,6 +310,7 @@ __global__ void __launch_bounds__(kNW * 32, 1) layer_attn_block_kernel(const Blo
 
   // ---- QKV: one row pair per warp (the GEMV kernel's summation order: the appended K/V carry the same bits) -----
   float f1, f2;                                        // lane t: the pair's values for row t, bf16-rounded
+  bf16 kv_b1, kv_b2;                                   // ... as bf16: stored to q_out / the KV page at the END of the kernel
   {
     float acc[2][TT];
 #pragma unroll
@@ -341,25 +342,8 @@ __global__ void __launch_bounds__(kNW * 32, 1) layer_attn_block_kernel(const Blo
       o1 = x1 * rc - x2 * rs;
       o2 = x2 * rc + x1 * rs;
     }
-    const bf16 b1 = __float2bfloat16_rn(o1), b2 = __float2bfloat16_rn(o2);
-    f1 = __bfloat162float(b1); f2 = __bfloat162float(b2);
-    if (lane < T) {
-      if (which == 0) {
-        if (a.q_out) { bf16* q = a.q_out + (size_t)lane * 3072 + h * 64; q[pi] = b1; q[pi + 32] = b2; }
-      } else if (my_slot >= 0) {                       // append the new token's K / V to its page
-        uint8_t* page = a.kv_layer + (size_t)(my_slot / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
-        const int tok = (int)(my_slot % CBX_BLOCK_SIZE);
-        if (which == 1) {                              // K: 16-byte chunks XOR-swizzled by tok & 7
-          uint8_t* kt = page + h * 2048 + tok * 128;
-          const int c1 = (pi >> 3) ^ (tok & 7), c2 = ((pi + 32) >> 3) ^ (tok & 7);
-          *reinterpret_cast<bf16*>(kt + c1 * 16 + (pi & 7) * 2) = b1;
-          *reinterpret_cast<bf16*>(kt + c2 * 16 + (pi & 7) * 2) = b2;
-        } else {
-          bf16* vt = reinterpret_cast<bf16*>(page + 32768 + h * 2048 + tok * 128);
-          vt[pi] = b1; vt[pi + 32] = b2;
-        }
-      }
-    }
+    kv_b1 = __float2bfloat16_rn(o1); kv_b2 = __float2bfloat16_rn(o2);
+    f1 = __bfloat162float(kv_b1); f2 = __bfloat162float(kv_b2);
   }
   BPROF(4);
   if (a.stop == 3) return;
@@ -533,6 +517,25 @@ __global__ void __launch_bounds__(kNW * 32, 1) layer_attn_block_kernel(const Blo
           if (c == 0 && t < T)                         // RED.ADD.64: fire and forget, ordered by kernel completion
             atomicAdd(a.acc + (size_t)t * 1024 + g * 4 + (lane >> 3), (unsigned long long)__float2ll_rn(s * kAccScale));
         }
+      }
+    }
+  }
+  // ---- the new token's K / V go to their page LAST (and q to q_out): this step's attention took them from shared memory;
+  // stored before the cluster barriers, their .release (a GPU-scope fence) would wait for these stores to be acknowledged
+  if (lane < T) {
+    if (which == 0) {
+      if (a.q_out) { bf16* q = a.q_out + (size_t)lane * 3072 + h * 64; q[pi] = kv_b1; q[pi + 32] = kv_b2; }
+    } else if (my_slot >= 0) {                         // append the new token's K / V to its page
+      uint8_t* page = a.kv_layer + (size_t)(my_slot / CBX_BLOCK_SIZE) * CBX_PAGE_BYTES;
+      const int tok = (int)(my_slot % CBX_BLOCK_SIZE);
+      if (which == 1) {                                // K: 16-byte chunks XOR-swizzled by tok & 7
+        uint8_t* kt = page + h * 2048 + tok * 128;
+        const int c1 = (pi >> 3) ^ (tok & 7), c2 = ((pi + 32) >> 3) ^ (tok & 7);
+        *reinterpret_cast<bf16*>(kt + c1 * 16 + (pi & 7) * 2) = kv_b1;
+        *reinterpret_cast<bf16*>(kt + c2 * 16 + (pi & 7) * 2) = kv_b2;
+      } else {
+        bf16* vt = reinterpret_cast<bf16*>(page + 32768 + h * 2048 + tok * 128);
+        vt[pi] = kv_b1; vt[pi + 32] = kv_b2;
       }
     }
   }
